@@ -1,0 +1,189 @@
+/*
+ * zb200.h — C ABI of the B200-native Alard–Lupton image-subtraction path.
+ *
+ * This library replaces the `hotpants` executable that zuds fork/execs for every
+ * image pair (zuds/subtraction.py:162, command line built by zuds/hotpants.py:77-93).
+ * The reference crosses that boundary with FITS files and argv; here the same
+ * inputs cross as plain pointers + a parameter struct.  No C++/torch types.
+ *
+ * Entry point            replaces (reference file:line)
+ * ---------------------  ------------------------------------------------------
+ * zb_params_default      hotpants/vargs.c:55-128      (defaults of every flag)
+ * zb_params_check        hotpants/vargs.c:482-647     (FATAL ERROR sanity checks)
+ * zb_sizes               hotpants/main.c:382-428,535-555 (derived sizes, region grid)
+ * zb_subtract            hotpants/main.c:606-1867     (per-region loop: masks, stamp
+ *                        search, fit, spatial_convolve, subtract, noise, output mask, QA)
+ * zb_subtract_host       same, with host buffers (what subprocess.check_call +
+ *                        FITS I/O deliver in the reference, zuds/subtraction.py:162)
+ * zb_region_info etc.    per-region FITS keywords hotpants/main.c:1719-1819 and the
+ *                        -hki kernel table main.c:573-579,1824-1835
+ *
+ * Conventions: images are row-major, x fastest, idx = x + nx*y (main.c:648-652);
+ * float32 pixels; device pointers unless the name says host.  Return 0 on
+ * success, negative zb_status on error (zb_last_error gives the text).  The
+ * caller owns every buffer; a ctx owns only its private workspace and is used by
+ * one host thread at a time.
+ */
+#ifndef ZB200_H
+#define ZB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ZB_MAX_GAUSS   8
+#define ZB_MAX_KSS     8     /* max -nss (sub-stamp centres kept per stamp) */
+
+/* hotpants mask bits, hotpants/defaults.h:4-19 */
+#define ZB_FLAG_BAD_PIXVAL   0x01
+#define ZB_FLAG_SAT_PIXEL    0x02
+#define ZB_FLAG_LOW_PIXEL    0x04
+#define ZB_FLAG_ISNAN        0x08
+#define ZB_FLAG_BAD_CONV     0x10
+#define ZB_FLAG_INPUT_MASK   0x20
+#define ZB_FLAG_OK_CONV      0x40
+#define ZB_FLAG_INPUT_ISBAD  0x80
+#define ZB_FLAG_T_BAD        0x100
+#define ZB_FLAG_T_SKIP       0x200
+#define ZB_FLAG_I_BAD        0x400
+#define ZB_FLAG_I_SKIP       0x800
+#define ZB_FLAG_OUTPUT_ISBAD 0x8000
+
+typedef enum zb_status {
+    ZB_OK              =  0,
+    ZB_ERR_PARAM       = -1,   /* a vargs.c FATAL ERROR condition */
+    ZB_ERR_UNSUPPORTED = -2,   /* valid hotpants option outside this build's scope */
+    ZB_ERR_CUDA        = -3,
+    ZB_ERR_NOMEM       = -4,
+    ZB_ERR_INTERNAL    = -5
+} zb_status;
+
+/* mask element types accepted for -imi / -tmi */
+#define ZB_MASK_U8   1
+#define ZB_MASK_I16  2
+#define ZB_MASK_I32  4
+
+/* zb_region_info.flags */
+#define ZB_REGION_SKIPPED   0x1   /* no usable stamps: region left untouched, main.c:1002-1009 */
+#define ZB_REGION_SINGULAR  0x2   /* ludcmp saw an all-zero row, alard.c:1480-1493 (ignored, as in hotpants) */
+#define ZB_REGION_RETRIED   0x4   /* stamp search redone with kerFitThresh*scaleFitThresh, main.c:948-995 */
+
+/* Mirrors the hotpants globals that the path uses (hotpants/globals.h:27-60). */
+typedef struct zb_params {
+    int32_t nx, ny;                                   /* NAXIS1, NAXIS2 */
+    int32_t hw_kernel, hw_ksstamp, n_ksstamps;        /* -r -rss -nss */
+    int32_t ker_order, bg_order;                      /* -ko -bgo */
+    int32_t nreg_x, nreg_y, nstamp_x, nstamp_y;       /* -nrx -nry -nsx -nsy */
+    int32_t kc_step;                                  /* -kcs, 0 => fwKernel */
+    int32_t ngauss;                                   /* -ng */
+    int32_t deg[ZB_MAX_GAUSS];
+    float   beta[ZB_MAX_GAUSS];                       /* 1/(2 sigma^2) as the float vargs.c:62-64 stores */
+    float   t_uthresh, t_ukthresh, t_lthresh;         /* -tu -tuk -tl */
+    float   i_uthresh, i_ukthresh, i_lthresh;         /* -iu -iuk -il */
+    float   t_gain, t_rdnoise, i_gain, i_rdnoise;     /* -tg -tr -ig -ir */
+    float   t_pedestal, i_pedestal;                   /* -tp -ip */
+    float   ker_fit_thresh, scale_fit_thresh, min_frac_good_stamps;  /* -ft -sft -nft */
+    float   stat_sig, ker_sig_reject, ker_frac_mask;  /* -ssig -ks -kfm */
+    float   kf_spread_mask1, kf_spread_mask2;         /* -mins -mous */
+    float   fill_val, fill_val_noise;                 /* -fi -fin */
+    int32_t force_convolve;                           /* -c : 't' | 'i' | 'b' */
+    int32_t phot_normalize;                           /* -n : 't' | 'i' | 'u' */
+    int32_t fig_merit;                                /* -fom : 'v' | 's' | 'h' */
+    int32_t convolve_variance;                        /* -convvar */
+    int32_t rescale_ok;                               /* -okn */
+    int32_t use_full_ss;                              /* (not a flag in 5.1.11; D_USEFULLSS) */
+} zb_params;
+
+/* Sizes derived exactly as hotpants/main.c:382-428 does. */
+typedef struct zb_sizes {
+    int32_t n_comp_ker, n_comp, n_bg_vectors, n_comp_total, mat_size;
+    int32_t fw_kernel, fw_ksstamp, fw_stamp, kc_step;
+    int32_t nstamp_x, nstamp_y, n_stamps;             /* per region (may be lowered, main.c:411-421) */
+    int32_t n_regions, s_border;
+    int32_t max_rpix_x, max_rpix_y;                   /* largest buffered region */
+} zb_sizes;
+
+/* Per-region results = the per-region FITS keywords of hotpants/main.c:1719-1819. */
+typedef struct zb_region_info {
+    int32_t rx_min, rx_max, ry_min, ry_max;           /* good-data bounds, 0-indexed inclusive (REGIONnn is these +1) */
+    int32_t bx_min, bx_max, by_min, by_max;           /* buffered bounds */
+    int32_t conv_template;                            /* CONVOLnn: 1 TEMPLATE, 0 IMAGE */
+    int32_t flags;
+    int32_t n_stamps;                                 /* stamps with >= 1 sub-stamp (compacted, main.c:896-904) */
+    int32_t n_skipped;                                /* NskippedSubstamps of the last check_again */
+    int32_t fit_iters;                                /* build/solve/check passes done */
+    int32_t nx2norm;                                  /* NX2NRMnn */
+    double  ksum;                                     /* KSUMnn */
+    double  sssig, ssscat;                            /* SSSIGnn SSSCATnn */
+    double  fsig, fscat;                              /* FSIGnn FSCATnn */
+    double  x2norm;                                   /* X2NRMnn */
+    double  dmean, dsige, dsig;                       /* DMEANnn DSIGEnn DSIGnn */
+    double  dmeano, dsigeo, dsigo;                    /* DMEANOnn DSIGEOnn DSIGOnn */
+    double  nscalo;                                   /* NSCALOnn (sd/nmean) */
+} zb_region_info;
+
+/* Per-stamp bookkeeping = hotpants/globals.h:1-24 minus the big arrays (what -savexy dumps). */
+typedef struct zb_stamp_info {
+    int32_t x0, y0;                                   /* stamp origin, region coords */
+    int32_t nss, sscnt;                               /* sub-stamps found / index in use (== nss: exhausted) */
+    int32_t xss[ZB_MAX_KSS], yss[ZB_MAX_KSS];         /* sub-stamp centres, region coords */
+    double  mode, fwhm;                               /* sky and sky width from getStampStats3 */
+    double  chi2;                                     /* last figure of merit */
+} zb_stamp_info;
+
+typedef struct zb_ctx zb_ctx;
+
+const char *zb_version(void);
+void  zb_params_default(zb_params *p);
+int   zb_params_check(const zb_params *p, char *msg, int msglen);
+int   zb_sizes_of(const zb_params *p, zb_sizes *s);
+
+int   zb_create(int device, zb_ctx **out);
+void  zb_destroy(zb_ctx *ctx);
+const char *zb_last_error(const zb_ctx *ctx);
+
+/*
+ * One image pair, everything resident on the ctx's device.
+ *   sci, ref            float32 [ny*nx]                      (-inim, -tmplim)
+ *   sci_rms, ref_rms    float32 [ny*nx] or NULL              (-ini, -tni; NULL => gain/rdnoise model, functions.c:1172)
+ *   sci_mask, ref_mask  [ny*nx] of *_dtype or NULL           (-imi, -tmi; >0 means masked, main.c:778-803)
+ *   diff, noise         float32 [ny*nx] outputs              (-outim, -oni)
+ *   out_mask            int32 [ny*nx] output or NULL         (-omi)
+ *   regions             host, [n_regions]                    out
+ *   kernel_sol          host, [n_regions*(n_comp_total+1)] or NULL   (-hki table column per region)
+ *   stamps              host, [n_regions*n_stamps] or NULL
+ *   stream              cudaStream_t (as void*), NULL = ctx's own stream
+ * Returns when the results are complete (host outputs are filled, device outputs
+ * are ordered on `stream`).
+ */
+int zb_subtract(zb_ctx *ctx, const zb_params *p,
+                const float *sci, const float *ref,
+                const float *sci_rms, const float *ref_rms,
+                const void *sci_mask, int sci_mask_dtype,
+                const void *ref_mask, int ref_mask_dtype,
+                float *diff, float *noise, int32_t *out_mask,
+                zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps,
+                void *stream);
+
+/* Same call with HOST pointers for every array: copies in, runs, copies out. */
+int zb_subtract_host(zb_ctx *ctx, const zb_params *p,
+                     const float *sci, const float *ref,
+                     const float *sci_rms, const float *ref_rms,
+                     const void *sci_mask, int sci_mask_dtype,
+                     const void *ref_mask, int ref_mask_dtype,
+                     float *diff, float *noise, int32_t *out_mask,
+                     zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps);
+
+/* Timing/diagnostics of the last zb_subtract on this ctx (ms per stage, CUDA events). */
+#define ZB_NSTAGES 12
+int zb_last_timings(const zb_ctx *ctx, float *ms, int n);
+const char *zb_stage_name(int i);
+/* number of kernel launches issued by this ctx since creation */
+long long zb_launch_count(const zb_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZB200_H */
