@@ -1,0 +1,185 @@
+"""ctypes binding of libzb200.so (include/zb200.h).  There is no CPU fallback: if the CUDA
+library is missing or no GPU is visible, every compute entry point raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import params as P
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libzb200.so")
+ZB_NSTAGES = 12
+MASK_DTYPES = {"uint8": 1, "bool": 1, "int16": 2, "int32": 4}
+
+EXPORTS = ("zb_version", "zb_params_default", "zb_params_check", "zb_sizes_of", "zb_create", "zb_destroy",
+           "zb_last_error", "zb_subtract", "zb_subtract_host", "zb_last_timings", "zb_stage_name", "zb_launch_count")
+
+
+class ZbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("zb200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+_lib = None
+
+
+def load():
+    """Load libzb200.so (built in-tree by build.sh / __graft_entry__.build)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("libzb200.so is not built (run ./build.sh); the subtraction path has no CPU fallback")
+    lib = C.CDLL(LIB_PATH)
+    vp = C.c_void_p
+    lib.zb_version.restype = C.c_char_p
+    lib.zb_params_default.argtypes = [C.POINTER(P.ZbParams)]
+    lib.zb_params_check.argtypes = [C.POINTER(P.ZbParams), C.c_char_p, C.c_int]
+    lib.zb_sizes_of.argtypes = [C.POINTER(P.ZbParams), C.POINTER(P.ZbSizes)]
+    lib.zb_create.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.zb_destroy.argtypes = [vp]
+    lib.zb_last_error.argtypes = [vp]
+    lib.zb_last_error.restype = C.c_char_p
+    sub_args = [vp, C.POINTER(P.ZbParams), vp, vp, vp, vp, vp, C.c_int, vp, C.c_int, vp, vp, vp,
+                C.POINTER(P.ZbRegionInfo), vp, C.POINTER(P.ZbStampInfo)]
+    lib.zb_subtract.argtypes = sub_args + [vp]
+    lib.zb_subtract_host.argtypes = sub_args
+    lib.zb_last_timings.argtypes = [vp, C.POINTER(C.c_float), C.c_int]
+    lib.zb_stage_name.argtypes = [C.c_int]
+    lib.zb_stage_name.restype = C.c_char_p
+    lib.zb_launch_count.argtypes = [vp]
+    lib.zb_launch_count.restype = C.c_longlong
+    _lib = lib
+    return lib
+
+
+def sizes_of(p):
+    s = P.ZbSizes()
+    load().zb_sizes_of(C.byref(p), C.byref(s))
+    return s
+
+
+def check_params(p):
+    buf = C.create_string_buffer(512)
+    rc = load().zb_params_check(C.byref(p), buf, 512)
+    return rc, buf.value.decode()
+
+
+class Result:
+    """Outputs of one subtraction (arrays are torch tensors for device calls, numpy for host calls)."""
+
+
+class Context:
+    """One zb_ctx: owns the device workspace of one GPU; use from one thread at a time."""
+
+    def __init__(self, device=0):
+        self.lib = load()
+        self.h = C.c_void_p()
+        rc = self.lib.zb_create(int(device), C.byref(self.h))
+        if rc != 0:
+            raise ZbError(rc, "zb_create(device=%d) failed: no usable CUDA device" % device)
+        self.device = int(device)
+
+    def close(self):
+        if self.h:
+            self.lib.zb_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _err(self, rc):
+        raise ZbError(rc, (self.lib.zb_last_error(self.h) or b"").decode())
+
+    def timings(self):
+        ms = (C.c_float * ZB_NSTAGES)()
+        self.lib.zb_last_timings(self.h, ms, ZB_NSTAGES)
+        return {self.lib.zb_stage_name(i).decode(): ms[i] for i in range(ZB_NSTAGES) if self.lib.zb_stage_name(i)}
+
+    def launch_count(self):
+        return int(self.lib.zb_launch_count(self.h))
+
+    def _outputs(self, p):
+        sz = sizes_of(p)
+        r = Result()
+        r.sizes = sz
+        r.regions = (P.ZbRegionInfo * sz.n_regions)()
+        r.sol = np.zeros((sz.n_regions, sz.n_comp_total + 1), np.float64)
+        r.stamps = (P.ZbStampInfo * (sz.n_regions * sz.n_stamps))()
+        return r
+
+    def subtract_host(self, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=None, ref_mask=None,
+                      want_mask=True, out=None):
+        """numpy host arrays in, numpy host arrays out (H2D/D2H inside the call)."""
+        ny, nx = sci.shape
+        assert (p.nx, p.ny) == (nx, ny)
+        r = self._outputs(p)
+        if out is None:
+            r.diff = np.empty((ny, nx), np.float32)
+            r.noise = np.empty((ny, nx), np.float32)
+            r.mask = np.empty((ny, nx), np.int32) if want_mask else None
+        else:
+            r.diff, r.noise, r.mask = out
+
+        def ptr(a):
+            return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+        def mk(a):
+            if a is None:
+                return None, 0
+            a = np.ascontiguousarray(a)
+            if a.dtype == np.bool_:
+                a = a.view(np.uint8)
+            return a, MASK_DTYPES[a.dtype.name]
+        f = [None if a is None else np.ascontiguousarray(a, np.float32) for a in (sci, ref, sci_rms, ref_rms)]
+        m1, d1 = mk(sci_mask)
+        m2, d2 = mk(ref_mask)
+        rc = self.lib.zb_subtract_host(self.h, C.byref(p), ptr(f[0]), ptr(f[1]), ptr(f[2]), ptr(f[3]),
+                                       ptr(m1), d1, ptr(m2), d2, ptr(r.diff), ptr(r.noise), ptr(r.mask),
+                                       r.regions, ptr(r.sol), r.stamps)
+        if rc != 0:
+            self._err(rc)
+        return r
+
+    def subtract(self, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=None, ref_mask=None,
+                 want_mask=True, out=None, stream=None):
+        """torch CUDA tensors in/out; only data_ptr() crosses the C ABI."""
+        import torch
+        ny, nx = sci.shape
+        assert (p.nx, p.ny) == (nx, ny)
+        for t in (sci, ref, sci_rms, ref_rms, sci_mask, ref_mask):
+            if t is not None:
+                assert t.is_cuda and t.is_contiguous() and t.device.index == self.device
+        r = self._outputs(p)
+        dev = sci.device
+        if out is None:
+            r.diff = torch.empty((ny, nx), dtype=torch.float32, device=dev)
+            r.noise = torch.empty((ny, nx), dtype=torch.float32, device=dev)
+            r.mask = torch.empty((ny, nx), dtype=torch.int32, device=dev) if want_mask else None
+        else:
+            r.diff, r.noise, r.mask = out
+
+        def ptr(t):
+            return None if t is None else C.c_void_p(t.data_ptr())
+
+        def md(t):
+            if t is None:
+                return 0
+            return MASK_DTYPES[str(t.dtype).replace("torch.", "")]
+        if stream is None:
+            stream = torch.cuda.current_stream(dev)
+        s = C.c_void_p(stream.cuda_stream)
+        rc = self.lib.zb_subtract(self.h, C.byref(p), ptr(sci), ptr(ref), ptr(sci_rms), ptr(ref_rms),
+                                  ptr(sci_mask), md(sci_mask), ptr(ref_mask), md(ref_mask),
+                                  ptr(r.diff), ptr(r.noise), ptr(r.mask), r.regions,
+                                  r.sol.ctypes.data_as(C.c_void_p), r.stamps, s)
+        if rc != 0:
+            self._err(rc)
+        return r

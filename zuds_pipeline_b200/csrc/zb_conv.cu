@@ -1,0 +1,369 @@
+// zb_conv.cu — the output pass: spatially varying convolution fused with background, noise,
+// mask propagation, subtraction, photometric scaling and output masking.
+//
+//   k_make_kernels   alard.c:1346-1385 make_kernel, once per kcStep x kcStep block (alard.c:1272-1280)
+//                    plus the region-centre kernel whose sum is KSUMnn (main.c:1131-1137)
+//   k_convolve       alard.c:1249-1344 spatial_convolve  (image, variance, mask OR, uks/aks test)
+//                    main.c:1126-1128 background, :1145-1163 noise, :1167-1173 unconvolved-side mask,
+//                    :1399-1415 / :1439-1454 subtract + scale, :1584-1605 output masking
+//   k_region_frame   the hwKernel frame spatial_convolve never touches (main.c:1089,1320-1331; alard.c:1264)
+//
+// Bound: the reference semantics (one dense (2hw+1)^2 kernel per block, double accumulation of
+// float x double products) make this pass FP64-pipe bound, not HBM bound: 2*(2hw+1)^2 DFMA per
+// pixel against 29 bytes of traffic.  Layout: a CTA owns NB horizontally adjacent blocks; the
+// image/variance tile (+halo) is converted to double ONCE while it is staged in shared memory,
+// each thread keeps TX adjacent outputs in registers and slides a register window along the
+// kernel row so that one shared-memory load feeds up to TX DFMAs.
+#include "zb_internal.h"
+
+#define TX 7          // outputs per thread (along x)
+#define CH 7          // kernel taps per register-window refill
+
+// ----------------------------------------------------------------------- kernels table
+
+#define MK_NB 16      // convolution blocks per CTA of k_make_kernels
+__global__ void __launch_bounds__(256)
+k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, const double *__restrict__ kvec,
+               double *__restrict__ kern, double *__restrict__ ksum_out, int nbx_max, int nby_max)
+{
+    __shared__ double coef[MK_NB][ZB_MAX_BASIS];
+    const int r = blockIdx.y;
+    const ZbRegion R = D->reg[r];
+    if (R.skip) return;
+    const int hw = D->p.hw_kernel, fw = D->sz.fw_kernel, fw2 = fw * fw, kc = D->sz.kc_step;
+    const int nK = D->sz.n_comp_ker, nc2 = D->sz.n_comp, ko = D->p.ker_order;
+    const int nbx = (R.rpx + kc - 1) / kc, nby = (R.rpy + kc - 1) / kc, nb = nbx * nby;   // ceil(xSize/kcStep)
+    const int per_region = nbx_max * nby_max + 1;
+    const int b0 = blockIdx.x * MK_NB;
+    if (b0 > nb) return;
+    const double *sol = sols + (long long)r * (D->sz.n_comp_total + 1);
+    const int tid = threadIdx.x;
+    // coefficients of every basis at the block centre, terms in the reference order
+    for (int it = tid; it < MK_NB * nK; it += blockDim.x) {
+        int lb = it / nK, i1 = it - lb * nK, b = b0 + lb;
+        if (b > nb) continue;
+        int xi, yi;
+        if (b == nb) { xi = R.rpx / 2; yi = R.rpy / 2; }          // KSUM kernel, main.c:1136
+        else { int j1 = b / nbx, i1b = b - j1 * nbx; xi = i1b * kc + hw + hw; yi = j1 * kc + hw + hw; }
+        double xf = (xi - 0.5 * R.rpx) / (0.5 * R.rpx), yf = (yi - 0.5 * R.rpy) / (0.5 * R.rpy);
+        double c;
+        if (i1 == 0) c = sol[1];
+        else {
+            int k = 2 + (i1 - 1) * nc2;
+            c = 0.0; double ax = 1.0;
+            for (int ix = 0; ix <= ko; ix++) {
+                double ay = 1.0;
+                for (int iy = 0; iy <= ko - ix; iy++) { c = __dadd_rn(c, __dmul_rn(__dmul_rn(sol[k++], ax), ay)); ay = __dmul_rn(ay, yf); }
+                ax = __dmul_rn(ax, xf);
+            }
+        }
+        coef[lb][i1] = c;
+    }
+    __syncthreads();
+    for (int t = tid; t < fw2; t += blockDim.x) {
+        double acc[MK_NB];
+#pragma unroll
+        for (int lb = 0; lb < MK_NB; lb++) acc[lb] = 0.0;
+        for (int n = 0; n < nK; n++) {
+            double kv = kvec[(long long)n * fw2 + t];
+#pragma unroll
+            for (int lb = 0; lb < MK_NB; lb++) acc[lb] = __dadd_rn(acc[lb], __dmul_rn(coef[lb][n], kv));
+        }
+#pragma unroll
+        for (int lb = 0; lb < MK_NB; lb++) {
+            int b = b0 + lb;
+            if (b > nb) continue;
+            double *o = kern + ((long long)r * per_region + b) * 2 * fw2;
+            o[t] = acc[lb];
+            o[fw2 + t] = acc[lb] * acc[lb];
+        }
+    }
+    if (b0 <= nb && nb < b0 + MK_NB) {                             // this CTA made the centre kernel
+        __syncthreads();
+        if (tid == 0) {
+            const double *o = kern + ((long long)r * per_region + nb) * 2 * fw2;
+            double s = 0.0;
+            for (int i = 0; i < fw2; i++) s = __dadd_rn(s, o[i]);
+            ksum_out[r] = s;
+        }
+    }
+}
+
+// --------------------------------------------------------------------------- helpers
+
+struct PixCtx {
+    const float *conv, *other, *conv_rms, *other_rms;
+    const void *cmask_src; int cdt;       // user mask of the convolved image (-tmi for -c t)
+    const void *omask_src; int odt;       // user mask of the other image     (-imi for -c t)
+    float cU, cL, oU, oL;                 // value thresholds: convolved / other image
+    float c_invgain, c_quad, o_invgain, o_quad;
+};
+
+__device__ static inline int value_bits(float v, float fill, float hi, float lo) {
+    int m = 0;
+    m |= (ZB_FLAG_INPUT_ISBAD | ZB_FLAG_BAD_PIXVAL) * (v == fill);
+    m |= (ZB_FLAG_INPUT_ISBAD | ZB_FLAG_SAT_PIXEL) * (v >= hi);
+    m |= (ZB_FLAG_INPUT_ISBAD | ZB_FLAG_LOW_PIXEL) * (v <= lo);
+    return m;
+}
+
+__device__ static inline int user_bits(const void *m, int dt, long long g) {
+    int v = zb_read_mask(m, dt, g);
+    return v | (ZB_FLAG_INPUT_MASK * (v > 0));
+}
+
+__device__ static inline float var_of(const float *rms, const float *img, float invgain, float quad, long long g) {
+    if (rms) { float v = rms[g]; return __fmul_rn(v, v); }
+    double qq = __fmul_rn(quad, quad);
+    return (float)__dadd_rn(__dmul_rn(fabs((double)img[g]), (double)invgain), qq);   // functions.c:1172-1187
+}
+
+__device__ static inline double background_at(const ZbDev *D, const ZbRegion &R, const double *sol, int xi, int yi) {
+    const int ncompBG = (D->sz.n_comp_ker - 1) * D->sz.n_comp + 1, bgo = D->p.bg_order;
+    double xf = (xi - 0.5 * R.rpx) / (0.5 * R.rpx), yf = (yi - 0.5 * R.rpy) / (0.5 * R.rpy);
+    double bg = 0.0, ax = 1.0; int k = 1;
+    for (int i = 0; i <= bgo; i++) {
+        double ay = 1.0;
+        for (int j = 0; j <= bgo - i; j++) { bg = __dadd_rn(bg, __dmul_rn(__dmul_rn(sol[ncompBG + k++], ax), ay)); ay = __dmul_rn(ay, yf); }
+        ax = __dmul_rn(ax, xf);
+    }
+    return bg;
+}
+
+// everything after the convolution sum for one region pixel
+__device__ static inline void finish_pixel(const ZbDev *D, const ZbRegion &R, const PixCtx &P, const double *sol,
+                                           int x, int y, bool interior, float conv_out, float var_out, int mconv,
+                                           double inv1, bool do_scale,
+                                           float *rdiff, float *rnoise, int32_t *omask,
+                                           float *diff, float *noise, int32_t *out_mask)
+{
+    const long long g = (long long)(R.by0 + y) * D->nx + (R.bx0 + x);
+    const long long l = R.off + (long long)y * R.rpx + x;
+    const float fill = D->p.fill_val;
+    const float oth = P.other[g];
+    int m = mconv;
+    int ob = value_bits(oth, fill, P.oU, P.oL);
+    if (ob) m |= ob | ZB_FLAG_OUTPUT_ISBAD;
+    int ub = user_bits(P.omask_src, P.odt, g);
+    m |= ub;
+    if (ub & ZB_FLAG_INPUT_ISBAD) m |= ZB_FLAG_OUTPUT_ISBAD;
+    float nz = __fadd_rn(var_of(P.other_rms, P.other, P.o_invgain, P.o_quad, g), var_out);
+    nz = (float)sqrt((double)nz);
+    float d;
+    if (interior) {
+        float o = (float)__dadd_rn((double)conv_out, background_at(D, R, sol, x, y));
+        d = __fsub_rn(o, oth);
+        if (do_scale) { d = (float)__dmul_rn((double)d, inv1); nz = (float)__dmul_rn((double)nz, inv1); }
+        if (D->conv_template) d = -d;
+    } else {
+        d = fill;                                   // oRData was pre-filled and never written here
+        m |= ZB_FLAG_OUTPUT_ISBAD;                  // main.c:1320-1331
+    }
+    rdiff[l] = d; rnoise[l] = nz; omask[l] = m;
+    if (x >= R.rx0 - R.bx0 && x <= R.own_x1 - R.bx0 && y >= R.ry0 - R.by0 && y <= R.own_y1 - R.by0) {
+        float dd = d, nn = nz;
+        if (interior && D->p.kf_spread_mask2 >= 0 && (m & ZB_FLAG_OUTPUT_ISBAD)) { dd = fill; nn = D->p.fill_val_noise; }
+        diff[g] = dd; noise[g] = nn;
+        if (out_mask) out_mask[g] = m;
+    }
+}
+
+// --------------------------------------------------------------------------- convolution
+
+__global__ void __launch_bounds__(256)
+k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sols, const double *__restrict__ kern,
+           const double *__restrict__ ksums, int nbx_max, int nby_max, int NB, int tpb /*threads per block, padded*/,
+           float *__restrict__ rdiff, float *__restrict__ rnoise, int32_t *__restrict__ omask,
+           float *__restrict__ diff, float *__restrict__ noise, int32_t *__restrict__ out_mask)
+{
+    extern __shared__ __align__(16) unsigned char dyn[];
+    const int r = blockIdx.z;
+    const ZbRegion R = D->reg[r];
+    if (R.skip) return;
+    const int hw = D->p.hw_kernel, fw = D->sz.fw_kernel, fw2 = fw * fw, B = D->sz.kc_step;
+    const int nbx = (R.rpx + B - 1) / B, nby = (R.rpy + B - 1) / B;
+    const int j1 = blockIdx.y, ib0 = blockIdx.x * NB;
+    if (j1 >= nby || ib0 >= nbx) return;
+    const int j0 = j1 * B + hw, i00 = ib0 * B + hw;           // first output pixel of the strip
+    if (j0 >= R.rpy - hw || i00 >= R.rpx - hw) return;
+    const int fwp = ((fw + CH - 1) / CH) * CH;
+    const int tw_need = NB * B + fw - 1 + (fwp - fw) + TX;    // columns a thread may touch
+    int W = tw_need; while ((W & 7) != 1) W++;               // row stride in double2, = 1 mod 8: conflict-free
+    const int TH = B + fw - 1;
+    double2 *tile = (double2 *)dyn;                           // [TH][W]  (image, variance)
+    double2 *Kr = tile + (size_t)TH * W;                      // [NB][fw][fwp] (K, K^2), reversed so loops ascend
+    unsigned char *flag = (unsigned char *)(Kr + (size_t)NB * fw * fwp);   // [TH][W]
+    __shared__ int s_any;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int per_region = nbx_max * nby_max + 1;
+    const float fill = D->p.fill_val;
+    if (tid == 0) s_any = 0;
+    // stage the tile: origin = (i00 - hw, j0 - hw) in region coords
+    int anyf = 0;
+    for (int k = tid; k < TH * W; k += nt) {
+        int ty = k / W, tx = k - ty * W;
+        int x = i00 - hw + tx, y = j0 - hw + ty;
+        double2 v = make_double2(0.0, 0.0); unsigned char f = 0;
+        if (x < R.rpx && y < R.rpy) {
+            long long g = (long long)(R.by0 + y) * D->nx + (R.bx0 + x);
+            float pv = P.conv[g];
+            v.x = (double)pv;
+            v.y = (double)var_of(P.conv_rms, P.conv, P.c_invgain, P.c_quad, g);
+            int cm = user_bits(P.cmask_src, P.cdt, g) | value_bits(pv, fill, P.cU, P.cL);
+            f = (cm ? 1 : 0) | ((cm & ZB_FLAG_INPUT_ISBAD) ? 2 : 0);
+        }
+        tile[k] = v; flag[k] = f; anyf |= f;
+    }
+    for (int k = tid; k < NB * fw * fwp; k += nt) {
+        int lb = k / (fw * fwp), rem = k - lb * fw * fwp, dy = rem / fwp, dx = rem - dy * fwp;
+        double2 kk = make_double2(0.0, 0.0);
+        int b = ib0 + lb;
+        if (dx < fw && b < nbx) {
+            const double *src = kern + ((long long)r * per_region + (long long)j1 * nbx + b) * 2 * fw2;
+            int idx = (fw - 1 - dx) + (fw - 1 - dy) * fw;
+            kk.x = src[idx]; kk.y = src[fw2 + idx];
+        }
+        Kr[k] = kk;
+    }
+    __syncthreads();
+    if (anyf) s_any = 1;
+    __syncthreads();
+    const int any = s_any;
+
+    // thread -> (block in strip, output row, column group); rows fastest
+    const int lb = tid / tpb, lt = tid - lb * tpb;
+    const int ncg = (B + TX - 1) / TX;
+    const int cg = lt / B, row = lt - cg * B;
+    const bool active = (lb < NB) && (cg < ncg) && (ib0 + lb < nbx);
+    if (!active) return;
+    const int c0 = lb * B + cg * TX;                          // first output column within the strip
+    double aq[TX], av[TX];
+#pragma unroll
+    for (int t = 0; t < TX; t++) { aq[t] = 0.0; av[t] = 0.0; }
+    const double2 *Kb = Kr + (size_t)lb * fw * fwp;
+    for (int dy = 0; dy < fw; dy++) {
+        const double2 *trow = tile + (size_t)(row + dy) * W + c0;
+        const double2 *krow = Kb + dy * fwp;
+        for (int ch = 0; ch < fwp; ch += CH) {
+            double2 w[TX + CH - 1];
+#pragma unroll
+            for (int q = 0; q < TX + CH - 1; q++) w[q] = trow[ch + q];
+#pragma unroll
+            for (int dx = 0; dx < CH; dx++) {
+                const double2 kk = krow[ch + dx];
+#pragma unroll
+                for (int t = 0; t < TX; t++) {
+                    aq[t] = fma(w[t + dx].x, kk.x, aq[t]);
+                    av[t] = fma(w[t + dx].y, kk.y, av[t]);
+                }
+            }
+        }
+    }
+    // epilogue
+    const double *sol = sols + (long long)r * (D->sz.n_comp_total + 1);
+    const double ksum = ksums[r], inv1 = 1. / ksum;
+    const bool do_scale = D->conv_template ? (D->p.phot_normalize == 't') : (D->p.phot_normalize == 'i');
+    const int y = j0 + row;
+    if (y >= R.rpy - hw) return;
+#pragma unroll
+    for (int t = 0; t < TX; t++) {
+        const int cb = cg * TX + t;                           // column within the block
+        if (cb >= B) break;
+        const int x = i00 + c0 + t;
+        if (x >= R.rpx - hw) break;
+        // mask of the convolved image at this pixel and under the footprint
+        const int cflag_idx = (row + hw) * W + (c0 + t + hw);
+        int m = 0;
+        if (any) {
+            int mbit = 0;
+            for (int dy = 0; dy < fw; dy++)
+                for (int dx = 0; dx < fw; dx++) mbit |= flag[(row + dy) * W + c0 + t + dx];
+            if (flag[cflag_idx]) {
+                long long g = (long long)(R.by0 + y) * D->nx + (R.bx0 + x);
+                int cm = user_bits(P.cmask_src, P.cdt, g) | value_bits(P.conv[g], fill, P.cU, P.cL);
+                m |= cm;
+                if (cm & ZB_FLAG_INPUT_ISBAD) m |= ZB_FLAG_OUTPUT_ISBAD;
+            }
+            if (mbit) {
+                double aks = 0.0, uks = 0.0;
+                if (mbit & 2) {
+                    for (int dy = 0; dy < fw; dy++)
+                        for (int dx = 0; dx < fw; dx++) {
+                            double ak = fabs(Kb[dy * fwp + dx].x);
+                            aks = __dadd_rn(aks, ak);
+                            if (!(flag[(row + dy) * W + c0 + t + dx] & 2)) uks = __dadd_rn(uks, ak);
+                        }
+                } else { aks = 1.0; uks = 1.0; }               // no bad tap: uks == aks exactly
+                if ((uks / aks) < D->p.ker_frac_mask) m |= (ZB_FLAG_OUTPUT_ISBAD | ZB_FLAG_BAD_CONV);
+                else m |= ZB_FLAG_OK_CONV;
+            }
+        }
+        finish_pixel(D, R, P, sol, x, y, true, (float)aq[t], (float)av[t], m, inv1, do_scale,
+                     rdiff, rnoise, omask, diff, noise, out_mask);
+    }
+}
+
+// The hwKernel frame of every region (not touched by spatial_convolve).
+__global__ void __launch_bounds__(256)
+k_region_frame(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sols,
+               float *__restrict__ rdiff, float *__restrict__ rnoise, int32_t *__restrict__ omask,
+               float *__restrict__ diff, float *__restrict__ noise, int32_t *__restrict__ out_mask)
+{
+    const int r = blockIdx.y;
+    const ZbRegion R = D->reg[r];
+    if (R.skip) return;
+    const int hw = D->p.hw_kernel;
+    const int nrow = 2 * hw * R.rpx, ncol = 2 * hw * (R.rpy - 2 * hw);
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < nrow + ncol; k += gridDim.x * blockDim.x) {
+        int x, y;
+        if (k < nrow) { int q = k / R.rpx; x = k - q * R.rpx; y = q < hw ? q : R.rpy - 2 * hw + q; }
+        else { int kk = k - nrow, q = kk / (2 * hw), c = kk - q * 2 * hw; y = hw + q; x = c < hw ? c : R.rpx - 2 * hw + c; }
+        // vData is calloc'ed: the convolved variance is 0 on the frame (alard.c:1264)
+        finish_pixel(D, R, P, sols + (long long)r * (D->sz.n_comp_total + 1), x, y, false, 0.f, 0.f, 0, 1.0, false,
+                     rdiff, rnoise, omask, diff, noise, out_mask);
+    }
+}
+
+int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
+                       const void *smask, int sdt, const void *tmask, int tdt,
+                       float *diff, float *noise, int32_t *out_mask, cudaStream_t st)
+{
+    const zb_sizes &sz = ctx->sz;
+    const zb_params &p = ctx->p;
+    const ZbDev *H = ctx->h_dev;
+    const int fw = sz.fw_kernel, B = sz.kc_step, nR = sz.n_regions;
+    const int nbx_max = (sz.max_rpix_x + B - 1) / B, nby_max = (sz.max_rpix_y + B - 1) / B;
+    PixCtx P;
+    const bool ct = H->conv_template != 0;
+    P.conv = ct ? ref : sci;            P.other = ct ? sci : ref;
+    P.conv_rms = ct ? ref_rms : sci_rms; P.other_rms = ct ? sci_rms : ref_rms;
+    P.cmask_src = ct ? tmask : smask;   P.cdt = ct ? tdt : sdt;
+    P.omask_src = ct ? smask : tmask;   P.odt = ct ? sdt : tdt;
+    P.cU = ct ? H->tU : H->iU; P.cL = ct ? H->tL : H->iL;
+    P.oU = ct ? H->iU : H->tU; P.oL = ct ? H->iL : H->tL;
+    const float tinv = (float)(1. / p.t_gain), tq = p.t_rdnoise / p.t_gain, iinv = (float)(1. / p.i_gain), iq = p.i_rdnoise / p.i_gain;
+    P.c_invgain = ct ? tinv : iinv; P.c_quad = ct ? tq : iq;
+    P.o_invgain = ct ? iinv : tinv; P.o_quad = ct ? iq : tq;
+
+    dim3 gk((nbx_max * nby_max + 1 + MK_NB - 1) / MK_NB + 1, nR);
+    k_make_kernels<<<gk, 256, 0, st>>>(ctx->d_dev, ctx->d_sol, ctx->d_kvec, ctx->d_kern, ctx->d_kstat, nbx_max, nby_max);
+
+    const int ncg = (B + TX - 1) / TX;
+    int tpb = ((B * ncg + 31) / 32) * 32;
+    int NB = 256 / tpb; if (NB < 1) NB = 1;
+    if (tpb > 256) { snprintf(ctx->err, sizeof ctx->err, "kc_step %d too large for the convolution kernel", B); return ZB_ERR_UNSUPPORTED; }
+    const int fwp = ((fw + CH - 1) / CH) * CH;
+    int W = NB * B + fw - 1 + (fwp - fw) + TX; while ((W & 7) != 1) W++;
+    const int TH = B + fw - 1;
+    size_t smem = (size_t)TH * W * sizeof(double2) + (size_t)NB * fw * fwp * sizeof(double2) + (size_t)TH * W;
+    if (smem > 220 * 1024) { snprintf(ctx->err, sizeof ctx->err, "convolution tile needs %zu bytes of shared memory", smem); return ZB_ERR_UNSUPPORTED; }
+    cudaFuncSetAttribute(k_convolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    dim3 gc((nbx_max + NB - 1) / NB, nby_max, nR);
+    k_convolve<<<gc, NB * tpb, smem, st>>>(ctx->d_dev, P, ctx->d_sol, ctx->d_kern, ctx->d_kstat, nbx_max, nby_max, NB, tpb,
+                                           ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask);
+    k_region_frame<<<dim3(64, nR), 256, 0, st>>>(ctx->d_dev, P, ctx->d_sol, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask);
+    ctx->launches += 3;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "convolution kernels", __FILE__, __LINE__);
+    return ZB_OK;
+}

@@ -1,0 +1,540 @@
+// zb_fit.cu — the least-squares side of the path, batched over all stamps / regions of a pair.
+//
+//   k_fill_conv     alard.c:230-279  xy_conv_stamp   separable basis convolution of a sub-stamp
+//   k_fill_post     alard.c:81-85,273-276 (ren), functions.c:390-443 cutSStamp, alard.c:100-124 bg vectors
+//   k_gram          alard.c:384-434  build_matrix0 (+ the bg dot products of build_matrix :925-953)
+//   k_rhs           alard.c:436-481  build_scprod0 (+ bg right-hand sides of build_scprod :1008-1019)
+//   k_wxy / k_build_matrix   alard.c:843-965 build_matrix, :967-1025 build_scprod
+//   k_lu_solve      alard.c:1465-1552 ludcmp + lubksb
+//   k_stamp_sig     alard.c:1062-1140 getStampSig (+ :1417-1463 make_model, :1387-1415 get_background)
+//   k_clip          alard.c:1143-1247 check_again
+//
+// All of it is FP64 and compiled with -fmad=false.  Every reduction that feeds the solution is
+// evaluated per element in the reference's own term order (one thread owns one output element
+// and walks its terms sequentially; parallelism comes from the thousands of elements), so the
+// fitted kernel coefficients come out bit-identical to the reference, not merely close.
+#include "zb_internal.h"
+
+// ------------------------------------------------------------------ fillStamp
+
+__global__ void __launch_bounds__(256)
+k_fill_conv(const ZbDev *__restrict__ D, const float *__restrict__ img, const ZbStamp *__restrict__ stamps,
+            const int *__restrict__ jobs, const double *__restrict__ fxs, const double *__restrict__ fys,
+            double *__restrict__ vec)
+{
+    extern __shared__ __align__(16) unsigned char dyn[];
+    const int slot = jobs[blockIdx.x], n = blockIdx.y;
+    const ZbStamp &S = stamps[slot];
+    if (S.sscnt >= S.nss) return;
+    const ZbRegion R = D->reg[S.region];
+    const int hw = D->p.hw_kernel, hwss = D->p.hw_ksstamp, fw = D->sz.fw_kernel, fwss = D->sz.fw_ksstamp;
+    const int sw = fwss + fw - 1;                     // sub_width
+    const int xi = S.xss[S.sscnt], yi = S.yss[S.sscnt];
+    double *fx = (double *)dyn, *fy = fx + fw;
+    float *patch = (float *)(fy + fw);                // [sw][sw]
+    float *temp = patch + sw * sw;                    // [fwss][sw]
+    const int tid = threadIdx.x, nt = blockDim.x;
+    for (int k = tid; k < fw; k += nt) { fx[k] = fxs[k + n * fw]; fy[k] = fys[k + n * fw]; }
+    const int px0 = xi - hwss - hw, py0 = yi - hwss - hw;
+    for (int k = tid; k < sw * sw; k += nt) {
+        int py = k / sw, px = k - py * sw;
+        patch[k] = img[(long long)(R.by0 + py0 + py) * D->nx + (R.bx0 + px0 + px)];
+    }
+    __syncthreads();
+    // y pass: float accumulator, rounded after every tap (the reference's scratch is float)
+    for (int k = tid; k < sw * fwss; k += nt) {
+        int r = k / sw, c = k - r * sw;               // r: row of the sub-stamp, c: column incl. halo
+        float t = 0.0f;
+        for (int yc = -hw; yc <= hw; yc++)
+            t = (float)((double)t + (double)patch[c + sw * (r + hw + yc)] * fy[hw - yc]);
+        temp[k] = t;
+    }
+    __syncthreads();
+    const int npix = fwss * fwss;
+    double *out = vec + (long long)slot * (D->sz.n_comp_ker + D->sz.n_bg_vectors) * npix + (long long)n * npix;
+    for (int k = tid; k < npix; k += nt) {
+        int r = k / fwss, c = k - r * fwss;
+        double acc = 0.0;
+        for (int xc = -hw; xc <= hw; xc++)
+            acc += (double)temp[(c + xc + hw) + sw * r] * fx[hw - xc];
+        out[k] = acc;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_fill_post(const ZbDev *__restrict__ D, const float *__restrict__ refimg, const ZbStamp *__restrict__ stamps,
+            const int *__restrict__ jobs, const int *__restrict__ ren, double *__restrict__ vec, double *__restrict__ kref)
+{
+    const int slot = jobs[blockIdx.x];
+    const ZbStamp &S = stamps[slot];
+    if (S.sscnt >= S.nss) return;
+    const ZbRegion R = D->reg[S.region];
+    const int hwss = D->p.hw_ksstamp, fwss = D->sz.fw_ksstamp, npix = fwss * fwss;
+    const int nK = D->sz.n_comp_ker, nvec = nK + D->sz.n_bg_vectors, bgo = D->p.bg_order;
+    const int xi = S.xss[S.sscnt], yi = S.yss[S.sscnt];
+    double *v = vec + (long long)slot * nvec * npix;
+    double *kr = kref + (long long)slot * npix;
+    const float rPixX2 = 0.5f * R.rpx, rPixY2 = 0.5f * R.rpy;
+    for (int k = threadIdx.x; k < npix; k += blockDim.x) {
+        int r = k / fwss, c = k - r * fwss;
+        int i = xi - hwss + c, j = yi - hwss + r;
+        double v0 = v[k];
+        for (int n = 1; n < nK; n++)
+            if (ren[n]) v[(long long)n * npix + k] -= v0;
+        kr[k] = (double)refimg[(long long)(R.by0 + j) * D->nx + (R.bx0 + i)];
+        // background monomials; the normalised coordinate is formed in FLOAT (alard.c:60-63,105,109)
+        double xf = (double)(((float)i - rPixX2) / rPixX2);
+        double yf = (double)(((float)j - rPixY2) / rPixY2);
+        double ax = 1.0; int nv = nK;
+        for (int a = 0; a <= bgo; a++) {
+            double ay = 1.0;
+            for (int b = 0; b <= bgo - a; b++) { v[(long long)nv * npix + k] = ax * ay; ay *= yf; ++nv; }
+            ax *= xf;
+        }
+    }
+}
+
+// Gram matrix of the stamp's vectors, lower triangle: G[i(i+1)/2+j] = sum_k v_i[k] v_j[k], k ascending.
+#define GRAM_KC 32
+#define GRAM_ITEMS 6
+__global__ void __launch_bounds__(256)
+k_gram(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const int *__restrict__ jobs,
+       const double *__restrict__ vec, double *__restrict__ gram)
+{
+    extern __shared__ __align__(16) unsigned char dyn[];
+    const int slot = jobs[blockIdx.x];
+    const ZbStamp &S = stamps[slot];
+    if (S.sscnt >= S.nss) return;
+    const int fwss = D->sz.fw_ksstamp, npix = fwss * fwss;
+    const int nvec = D->sz.n_comp_ker + D->sz.n_bg_vectors, npair = nvec * (nvec + 1) / 2;
+    const double *v = vec + (long long)slot * nvec * npix;
+    double *g = gram + (long long)slot * npair;
+    double *s = (double *)dyn;                         // [GRAM_KC][nvec]
+    const int tid = threadIdx.x, nt = blockDim.x;
+    for (int base = 0; base < npair; base += nt * GRAM_ITEMS) {
+        int ii[GRAM_ITEMS], jj[GRAM_ITEMS]; double acc[GRAM_ITEMS];
+#pragma unroll
+        for (int q = 0; q < GRAM_ITEMS; q++) {
+            int e = base + q * nt + tid;
+            acc[q] = 0.0; ii[q] = -1; jj[q] = 0;
+            if (e < npair) {
+                int i = (int)((sqrt(8.0 * e + 1.0) - 1.0) * 0.5);
+                while (i * (i + 1) / 2 > e) i--;
+                while ((i + 1) * (i + 2) / 2 <= e) i++;
+                ii[q] = i; jj[q] = e - i * (i + 1) / 2;
+            }
+        }
+        for (int k0 = 0; k0 < npix; k0 += GRAM_KC) {
+            int kc = min(GRAM_KC, npix - k0);
+            __syncthreads();
+            for (int idx = tid; idx < nvec * GRAM_KC; idx += nt) {
+                int n = idx / GRAM_KC, kk = idx - n * GRAM_KC;
+                s[kk * nvec + n] = (kk < kc) ? v[(long long)n * npix + k0 + kk] : 0.0;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int q = 0; q < GRAM_ITEMS; q++) {
+                if (ii[q] < 0) continue;
+                double a = acc[q];
+                for (int kk = 0; kk < kc; kk++) a += s[kk * nvec + ii[q]] * s[kk * nvec + jj[q]];
+                acc[q] = a;
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < GRAM_ITEMS; q++) {
+            int e = base + q * nt + tid;
+            if (e < npair) g[e] = acc[q];
+        }
+    }
+}
+
+// rhs[i] = sum over the sub-stamp of v_i * imRef, x outer / y inner (alard.c:459-466)
+__global__ void __launch_bounds__(128)
+k_rhs(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const int *__restrict__ jobs,
+      const double *__restrict__ vec, const double *__restrict__ kref, double *__restrict__ rhs)
+{
+    extern __shared__ __align__(16) unsigned char dyn[];
+    const int slot = jobs[blockIdx.x];
+    const ZbStamp &S = stamps[slot];
+    if (S.sscnt >= S.nss) return;
+    const int fwss = D->sz.fw_ksstamp, npix = fwss * fwss;
+    const int nvec = D->sz.n_comp_ker + D->sz.n_bg_vectors;
+    double *kr = (double *)dyn;
+    const double *krg = kref + (long long)slot * npix;
+    for (int k = threadIdx.x; k < npix; k += blockDim.x) kr[k] = krg[k];
+    __syncthreads();
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+        const double *v = vec + ((long long)slot * nvec + i) * npix;
+        double p0 = 0.0;
+        for (int xc = 0; xc < fwss; xc++)
+            for (int yc = 0; yc < fwss; yc++)
+                p0 += v[xc + fwss * yc] * kr[xc + fwss * yc];   // kref holds the float pixel exactly
+        rhs[(long long)slot * nvec + i] = p0;
+    }
+}
+
+int zb_launch_fill(zb_ctx *ctx, const float *conv_img, const float *ref_img, const int *d_jobs, int n_jobs, cudaStream_t st)
+{
+    if (n_jobs <= 0) return ZB_OK;
+    const zb_sizes &sz = ctx->sz;
+    const int fw = sz.fw_kernel, fwss = sz.fw_ksstamp, sw = fwss + fw - 1, npix = fwss * fwss;
+    const int nvec = sz.n_comp_ker + sz.n_bg_vectors;
+    size_t sm1 = 2 * fw * sizeof(double) + ((size_t)sw * sw + (size_t)sw * fwss) * sizeof(float);
+    size_t sm3 = (size_t)GRAM_KC * nvec * sizeof(double);
+    size_t sm4 = (size_t)npix * sizeof(double);
+    if (sm1 > 200 * 1024 || sm3 > 200 * 1024 || sm4 > 200 * 1024) {
+        snprintf(ctx->err, sizeof ctx->err, "sub-stamp of %d pixels too large for shared memory", fwss);
+        return ZB_ERR_UNSUPPORTED;
+    }
+    cudaFuncSetAttribute(k_fill_conv, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
+    cudaFuncSetAttribute(k_gram, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm3);
+    cudaFuncSetAttribute(k_rhs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm4);
+    k_fill_conv<<<dim3(n_jobs, sz.n_comp_ker), 256, sm1, st>>>(ctx->d_dev, conv_img, ctx->d_stamps, d_jobs, ctx->d_fx, ctx->d_fy, ctx->d_vec);
+    k_fill_post<<<n_jobs, 256, 0, st>>>(ctx->d_dev, ref_img, ctx->d_stamps, d_jobs, ctx->d_ren, ctx->d_vec, ctx->d_kref);
+    k_gram<<<n_jobs, 256, sm3, st>>>(ctx->d_dev, ctx->d_stamps, d_jobs, ctx->d_vec, ctx->d_gram);
+    k_rhs<<<n_jobs, 128, sm4, st>>>(ctx->d_dev, ctx->d_stamps, d_jobs, ctx->d_vec, ctx->d_kref, ctx->d_rhs);
+    ctx->launches += 4;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "fill kernels", __FILE__, __LINE__);
+    return ZB_OK;
+}
+
+// --------------------------------------------------------------- global system
+
+// spatial weights of each stamp at its current sub-stamp centre (alard.c:886-903)
+__global__ void k_wxy(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, int n_slots, double *__restrict__ wxy)
+{
+    int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n_slots) return;
+    const ZbStamp &S = stamps[slot];
+    if (S.nss <= 0 || S.sscnt >= S.nss) return;
+    const ZbRegion R = D->reg[S.region];
+    const float rPixX2 = 0.5f * R.rpx, rPixY2 = 0.5f * R.rpy;
+    double fx = (double)(((float)S.xss[S.sscnt] - rPixX2) / rPixX2);
+    double fy = (double)(((float)S.yss[S.sscnt] - rPixY2) / rPixY2);
+    double *w = wxy + (long long)slot * D->sz.n_comp;
+    int k = 0; double a1 = 1.0;
+    for (int a = 0; a <= D->p.ker_order; a++) {
+        double a2 = 1.0;
+        for (int b = 0; b <= D->p.ker_order - a; b++) { w[k++] = a1 * a2; a2 *= fy; }
+        a1 *= fx;
+    }
+}
+
+__device__ static inline double gram_at(const double *g, int u, int v) {   // u >= v
+    return g[u * (u + 1) / 2 + v];
+}
+
+// One thread per matrix element (I >= J) or right-hand-side element; stamps summed in ascending order.
+__global__ void __launch_bounds__(256)
+k_build_matrix(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
+               const double *__restrict__ gram, const double *__restrict__ rhs, const double *__restrict__ wxy,
+               double *__restrict__ mat, double *__restrict__ sol)
+{
+    const int r = blockIdx.z;
+    if (!fit[r].active) return;
+    const int n = D->sz.mat_size, nK = D->sz.n_comp_ker, nc2 = D->sz.n_comp, ncomp = (nK - 1) * nc2;
+    const int nvec = nK + D->sz.n_bg_vectors, npair = nvec * (nvec + 1) / 2;
+    const int I = blockIdx.y * 16 + threadIdx.y, J = blockIdx.x * 16 + threadIdx.x;
+    if (I >= n || J > n || (J < n && J > I)) return;
+    const int base = D->reg[r].stamp_base, nS = fit[r].n_stamps;
+    // classify the element once
+    int kind, u = 0, v = 0, wi = -1, wj = -1;
+    if (J == n) {                                     // right-hand side
+        if (I == 0) { kind = 10; u = 0; }
+        else if (I <= ncomp) { kind = 11; u = (I - 1) / nc2 + 1; wi = (I - 1) % nc2; }
+        else { kind = 10; u = nK + (I - ncomp - 1); }
+    } else if (I == 0) { kind = 0; u = 0; v = 0; }
+    else if (I <= ncomp) {
+        int i = I - 1, i1 = i / nc2; wi = i - i1 * nc2;
+        if (J == 0) { kind = 1; u = i1 + 1; v = 0; }
+        else { int j = J - 1, j1 = j / nc2; wj = j - j1 * nc2; kind = 2; u = i1 + 1; v = j1 + 1; }
+    } else {
+        int ibg = I - ncomp - 1; u = nK + ibg;
+        if (J == 0) { kind = 0; v = 0; }
+        else if (J <= ncomp) { int j = J - 1, j1 = j / nc2; wi = j - j1 * nc2; kind = 1; v = j1 + 1; }
+        else { kind = 0; v = nK + (J - ncomp - 1); }
+    }
+    double acc = 0.0;
+    for (int k = 0; k < nS; k++) {
+        const int slot = base + k;
+        const ZbStamp &S = stamps[slot];
+        if (S.sscnt >= S.nss) continue;
+        const double *g = gram + (long long)slot * npair;
+        const double *w = wxy + (long long)slot * nc2;
+        switch (kind) {
+        case 0:  acc += gram_at(g, u, v); break;
+        case 1:  acc += w[wi] * gram_at(g, u, v); break;
+        case 2:  acc += w[wi] * w[wj] * gram_at(g, u, v); break;
+        case 10: acc += rhs[(long long)slot * nvec + u]; break;
+        default: acc += rhs[(long long)slot * nvec + u] * w[wi]; break;
+        }
+    }
+    if (J == n) sol[(long long)r * (D->sz.n_comp_total + 1) + I + 1] = acc;     // 1-indexed like kernelSol
+    else {
+        double *M = mat + (long long)r * n * n;
+        M[(long long)I * n + J] = acc;
+        M[(long long)J * n + I] = acc;
+    }
+}
+
+// Right-looking LU with the reference's pivot rule (implicit scaling, ties: last row wins) and
+// substitution, one CTA per region.  For every element the subtractions a_ij -= l_ik*u_kj happen
+// for k ascending, unfused, exactly as in the Crout loops of alard.c:1495-1509.
+#define LU_NT 1024
+__global__ void __launch_bounds__(LU_NT)
+k_lu_solve(const ZbDev *__restrict__ D, ZbFit *__restrict__ fit, double *__restrict__ mat, double *__restrict__ sol,
+           double *__restrict__ vvs, int *__restrict__ indxs)
+{
+    const int r = blockIdx.x;
+    if (!fit[r].active) return;
+    const int n = D->sz.mat_size, tid = threadIdx.x;
+    double *a = mat + (long long)r * n * n;
+    double *b = sol + (long long)r * (D->sz.n_comp_total + 1) + 1;
+    double *vv = vvs + (long long)r * n;
+    int *indx = indxs + (long long)r * n;
+    __shared__ int s_imax, s_sing;
+    if (tid == 0) s_sing = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += LU_NT) {
+        double big = 0.0;
+        for (int j = 0; j < n; j++) { double t = fabs(a[(long long)i * n + j]); if (t > big) big = t; }
+        if (big == 0.) s_sing = 1; else vv[i] = 1.0 / big;
+    }
+    __syncthreads();
+    if (s_sing) { if (tid == 0) fit[r].singular = 1; return; }   // ludcmp returns 1, solution is meaningless
+    for (int k = 0; k < n; k++) {
+        // pivot: max of vv[i]*|a[i][k]| over i >= k, last index on ties.  The products are >= 0,
+        // so their IEEE bit patterns order like the values.
+        double bestv = -1.0; int besti = -1;
+        for (int i = k + tid; i < n; i += LU_NT) {
+            double dum = vv[i] * fabs(a[(long long)i * n + k]);
+            if (dum >= bestv) { bestv = dum; besti = i; }
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            double ov = __shfl_xor_sync(0xffffffffu, bestv, o);
+            int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+            if (ov > bestv || (ov == bestv && oi > besti)) { bestv = ov; besti = oi; }
+        }
+        __shared__ double s_v[LU_NT / 32]; __shared__ int s_i[LU_NT / 32];
+        if ((tid & 31) == 0) { s_v[tid >> 5] = bestv; s_i[tid >> 5] = besti; }
+        __syncthreads();
+        if (tid == 0) {
+            double bv = -1.0; int bi = -1;
+            for (int w = 0; w < LU_NT / 32; w++)
+                if (s_v[w] > bv || (s_v[w] == bv && s_i[w] > bi)) { bv = s_v[w]; bi = s_i[w]; }
+            s_imax = bi;
+        }
+        __syncthreads();
+        const int imax = s_imax;
+        if (imax != k) {
+            for (int c = tid; c < n; c += LU_NT) {
+                double t = a[(long long)imax * n + c];
+                a[(long long)imax * n + c] = a[(long long)k * n + c];
+                a[(long long)k * n + c] = t;
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            if (imax != k) vv[imax] = vv[k];
+            indx[k] = imax;
+            if (a[(long long)k * n + k] == 0.0) a[(long long)k * n + k] = 1.0e-20;
+        }
+        __syncthreads();
+        if (k != n - 1) {
+            const double dum = 1.0 / a[(long long)k * n + k];
+            for (int i = k + 1 + tid; i < n; i += LU_NT) a[(long long)i * n + k] *= dum;
+            __syncthreads();
+            const int m = n - k - 1;
+            for (int e = tid; e < m * m; e += LU_NT) {
+                int i = k + 1 + e / m, j = k + 1 + e % m;
+                a[(long long)i * n + j] -= a[(long long)i * n + k] * a[(long long)k * n + j];
+            }
+            __syncthreads();
+        }
+    }
+    // lubksb: permutation, forward substitution (column sweep keeps j ascending per row), back substitution
+    if (tid == 0)
+        for (int i = 0; i < n; i++) { int ip = indx[i]; double t = b[ip]; b[ip] = b[i]; b[i] = t; }
+    __syncthreads();
+    for (int j = 0; j < n - 1; j++) {
+        const double bj = b[j];
+        for (int i = j + 1 + tid; i < n; i += LU_NT) b[i] -= a[(long long)i * n + j] * bj;
+        __syncthreads();
+    }
+    if (tid == 0)
+        for (int i = n - 1; i >= 0; i--) {
+            double sum = b[i];
+            const double *row = a + (long long)i * n;
+            for (int j = i + 1; j < n; j++) sum -= row[j] * b[j];
+            b[i] = sum / row[i];
+        }
+}
+
+// ------------------------------------------------------------ model and clipping
+
+// noise^2 used as the fit's figure-of-merit weight (hotpants/main.c:739-770): float arithmetic
+__device__ static inline float approx_var(const ZbDev *D, const float *sci, const float *ref,
+                                          const float *sci_rms, const float *ref_rms, long long g)
+{
+    float o, e;
+    if (sci_rms) { float v = sci_rms[g]; o = v * v; }
+    else { float inv = (float)(1. / D->p.i_gain), quad = D->p.i_rdnoise / D->p.i_gain; double qq = quad * quad; o = (float)(fabs(sci[g]) * inv + qq); }
+    if (ref_rms) { float v = ref_rms[g]; e = v * v; }
+    else { float inv = (float)(1. / D->p.t_gain), quad = D->p.t_rdnoise / D->p.t_gain; double qq = quad * quad; e = (float)(fabs(ref[g]) * inv + qq); }
+    return o + e;
+}
+
+__global__ void __launch_bounds__(256)
+k_stamp_sig(const ZbDev *__restrict__ D, ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
+            const double *__restrict__ vec, const double *__restrict__ kref, const double *__restrict__ sols,
+            const float *__restrict__ sci, const float *__restrict__ ref,
+            const float *__restrict__ sci_rms, const float *__restrict__ ref_rms, int32_t *__restrict__ m_in)
+{
+    extern __shared__ __align__(16) unsigned char dyn[];
+    const int slot = blockIdx.x;
+    ZbStamp &S = stamps[slot];
+    if (S.nss <= 0 || S.sscnt >= S.nss) return;
+    if (!fit[S.region].active) return;
+    const ZbRegion R = D->reg[S.region];
+    const int hwss = D->p.hw_ksstamp, fwss = D->sz.fw_ksstamp, npix = fwss * fwss;
+    const int nK = D->sz.n_comp_ker, nvec = nK + D->sz.n_bg_vectors, ko = D->p.ker_order, bgo = D->p.bg_order;
+    const double *sol = sols + (long long)S.region * (D->sz.n_comp_total + 1);
+    double *term = (double *)dyn;                     // [npix]
+    double *coef = term + npix;                       // [nK]
+    signed char *ok = (signed char *)(coef + nK);     // [npix]
+    __shared__ double s_bg;
+    const int xR = S.xss[S.sscnt], yR = S.yss[S.sscnt];
+    const double xf = (xR - 0.5 * R.rpx) / (0.5 * R.rpx), yf = (yR - 0.5 * R.rpy) / (0.5 * R.rpy);
+    const int nc2 = D->sz.n_comp;
+    for (int i1 = threadIdx.x; i1 < nK; i1 += blockDim.x) {
+        if (i1 == 0) { coef[0] = sol[1]; continue; }
+        int k = 2 + (i1 - 1) * nc2;
+        double c = 0.0, ax = 1.0;
+        for (int ix = 0; ix <= ko; ix++) {
+            double ay = 1.0;
+            for (int iy = 0; iy <= ko - ix; iy++) { c += sol[k++] * ax * ay; ay *= yf; }
+            ax *= xf;
+        }
+        coef[i1] = c;
+    }
+    if (threadIdx.x == 0) {
+        int ncompBG = (nK - 1) * nc2 + 1, k = 1;
+        double bg = 0.0, ax = 1.0;
+        for (int i = 0; i <= bgo; i++) {
+            double ay = 1.0;
+            for (int j = 0; j <= bgo - i; j++) { bg += sol[ncompBG + k++] * ax * ay; ay *= yf; }
+            ax *= xf;
+        }
+        s_bg = bg;
+    }
+    __syncthreads();
+    const double bg = s_bg;
+    const double *v = vec + (long long)slot * nvec * npix;
+    const double *kr = kref + (long long)slot * npix;
+    int32_t *gm = m_in + R.off;
+    for (int k = threadIdx.x; k < npix; k += blockDim.x) {
+        float m = 0.0f;
+        for (int n = 0; n < nK; n++) m = (float)((double)m + coef[n] * v[(long long)n * npix + k]);   // model kept in float
+        int j = k / fwss, i = k - j * fwss;
+        int x2 = xR - hwss + i, y2 = yR - hwss + j;
+        double tdat = m, idat = kr[k];
+        double ndat = approx_var(D, sci, ref, sci_rms, ref_rms, (long long)(R.by0 + y2) * D->nx + (R.bx0 + x2));
+        double diff = tdat - idat + bg;
+        signed char f = 0;
+        if (!((gm[(long long)y2 * R.rpx + x2] & ZB_FLAG_INPUT_ISBAD) || (fabs(idat) <= ZB_ZEROVAL))) {
+            if ((tdat * 0.0 != 0.0) || (idat * 0.0 != 0.0))
+                atomicOr(&gm[(long long)y2 * R.rpx + x2], ZB_FLAG_INPUT_ISBAD | ZB_FLAG_ISNAN);
+            else { f = 1; term[k] = diff * diff / ndat; }
+        }
+        ok[k] = f;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double sig1 = 0; int nsig = 0;
+        for (int k = 0; k < npix; k++) if (ok[k]) { nsig++; sig1 += term[k]; }
+        if (nsig > 0) { sig1 /= nsig; if (sig1 >= ZB_MAXVAL) sig1 = -1; }
+        else sig1 = -1;
+        S.sig1 = sig1;
+    }
+}
+
+// functions.c:1037-1107 sigma_clip, single thread, on a small float array
+__device__ static void sigma_clip_seq(const float *data, char *rej, int count, double *mean, double *stdev, int maxiter, float statSig)
+{
+    if (count == 0) { *mean = 0; *stdev = ZB_MAXVAL; return; }
+    for (int i = 0; i < count; i++) rej[i] = 0;
+    int cnt = 0, ncnt = count, iter = 0;
+    while (ncnt != cnt && iter < maxiter) {
+        cnt = ncnt;
+        *mean = 0; *stdev = 0;
+        for (int i = 0; i < count; i++) if (!rej[i]) { float d = data[i]; *mean += d; *stdev += (double)(d * d); }
+        if (ncnt > 0) *mean /= ncnt; else { *mean = 0; *stdev = ZB_MAXVAL; return; }
+        if (ncnt > 1) { *stdev = *stdev - ncnt * (*mean) * (*mean); *stdev = sqrt(*stdev / (double)(ncnt - 1)); }
+        else { *stdev = ZB_MAXVAL; return; }
+        ncnt = 0;
+        double istd = 1. / (*stdev);
+        for (int i = 0; i < count; i++)
+            if (!rej[i]) { if ((fabs(data[i] - (*mean)) * istd) > statSig) rej[i] = 1; else ncnt++; }
+        iter++;
+    }
+}
+
+// check_again: one thread per region walks its stamps in order (the decisions are sequential and tiny).
+__global__ void k_clip(const ZbDev *__restrict__ D, ZbStamp *__restrict__ stamps, ZbFit *__restrict__ fit,
+                       float *__restrict__ ss_scratch, char *__restrict__ rej_scratch, int *__restrict__ jobs, int *__restrict__ njobs)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= D->n_regions) return;
+    ZbFit &F = fit[r];
+    if (!F.active) return;
+    const int base = D->reg[r].stamp_base, nS = F.n_stamps, cap = D->sz.n_stamps;
+    float *ss = ss_scratch + (long long)r * cap;
+    char *rej = rej_scratch + (long long)r * cap;
+    int nss = 0, check = 0, nskip = 0;
+    for (int k = 0; k < nS; k++) {
+        ZbStamp &S = stamps[base + k];
+        S.refill = 0;
+        if (S.sscnt < S.nss) {
+            if (S.sig1 == -1) { S.sscnt++; S.refill = 1; check = 1; }
+            else { S.chi2 = S.sig1; ss[nss++] = (float)S.sig1; }
+        } else nskip++;
+    }
+    double mean = 0, stdev = 0;
+    sigma_clip_seq(ss, rej, nss, &mean, &stdev, 10, D->p.stat_sig);
+    for (int k = 0; k < nS; k++) {
+        ZbStamp &S = stamps[base + k];
+        if (S.sscnt < S.nss) {
+            if ((S.chi2 - mean) > D->p.ker_sig_reject * stdev) { S.sscnt++; S.refill = 1; check = 1; }
+        }
+    }
+    for (int k = 0; k < nS; k++) {
+        ZbStamp &S = stamps[base + k];
+        if (S.refill && S.sscnt < S.nss) { int q = atomicAdd(njobs, 1); jobs[q] = base + k; }
+    }
+    F.meansig = mean; F.scatter = stdev; F.n_skipped = nskip; F.iters++;
+    F.active = check;
+}
+
+int zb_launch_fit_iteration(zb_ctx *ctx, const float *conv_img, const float *ref_img,
+                            const float *sci, const float *ref, const float *sci_rms, const float *ref_rms, cudaStream_t st)
+{
+    const zb_sizes &sz = ctx->sz;
+    const int n = sz.mat_size, nR = sz.n_regions, npix = sz.fw_ksstamp * sz.fw_ksstamp;
+    (void)conv_img; (void)ref_img;
+    k_wxy<<<(ctx->n_slots + 127) / 128, 128, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->n_slots, ctx->d_wxy);
+    dim3 gb((n + 1 + 15) / 16, (n + 15) / 16, nR);
+    k_build_matrix<<<gb, dim3(16, 16), 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_rhs, ctx->d_wxy, ctx->d_mat, ctx->d_sol);
+    k_lu_solve<<<nR, LU_NT, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_sol, ctx->d_vv, ctx->d_indx);
+    size_t sm = (size_t)npix * (sizeof(double) + 1) + (size_t)sz.n_comp_ker * sizeof(double) + 16;
+    cudaFuncSetAttribute(k_stamp_sig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    k_stamp_sig<<<ctx->n_slots, 256, sm, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_vec, ctx->d_kref, ctx->d_sol,
+                                                sci, ref, sci_rms, ref_rms, ctx->d_min);
+    cudaMemsetAsync(ctx->d_njobs, 0, sizeof(int), st);
+    k_clip<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, (float *)ctx->d_stats, (char *)(ctx->d_stats) + (size_t)nR * sz.n_stamps * sizeof(float),
+                                          ctx->d_jobs, ctx->d_njobs);
+    ctx->launches += 5;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "fit iteration", __FILE__, __LINE__);
+    return ZB_OK;
+}

@@ -1,0 +1,136 @@
+// zb_internal.h — shared host/device definitions of the B200 subtraction path.
+// Everything here is private to libzb200.so; the public surface is include/zb200.h.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include "../../include/zb200.h"
+
+#define ZB_MAXVAL  1e10      // hotpants/defaults.h:24
+#define ZB_ZEROVAL 1e-10     // hotpants/defaults.h:25
+#define ZB_MAX_REGIONS 64
+#define ZB_MAX_BASIS   160   // nCompKer + nBGVectors upper bound handled by the fit kernels
+#define ZB_MAX_COMP    32    // (ko+1)(ko+2)/2 upper bound (ko <= 6)
+
+// One buffered region (hotpants/main.c:606-658).  All coordinates are image pixels.
+struct ZbRegion {
+    int rx0, rx1, ry0, ry1;      // good-data bounds, inclusive
+    int bx0, bx1, by0, by1;      // buffered bounds, inclusive
+    int rpx, rpy;                // buffered size
+    int own_x1, own_y1;          // last column/row this region is the LAST writer of (main.c:548-551)
+    long long off;               // element offset of this region in the per-region scratch arrays
+    int stamp_base;              // first stamp slot of this region
+    int skip;                    // 1: no usable stamps, region left untouched (main.c:1002-1009)
+};
+
+// Device-resident constants of one call.
+struct ZbDev {
+    zb_params p;
+    zb_sizes  sz;
+    int nx, ny;
+    int n_regions;
+    int conv_template;           // 1: convolve template (ref), 0: convolve image (sci)
+    float tU, tUK, tL, iU, iUK, iL;   // thresholds after pedestal removal (main.c:212-217)
+    ZbRegion reg[ZB_MAX_REGIONS];
+};
+
+// One grid cell of the stamp search (hotpants/main.c:837-906) and its outcome.
+struct ZbCell {
+    int region, gk, gl;
+    int sx0, sy0, spx, spy;      // stamp origin (region coords) and size
+    float kft;                   // kerFitThresh in force (may be halved on retry)
+    int  stat_status;            // getStampStats3 return code
+    int  nss;
+    int  xss[ZB_MAX_KSS], yss[ZB_MAX_KSS];    // region coords
+    double in_mode, in_fwhm;     // slot contents before this cell ran (stale-slot quirk)
+    double sum, mean, median, mode, sd, fwhm, lfwhm;
+};
+
+// A stamp that survived the search: a slot with big per-stamp arrays.
+struct ZbStamp {
+    int region;
+    int x0, y0;
+    int nss, sscnt;
+    int xss[ZB_MAX_KSS], yss[ZB_MAX_KSS];
+    int refill;                  // set by the clip kernel when (sscnt) changed and the slot must be refilled
+    double mode, fwhm, chi2, sum;
+    double sig1;                 // last getStampSig value
+    int sig_flag;
+    int pad;
+};
+
+// Per-region state of the fit loop.
+struct ZbFit {
+    int n_stamps;                // kept stamps
+    int active;                  // 1 while check_again keeps asking for another pass
+    int iters, singular, n_skipped, pad;
+    double meansig, scatter;
+};
+
+#define ZB_CUDA_OK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return zb_cuda_fail(ctx, e_, #call, __FILE__, __LINE__); } while (0)
+
+struct zb_ctx {
+    int device;
+    cudaStream_t stream;
+    char err[512];
+    long long launches;
+    // cached configuration
+    zb_params p; zb_sizes sz; int configured;
+    ZbDev *h_dev; ZbDev *d_dev;
+    // device workspace
+    int32_t *d_min;              // input-stage mask per region   [sum rpx*rpy]
+    int32_t *d_cmask;            // mask of the convolved image   [sum rpx*rpy]
+    int32_t *d_omask;            // output-stage mask per region  [sum rpx*rpy]
+    float   *d_rdiff, *d_rnoise; // per-region diff / noise before output masking
+    long long region_elems;
+    double  *d_ran;  int n_ran;  // ran1 stream, seed -666 (functions.c:811)
+    double  *d_fx, *d_fy, *d_kvec; int *d_ren;   // basis (alard.c:134-197)
+    ZbCell  *d_cells, *h_cells; int n_cells;
+    ZbStamp *d_stamps, *h_stamps; int n_slots;
+    double  *d_vec;              // [slot][nvec][npix]
+    double  *d_kref;             // [slot][npix]
+    double  *d_gram;             // [slot][nvec*(nvec+1)/2]
+    double  *d_rhs;              // [slot][nvec]
+    double  *d_wxy;              // [slot][n_comp]
+    double  *d_mat;              // [region][n*n]
+    double  *d_sol;              // [region][n_comp_total+1]
+    double  *d_vv; int *d_indx;  // LU scratch
+    ZbFit   *d_fit, *h_fit;
+    int     *d_jobs, *d_njobs, *h_njobs;
+    double  *d_kern;             // [region][blocks][2*fw*fw]  (K, K^2) per convolution block
+    double  *d_kstat;            // per-region: ksum, aks
+    double  *d_stats;  double *h_stats;   // region QA scratch
+    // staging for zb_subtract_host
+    void *d_stage[9]; size_t stage_bytes[9];
+    // timings
+    cudaEvent_t ev[ZB_NSTAGES + 1];
+    float ms[ZB_NSTAGES];
+};
+
+int zb_cuda_fail(zb_ctx *ctx, cudaError_t e, const char *what, const char *file, int line);
+
+// kernel launchers (each returns a zb_status)
+int zb_launch_input_mask(zb_ctx *ctx, const float *sci, const float *ref, const void *smask, int sdt,
+                         const void *tmask, int tdt, cudaStream_t st);
+int zb_launch_stamp_search(zb_ctx *ctx, const float *conv_img, int first_cell, int n_cells, cudaStream_t st);
+int zb_launch_fill(zb_ctx *ctx, const float *conv_img, const float *ref_img, const int *d_jobs, int n_jobs, cudaStream_t st);
+int zb_launch_fit_iteration(zb_ctx *ctx, const float *conv_img, const float *ref_img,
+                            const float *sci, const float *ref, const float *sci_rms, const float *ref_rms, cudaStream_t st);
+int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
+                       const void *smask, int sdt, const void *tmask, int tdt,
+                       float *diff, float *noise, int32_t *out_mask, cudaStream_t st);
+int zb_launch_region_stats(zb_ctx *ctx, cudaStream_t st);
+int zb_launch_final_sig(zb_ctx *ctx, cudaStream_t st);
+
+// host helpers
+void zb_host_ran1_stream(double *out, int n);
+void zb_host_basis(const zb_params *p, double *kvec, double *fx, double *fy, int *ren);
+
+__host__ __device__ static inline int zb_read_mask(const void *m, int dt, long long idx) {
+    if (!m) return 0;
+    if (dt == ZB_MASK_U8)  return (int)((const uint8_t *)m)[idx];
+    if (dt == ZB_MASK_I16) return (int)((const int16_t *)m)[idx];
+    return ((const int32_t *)m)[idx];
+}
