@@ -182,6 +182,9 @@ int zb_last_timings(const zb_ctx *ctx, float *ms, int n);
 const char *zb_stage_name(int i);
 /* number of kernel launches issued by this ctx since creation */
 long long zb_launch_count(const zb_ctx *ctx);
+/* sizeof() of the public structs as built (0 zb_params, 1 zb_sizes, 2 zb_region_info, 3 zb_stamp_info):
+   lets a binding verify its own struct mirror before the first call */
+int zb_abi_sizeof(int which);
 
 #ifdef __cplusplus
 }

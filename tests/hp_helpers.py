@@ -110,13 +110,20 @@ def zuds_command(pair, d, nreg_side=3, hotpants_kws=None, exe="hotpants", extra=
 _BOX = re.compile(r"image;box\(\s*(-?\d+),\s*(-?\d+),")
 
 
-def run_reference(pair, nreg_side=3, hotpants_kws=None, workdir=None, raw_cmd=None):
+def run_reference(pair, nreg_side=3, hotpants_kws=None, workdir=None, case=None):
     """Run oracle/_ref/hotpants (the unmodified reference) on ``pair`` through FITS files.
-    Adds -omi (internal int mask) and -savexy (stamp centres) to the zuds command."""
+    Adds -omi (internal int mask) and -savexy (stamp centres) to the zuds command.
+    With ``case`` (tests/cases.py) the command comes from cases.command()."""
     assert os.path.exists(REF_BIN), "build it with: make -C oracle ref"
     tmp = workdir or tempfile.mkdtemp(prefix="hpref_")
     extra = " -omi %s -savexy %s" % (os.path.join(tmp, "sub.mask.fits"), os.path.join(tmp, "xy"))
-    cmd = raw_cmd(tmp) if raw_cmd else zuds_command(pair, tmp, nreg_side, hotpants_kws, exe=REF_BIN, extra=extra)
+    if case is not None:
+        import cases as CS
+        names = write_pair(pair, tmp)
+        names["out"] = os.path.join(tmp, "sub.fits")
+        cmd = CS.command(case, pair, names, exe=REF_BIN) + extra
+    else:
+        cmd = zuds_command(pair, tmp, nreg_side, hotpants_kws, exe=REF_BIN, extra=extra)
     pr = subprocess.run(cmd.split(), capture_output=True, text=True)
     if pr.returncode != 0:
         raise RuntimeError("reference hotpants failed: %s" % pr.stderr[-2000:])
@@ -126,10 +133,17 @@ def run_reference(pair, nreg_side=3, hotpants_kws=None, workdir=None, raw_cmd=No
     hdus = fitsio.read_hdus(os.path.join(tmp, "sub.fits"))
     r.diff, r.header = hdus[0][1], hdus[0][0]
     r.sol = hdus[1][1].T.copy() if len(hdus) > 1 else None          # [region][nCompTotal+1]
-    r.noise = fitsio.read_image(os.path.join(tmp, "sub.rms.fits"))[0]
+    r.table_header = hdus[1][0] if len(hdus) > 1 else None
+    rms = os.path.join(tmp, "sub.rms.fits")
+    r.noise, r.noise_header = (fitsio.read_image(rms)[0], fitsio.read_image(rms)[1]) if os.path.exists(rms) else (None, None)
     r.mask = fitsio.read_image(os.path.join(tmp, "sub.mask.fits"))[0].astype(np.int32)
-    r.xy_used = [tuple(map(int, m.groups())) for m in _BOX.finditer(open(os.path.join(tmp, "xy")).read())]
-    r.xy_all = [tuple(map(int, m.groups())) for m in _BOX.finditer(open(os.path.join(tmp, "xy.all")).read())]
+
+    def boxes(path):
+        if not os.path.exists(path):
+            return []
+        return [tuple(map(int, m.groups())) for m in _BOX.finditer(open(path).read())]
+    r.xy_used = boxes(os.path.join(tmp, "xy"))
+    r.xy_all = boxes(os.path.join(tmp, "xy.all"))
     r.workdir = tmp
     return r
 

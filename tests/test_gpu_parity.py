@@ -1,0 +1,158 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle and the reference's golden
+vectors.  The bars (BASELINE.json north_star): masks and selected stamps bit-exact; difference and
+noise within 1e-4 x local sigma; kernel coefficients within 1e-5 relative; sentinel pixels exact."""
+import numpy as np
+import pytest
+
+import cases as CS
+import hp_helpers as H
+from test_oracle_golden import check_against_golden, input_hash, load_golden, region_keywords
+
+pytestmark = pytest.mark.gpu
+
+TOL_SIGMA = 1e-4      # |delta diff|, |delta noise| <= TOL_SIGMA * noise_ref
+TOL_COEF = 1e-5       # |delta coef| <= TOL_COEF * max|coef| of the region
+
+
+def compare(o, g):
+    """o: oracle Result, g: CUDA Result (numpy arrays)."""
+    assert H.stamp_table(o) == H.stamp_table(g), "selected stamps / sscnt differ"
+    for r in range(o.sizes.n_regions):
+        ro, rg = o.regions[r], g.regions[r]
+        assert (ro.flags, ro.n_stamps, ro.fit_iters, ro.n_skipped) == (rg.flags, rg.n_stamps, rg.fit_iters, rg.n_skipped)
+    assert np.array_equal(o.mask, g.mask), "hotpants int mask differs in %d pixels" % int((o.mask != g.mask).sum())
+    scale = np.abs(o.sol).max(axis=1, keepdims=True) + 1e-300
+    assert (np.abs(o.sol - g.sol) / scale).max() <= TOL_COEF
+    sent = o.diff == np.float32(1e-30)
+    assert np.array_equal(sent, g.diff == np.float32(1e-30)), "1e-30 sentinel pixels differ"
+    sig = np.maximum(o.noise.astype(np.float64), 1e-3)
+    dd = np.abs(o.diff.astype(np.float64) - g.diff.astype(np.float64)) / sig
+    dn = np.abs(o.noise.astype(np.float64) - g.noise.astype(np.float64)) / sig
+    assert dd.max() <= TOL_SIGMA, "diff off by %.3g sigma" % dd.max()
+    assert dn.max() <= TOL_SIGMA, "noise off by %.3g sigma" % dn.max()
+    assert np.array_equal(o.noise[sent], g.noise[sent])
+    assert region_keywords(o) == region_keywords(g)
+    for r in range(o.sizes.n_regions):
+        a, b = o.regions[r].nscalo, g.regions[r].nscalo
+        assert ("%.4f" % a) == ("%.4f" % b)
+
+
+@pytest.mark.parametrize("case", CS.SMALL + [CS.TINY_FULL], ids=lambda c: c.name)
+def test_small_cases_host_call(case, oracle, gpu_ctx):
+    pair = CS.make_pair(case)
+    p = CS.params_of(case, pair)
+    ins = CS.inputs_of(case, pair)
+    o = H.run_oracle(oracle, p, *ins)
+    g = gpu_ctx.subtract_host(p, *ins)
+    assert gpu_ctx.launch_count() > 0
+    compare(o, g)
+    gold = load_golden(case.name)
+    if input_hash(case, pair) == gold["input_sha256"]:
+        check_against_golden(case, g, gold, exact=False)
+
+
+@pytest.mark.parametrize("case", CS.SMALL[:3], ids=lambda c: c.name)
+def test_small_cases_device_call(case, oracle, gpu_ctx):
+    """torch CUDA tensors in and out: only data_ptr() crosses the C ABI."""
+    import torch
+    pair = CS.make_pair(case)
+    p = CS.params_of(case, pair)
+    ins = CS.inputs_of(case, pair)
+    o = H.run_oracle(oracle, p, *ins)
+    dev = [None if a is None else torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in ins]
+    g = gpu_ctx.subtract(p, *dev)
+    torch.cuda.synchronize()
+    g.diff, g.noise, g.mask = g.diff.cpu().numpy(), g.noise.cpu().numpy(), g.mask.cpu().numpy()
+    compare(o, g)
+
+
+def test_mask_dtypes_agree(gpu_ctx):
+    case = CS.SMALL[0]
+    pair = CS.make_pair(case)
+    p = CS.params_of(case, pair)
+    ins = list(CS.inputs_of(case, pair))
+    base = gpu_ctx.subtract_host(p, *ins)
+    for dt in (np.int16, np.int32, np.bool_):
+        ins[4] = pair.bpm.astype(dt)
+        g = gpu_ctx.subtract_host(p, *ins)
+        assert np.array_equal(g.mask, base.mask) and np.array_equal(g.diff, base.diff)
+
+
+def test_repeatable_and_context_reuse(gpu_ctx):
+    """Same ctx, alternating configurations: the workspace is rebuilt and results are bit-identical."""
+    a, b = CS.SMALL[0], CS.SMALL[1]
+    pa, pb = CS.make_pair(a), CS.make_pair(b)
+    r1 = gpu_ctx.subtract_host(CS.params_of(a, pa), *CS.inputs_of(a, pa))
+    gpu_ctx.subtract_host(CS.params_of(b, pb), *CS.inputs_of(b, pb))
+    r2 = gpu_ctx.subtract_host(CS.params_of(a, pa), *CS.inputs_of(a, pa))
+    assert np.array_equal(r1.diff, r2.diff) and np.array_equal(r1.noise, r2.noise) and np.array_equal(r1.mask, r2.mask)
+    assert np.array_equal(r1.sol, r2.sol)
+
+
+def test_bad_params_are_refused(gpu_ctx):
+    from zuds_pipeline_b200 import _lib
+    case = CS.SMALL[0]
+    pair = CS.make_pair(case)
+    p = CS.params_of(case, pair)
+    p.hw_ksstamp = 3                      # rss < r : vargs.c FATAL ERROR
+    with pytest.raises(_lib.ZbError) as e:
+        gpu_ctx.subtract_host(p, *CS.inputs_of(case, pair))
+    assert e.value.code == -1
+
+
+def test_nan_and_constant_inputs(oracle, gpu_ctx):
+    """Edge inputs the reference tolerates: NaN pixels, fill-value pixels, a dead (constant) quadrant."""
+    case = CS.SMALL[0]
+    pair = CS.make_pair(case)
+    pair.sci[100:104, 200:203] = np.nan
+    pair.ref[300, 310] = np.inf
+    pair.sci[50, 60] = np.float32(1e-30)
+    pair.ref[400:, 400:] = 150.0
+    p = CS.params_of(case, pair)
+    ins = CS.inputs_of(case, pair)
+    o = H.run_oracle(oracle, p, *ins)
+    g = gpu_ctx.subtract_host(p, *ins)
+    assert H.stamp_table(o) == H.stamp_table(g)
+    assert np.array_equal(o.mask, g.mask)
+    fin = np.isfinite(o.diff) & np.isfinite(o.noise)
+    assert np.array_equal(fin, np.isfinite(g.diff) & np.isfinite(g.noise))
+    sig = np.maximum(o.noise.astype(np.float64), 1e-3)
+    assert (np.abs(o.diff.astype(np.float64) - g.diff)[fin] / sig[fin]).max() <= TOL_SIGMA
+
+
+@pytest.mark.parametrize("name", ["c1", "c1b"])
+def test_full_size_quadrant(name, oracle, gpu_ctx):
+    """BASELINE.json configs[0]/[1] (and the zuds-actual variant) at 3080x3072 against the oracle."""
+    case = CS.FULL[name]
+    pair = CS.make_pair(case)
+    p = CS.params_of(case, pair)
+    ins = CS.inputs_of(case, pair)
+    o = H.run_oracle(oracle, p, *ins)
+    g = gpu_ctx.subtract_host(p, *ins)
+    compare(o, g)
+    # zuds-level product: bit 17 where the difference carries the sentinel (zuds/subtraction.py:167-174)
+    zo = (pair.sci_mask.astype(np.int64) | pair.ref_mask) | ((o.diff == np.float32(1e-30)) * 2 ** 17)
+    zg = (pair.sci_mask.astype(np.int64) | pair.ref_mask) | ((g.diff == np.float32(1e-30)) * 2 ** 17)
+    assert np.array_equal(zo, zg)
+
+
+def test_full_size_properties(gpu_ctx):
+    """Size-independent properties at full size: idempotent re-run, the photometric scaling only
+    rescales (-n t vs -n i), and swapping the mask dtype changes nothing."""
+    case = CS.FULL["c1"]
+    pair = CS.make_pair(case)
+    p = CS.params_of(case, pair)
+    ins = CS.inputs_of(case, pair)
+    a = gpu_ctx.subtract_host(p, *ins)
+    b = gpu_ctx.subtract_host(p, *ins)
+    assert np.array_equal(a.diff, b.diff) and np.array_equal(a.mask, b.mask) and np.array_equal(a.noise, b.noise)
+    p2 = CS.params_of(case, pair)
+    p2.phot_normalize = ord("t")
+    c = gpu_ctx.subtract_host(p2, *ins)
+    assert np.array_equal(a.mask, c.mask) and np.array_equal(a.sol, c.sol)
+    good = (a.mask & 0x8000) == 0
+    # every pixel scaled by 1/ksum of ITS region; check on the first region's interior
+    r = a.regions[0]
+    sl = (slice(r.ry_min + 30, r.ry_max - 30), slice(r.rx_min + 30, r.rx_max - 30))
+    ratio = c.diff[sl][good[sl]].astype(np.float64) * r.ksum
+    assert np.allclose(ratio, a.diff[sl][good[sl]], rtol=2e-6, atol=1e-5)

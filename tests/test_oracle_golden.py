@@ -1,0 +1,156 @@
+"""Pins the CPU oracle (oracle/hp_oracle.c) against golden vectors produced by the UNMODIFIED
+reference hotpants (tests/golden/make_golden.py).  CPU only."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import cases as CS
+import hp_helpers as H
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def load_golden(name):
+    with open(os.path.join(GOLD, "golden_%s.json" % name)) as f:
+        return json.load(f)
+
+
+def input_hash(case, pair):
+    h = hashlib.sha256()
+    for a in CS.inputs_of(case, pair):
+        if a is not None:
+            h.update(np.ascontiguousarray(a).tobytes())
+    return h.hexdigest()
+
+
+def region_keywords(res):
+    """Per-region header keywords as hotpants/main.c:1719-1819 formats them (all strings)."""
+    out = {}
+    for i in range(res.sizes.n_regions):
+        r = res.regions[i]
+        out["REGION%02d" % i] = "[%d:%d,%d:%d]" % (r.rx_min + 1, r.rx_max + 1, r.ry_min + 1, r.ry_max + 1)
+        if r.flags & 0x1:          # region skipped: nothing else is written (main.c:1002-1009 'continue')
+            del out["REGION%02d" % i]
+            continue
+        out["CONVOL%02d" % i] = "TEMPLATE" if r.conv_template else "IMAGE"
+        for key, v in (("KSUM", r.ksum), ("SSSIG", r.sssig), ("SSSCAT", r.ssscat), ("FSIG", r.fsig), ("FSCAT", r.fscat),
+                       ("X2NRM", r.x2norm), ("DMEAN", r.dmean), ("DSIGE", r.dsige), ("DSIG", r.dsig),
+                       ("DMEANO", r.dmeano), ("DSIGEO", r.dsigeo), ("DSIGO", r.dsigo)):
+            out["%s%02d" % (key, i)] = "%.4f" % v
+        out["NX2NRM%02d" % i] = "%d" % r.nx2norm
+    return out
+
+
+def check_against_golden(case, res, gold, exact=True, pair=None):
+    """Compare a Result (oracle or GPU) with the reference's golden record."""
+    assert gold["xy_all"] == [list(c) for c in H.oracle_xy(res)[0]]
+    assert gold["xy_used"] == [list(c) for c in H.oracle_xy(res)[1]]
+    m = (res.mask & 0xffff).astype(np.int32)
+    for i in range(res.sizes.n_regions):
+        r = res.regions[i]
+        if r.flags & 0x1:
+            # a skipped region is never written to the -omi file, whose BZERO=32768 16-bit pixels then
+            # read back as 32768 (hotpants/main.c:362-373,1002-1009): a file-format artefact of the reference
+            m[r.ry_min:r.ry_max + 1, r.rx_min:r.rx_max + 1] = 0x8000
+    assert sha(m) == gold["mask_sha256"]
+    assert int((res.diff == np.float32(1e-30)).sum()) == gold["n_masked_1e30"]
+    if gold["sol"] is not None:
+        gsol = np.array([[float(v) for v in row] for row in gold["sol"]])
+        if exact:
+            assert np.array_equal(gsol, res.sol)
+        else:
+            scale = np.abs(gsol).max(axis=1, keepdims=True) + 1e-300
+            assert (np.abs(gsol - res.sol) / scale).max() <= 1e-5
+    ny, nx = res.diff.shape
+    cy, cx = ny // 2, nx // 2
+    gd = np.array([[float(v) for v in row] for row in gold["diff_patch"]], np.float32)
+    gn = np.array([[float(v) for v in row] for row in gold["noise_patch"]], np.float32)
+    if exact:
+        assert sha(res.diff) == gold["diff_sha256"]
+        assert sha(res.noise) == gold["noise_sha256"]
+        assert np.array_equal(res.diff[cy - 4:cy + 4, cx - 4:cx + 4], gd)
+        assert np.array_equal(res.noise[cy - 4:cy + 4, cx - 4:cx + 4], gn)
+    else:
+        # tolerance of the north star: |delta| <= 1e-4 x local sigma
+        assert (np.abs(res.diff[cy - 4:cy + 4, cx - 4:cx + 4] - gd) <= 1e-4 * np.maximum(gn, 1e-3)).all()
+        assert (np.abs(res.noise[cy - 4:cy + 4, cx - 4:cx + 4] - gn) <= 1e-4 * np.maximum(gn, 1e-3)).all()
+    mine = region_keywords(res)
+    assert mine == gold["region_keys"], {k: (mine.get(k), gold["region_keys"].get(k))
+                                         for k in set(mine) | set(gold["region_keys"])
+                                         if mine.get(k) != gold["region_keys"].get(k)}
+
+
+@pytest.mark.parametrize("case", CS.SMALL + [CS.TINY_FULL], ids=lambda c: c.name)
+def test_oracle_matches_reference_golden(case, oracle):
+    pair = CS.make_pair(case)
+    gold = load_golden(case.name)
+    if input_hash(case, pair) != gold["input_sha256"]:
+        pytest.skip("synthetic generator is not bit-reproducible on this host; see test_tiny_full_fixture")
+    p = CS.params_of(case, pair)
+    res = H.run_oracle(oracle, p, *CS.inputs_of(case, pair))
+    assert res.rc == 0
+    check_against_golden(case, res, gold, exact=True)
+
+
+def test_tiny_full_fixture(oracle):
+    """Inputs AND outputs come from the committed fixture: independent of the synthetic generator."""
+    z = np.load(os.path.join(GOLD, "tiny_full.npz"))
+    case = CS.TINY_FULL
+    gold = load_golden(case.name)
+
+    class _P:
+        pass
+    pair = _P()
+    pair.sci, pair.ref, pair.sci_rms, pair.ref_rms, pair.bpm = z["sci"], z["ref"], z["sci_rms"], z["ref_rms"], z["bpm"]
+    ny, nx = pair.sci.shape
+    from zuds_pipeline_b200 import params as P
+    a = P.parse_hotpants_args(gold["command"].split()[1:])
+    a.params.nx, a.params.ny = nx, ny
+    res = H.run_oracle(oracle, a.params, pair.sci, pair.ref, pair.sci_rms, pair.ref_rms, pair.bpm, None)
+    assert res.rc == 0
+    assert np.array_equal(res.diff, z["diff"])
+    assert np.array_equal(res.noise, z["noise"])
+    assert np.array_equal((res.mask & 0xffff).astype(np.uint16), z["mask"])
+    assert np.array_equal(res.sol, z["sol"])
+    assert [list(c) for c in H.oracle_xy(res)[1]] == z["xy_used"].tolist()
+
+
+def test_retry_case_really_retries(oracle):
+    case = [c for c in CS.SMALL if c.name == "retry"][0]
+    pair = CS.make_pair(case)
+    res = H.run_oracle(oracle, CS.params_of(case, pair), *CS.inputs_of(case, pair))
+    assert res.regions[0].flags & 0x4
+
+
+def test_no_stamps_region_is_skipped(oracle):
+    case = [c for c in CS.SMALL if c.name == "no_stamps"][0]
+    pair = CS.make_pair(case)
+    res = H.run_oracle(oracle, CS.params_of(case, pair), *CS.inputs_of(case, pair))
+    assert res.regions[0].flags & 0x1
+    assert not res.diff.any() and not res.noise.any()
+
+
+def test_sigma_clip_known_answer(oracle):
+    import ctypes as C
+    d = np.array([1, 2, 3, 4, 5, 100], np.float32)
+    m, s = C.c_double(), C.c_double()
+    oracle.hp_oracle_sigma_clip.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int, C.c_float]
+    oracle.hp_oracle_sigma_clip(d.ctypes.data_as(C.c_void_p), 6, C.byref(m), C.byref(s), 10, 2.0)
+    assert m.value == 3.0 and abs(s.value - np.std([1, 2, 3, 4, 5], ddof=1)) < 1e-12
+
+
+def test_ran1_first_values(oracle):
+    """Numerical Recipes ran1 seeded with -666 (hotpants/functions.c:1632-1662)."""
+    import ctypes as C
+    idum = C.c_int(-666)
+    v = [oracle.hp_oracle_ran1(C.byref(idum)) for _ in range(4)]
+    assert all(0.0 <= x < 1.0 for x in v) and len(set(v)) == 4
+    idum = C.c_int(-666)
+    assert [oracle.hp_oracle_ran1(C.byref(idum)) for _ in range(4)] == v

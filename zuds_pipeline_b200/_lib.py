@@ -15,7 +15,7 @@ ZB_NSTAGES = 12
 MASK_DTYPES = {"uint8": 1, "bool": 1, "int16": 2, "int32": 4}
 
 EXPORTS = ("zb_version", "zb_params_default", "zb_params_check", "zb_sizes_of", "zb_create", "zb_destroy",
-           "zb_last_error", "zb_subtract", "zb_subtract_host", "zb_last_timings", "zb_stage_name", "zb_launch_count")
+           "zb_last_error", "zb_subtract", "zb_subtract_host", "zb_last_timings", "zb_stage_name", "zb_launch_count", "zb_abi_sizeof")
 
 
 class ZbError(RuntimeError):

@@ -200,7 +200,7 @@ static void free_workspace(zb_ctx *ctx) {
                       (void **)&ctx->d_cells, (void **)&ctx->d_stamps, (void **)&ctx->d_vec, (void **)&ctx->d_kref, (void **)&ctx->d_gram,
                       (void **)&ctx->d_rhs, (void **)&ctx->d_wxy, (void **)&ctx->d_mat, (void **)&ctx->d_sol, (void **)&ctx->d_vv,
                       (void **)&ctx->d_indx, (void **)&ctx->d_fit, (void **)&ctx->d_jobs, (void **)&ctx->d_njobs, (void **)&ctx->d_kern,
-                      (void **)&ctx->d_kstat, (void **)&ctx->d_stats};
+                      (void **)&ctx->d_kstat, (void **)&ctx->d_stats, (void **)&ctx->d_qa, (void **)&ctx->d_qpart};
     for (size_t i = 0; i < sizeof dptrs / sizeof dptrs[0]; i++) { if (*dptrs[i]) cudaFree(*dptrs[i]); *dptrs[i] = NULL; }
     void **hptrs[] = {(void **)&ctx->h_dev, (void **)&ctx->h_cells, (void **)&ctx->h_stamps, (void **)&ctx->h_fit, (void **)&ctx->h_njobs, (void **)&ctx->h_stats};
     for (size_t i = 0; i < sizeof hptrs / sizeof hptrs[0]; i++) { if (*hptrs[i]) cudaFreeHost(*hptrs[i]); *hptrs[i] = NULL; }
@@ -222,7 +222,7 @@ extern "C" const char *zb_last_error(const zb_ctx *ctx) { return ctx ? ctx->err 
 extern "C" long long zb_launch_count(const zb_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
 static const char *k_stage_names[ZB_NSTAGES] = {"input_mask", "stamp_search", "stamp_resolve", "fill_stamps", "fit_loop",
-                                                "make_kernels+convolve", "final_sig", "region_stats", "readback", "", "", ""};
+                                                "make_kernels+convolve", "final_sig", "region_stats", "readback", "k_convolve", "", ""};
 extern "C" const char *zb_stage_name(int i) { return (i >= 0 && i < ZB_NSTAGES) ? k_stage_names[i] : ""; }
 extern "C" int zb_last_timings(const zb_ctx *ctx, float *ms, int n) {
     if (!ctx || !ms) return ZB_ERR_PARAM;
@@ -316,6 +316,8 @@ static int configure(zb_ctx *ctx, const zb_params *p) {
     const size_t stat_bytes = (size_t)sz.n_regions * ((size_t)sz.n_comp_total + 512) * sizeof(double) + ns * 8;
     DMALLOC(ctx->d_stats, stat_bytes);   HMALLOC(ctx->h_stats, stat_bytes);
     cudaMemset(ctx->d_stats, 0, stat_bytes);
+    DMALLOC(ctx->d_qa, (size_t)sz.n_regions * 4 * sizeof(ZbQaStat));
+    DMALLOC(ctx->d_qpart, (size_t)sz.n_regions * 5 * ZB_QA_NBLK * sizeof(ZbQaPart));
     cudaMemcpy(ctx->d_dev, H, sizeof(ZbDev), cudaMemcpyHostToDevice);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { free_workspace(ctx); return zb_cuda_fail(ctx, e, "configure", __FILE__, __LINE__); }
@@ -503,7 +505,7 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
     STAGE(6);
     CHECK_RC(zb_launch_final_sig(ctx, st));
     STAGE(7);
-    CHECK_RC(zb_launch_region_stats(ctx, st));
+    CHECK_RC(zb_launch_region_stats(ctx, noise, out_mask, st));
 
     // ---- stage 8: small read-backs
     STAGE(8);
@@ -516,6 +518,7 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
     STAGE(9);
     SYNC("final read-back");
     for (int i = 0; i < 9; i++) cudaEventElapsedTime(&ctx->ms[i], ctx->ev[i], ctx->ev[i + 1]);
+    if (njobs > 0) cudaEventElapsedTime(&ctx->ms[9], ctx->ev[10], ctx->ev[11]);
     for (int r = 0; r < nR; r++) {
         zb_region_info *ri = &regions[r];
         const ZbFit &F = ctx->h_fit[r];
@@ -593,4 +596,15 @@ extern "C" int zb_subtract_host(zb_ctx *ctx, const zb_params *p,
     cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "zb_subtract_host copies", __FILE__, __LINE__);
     return ZB_OK;
+}
+
+// ABI self-check used by the loader tests: sizeof of the public structs as this library was built.
+extern "C" int zb_abi_sizeof(int which) {
+    switch (which) {
+    case 0: return (int)sizeof(zb_params);
+    case 1: return (int)sizeof(zb_sizes);
+    case 2: return (int)sizeof(zb_region_info);
+    case 3: return (int)sizeof(zb_stamp_info);
+    default: return -1;
+    }
 }

@@ -69,6 +69,21 @@ struct ZbFit {
     double meansig, scatter;
 };
 
+// Region QA statistics (main.c:1479-1554): four getStampStats3 runs per region, advanced in lock
+// step by whole-grid passes over the region (zb_stats.cu).
+#define ZB_QA_NBLK 64
+struct ZbQaStat {
+    int phase;                   // 0 sigma-clip passes, 1 histogram passes, 2 done
+    int status;                  // getStampStats3 return code
+    int maxiter, umask, smask, use_noise;
+    int ncrit, cnt_prev, tries, imax, npts_s, pad;
+    double crit_mean[8], crit_istd[8];
+    double mean, sd, bin1, binsize, samp_med;
+    double sum, median, mode, fwhm, lfwhm;
+    int bins[256];
+};
+struct ZbQaPart { double s1, s2; int n, pad; };
+
 #define ZB_CUDA_OK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return zb_cuda_fail(ctx, e_, #call, __FILE__, __LINE__); } while (0)
 
 struct zb_ctx {
@@ -102,6 +117,8 @@ struct zb_ctx {
     double  *d_kern;             // [region][blocks][2*fw*fw]  (K, K^2) per convolution block
     double  *d_kstat;            // per-region: ksum, aks
     double  *d_stats;  double *h_stats;   // region QA scratch
+    ZbQaStat *d_qa;              // [region][4]
+    ZbQaPart *d_qpart;           // [region][5][ZB_QA_NBLK]  (4 stats + getNoiseStats3)
     // staging for zb_subtract_host
     void *d_stage[9]; size_t stage_bytes[9];
     // timings
@@ -121,7 +138,7 @@ int zb_launch_fit_iteration(zb_ctx *ctx, const float *conv_img, const float *ref
 int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
                        const void *smask, int sdt, const void *tmask, int tdt,
                        float *diff, float *noise, int32_t *out_mask, cudaStream_t st);
-int zb_launch_region_stats(zb_ctx *ctx, cudaStream_t st);
+int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStream_t st);
 int zb_launch_final_sig(zb_ctx *ctx, cudaStream_t st);
 
 // host helpers

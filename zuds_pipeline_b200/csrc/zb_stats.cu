@@ -1,12 +1,387 @@
 // zb_stats.cu — per-region QA numbers that hotpants writes as FITS keywords.
-//   k_final_sig     alard.c:1027-1060 getFinalStampSig + main.c:1417-1435 (FSIGnn / FSCATnn)
-//   region stats    main.c:1479-1554: getStampStats3 on diff and noise for GOOD and OK pixels
-//                   (functions.c:763-1035) and getNoiseStats3 (functions.c:719-761)
+//   k_final_sig / k_final_clip   alard.c:1027-1060 getFinalStampSig + main.c:1417-1435 (FSIGnn / FSCATnn)
+//   k_qa_sample / k_qa_pass / k_qa_decide
+//                                main.c:1479-1554: getStampStats3 (functions.c:763-1035) on the difference
+//                                and noise images for GOOD and OK pixels, getNoiseStats3 (functions.c:719-761)
+//   k_rescale_ok                 main.c:1557-1579 (-okn)
+//
+// The four getStampStats3 runs of a region read the same three arrays (difference, noise, mask),
+// so they advance in lock step: one grid-wide pass reads every region pixel once and feeds all
+// four; a tiny "decide" kernel between passes takes the reference's sequential decisions (clip
+// loop termination, histogram re-binning).  HBM/L2-bound streaming: 12 bytes per pixel per pass.
+// Block partial sums are combined in block order, so results are deterministic.
 #include "zb_internal.h"
+#include "zb_hist.cuh"
+
+// ------------------------------------------------------------------ FSIG / FSCAT
+
+__global__ void __launch_bounds__(256)
+k_final_sig(const ZbDev *__restrict__ D, ZbStamp *__restrict__ stamps,
+            const float *__restrict__ rdiff, const float *__restrict__ rnoise, const int32_t *__restrict__ omask)
+{
+    extern __shared__ __align__(16) unsigned char dyn[];
+    const int slot = blockIdx.x;
+    ZbStamp &S = stamps[slot];
+    if (S.nss <= 0 || S.sscnt >= S.nss) return;
+    const ZbRegion R = D->reg[S.region];
+    if (R.skip) return;
+    const int hwss = D->p.hw_ksstamp, fwss = D->sz.fw_ksstamp, npix = fwss * fwss;
+    double *term = (double *)dyn;
+    signed char *ok = (signed char *)(term + npix);
+    const int xR = S.xss[S.sscnt], yR = S.yss[S.sscnt];
+    for (int k = threadIdx.x; k < npix; k += blockDim.x) {
+        int j = k / fwss, i = k - j * fwss;
+        long long idx = R.off + (long long)(xR - hwss + i) + (long long)R.rpx * (yR - hwss + j);
+        float idat = rdiff[idx], indat = (float)(1. / rnoise[idx]);
+        signed char f = 0;
+        if (!(omask[idx] & ZB_FLAG_INPUT_ISBAD)) { f = 1; term[k] = (double)(idat * idat * indat * indat); }
+        ok[k] = f;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double sig = 0; int nsig = 0;
+        for (int k = 0; k < npix; k++) if (ok[k]) { nsig++; sig += term[k]; }
+        S.sig1 = nsig > 0 ? sig / nsig : -1;
+    }
+}
+
+// functions.c:1037-1107 sigma_clip on a short float array (one thread)
+__device__ static void sigma_clip_small(const float *data, char *rej, int count, double *mean, double *stdev, int maxiter, float statSig)
+{
+    if (count == 0) { *mean = 0; *stdev = ZB_MAXVAL; return; }
+    for (int i = 0; i < count; i++) rej[i] = 0;
+    int cnt = 0, ncnt = count, iter = 0;
+    while (ncnt != cnt && iter < maxiter) {
+        cnt = ncnt;
+        *mean = 0; *stdev = 0;
+        for (int i = 0; i < count; i++) if (!rej[i]) { float d = data[i]; *mean += d; *stdev += (double)(d * d); }
+        if (ncnt > 0) *mean /= ncnt; else { *mean = 0; *stdev = ZB_MAXVAL; return; }
+        if (ncnt > 1) { *stdev = *stdev - ncnt * (*mean) * (*mean); *stdev = sqrt(*stdev / (double)(ncnt - 1)); }
+        else { *stdev = ZB_MAXVAL; return; }
+        ncnt = 0;
+        double istd = 1. / (*stdev);
+        for (int i = 0; i < count; i++)
+            if (!rej[i]) { if ((fabs(data[i] - (*mean)) * istd) > statSig) rej[i] = 1; else ncnt++; }
+        iter++;
+    }
+}
+
+__global__ void k_final_clip(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
+                             float *__restrict__ ss_scratch, char *__restrict__ rej_scratch, double *__restrict__ q)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= D->n_regions || D->reg[r].skip) return;
+    const int base = D->reg[r].stamp_base, nS = fit[r].n_stamps, cap = D->sz.n_stamps;
+    float *ss = ss_scratch + (long long)r * cap;
+    char *rej = rej_scratch + (long long)r * cap;
+    int n = 0;
+    for (int k = 0; k < nS; k++) {
+        const ZbStamp &S = stamps[base + k];
+        if (S.sscnt < S.nss) ss[n++] = (float)S.sig1;
+    }
+    double mean = 0, sd = 0;
+    sigma_clip_small(ss, rej, n, &mean, &sd, 10, D->p.stat_sig);
+    q[(long long)r * 64 + 0] = mean;
+    q[(long long)r * 64 + 1] = sd;
+}
 
 int zb_launch_final_sig(zb_ctx *ctx, cudaStream_t st) {
-    cudaMemsetAsync(ctx->d_stats, 0, (size_t)ctx->sz.n_regions * 64 * sizeof(double), st);
+    const zb_sizes &sz = ctx->sz;
+    const int nR = sz.n_regions, npix = sz.fw_ksstamp * sz.fw_ksstamp;
+    cudaMemsetAsync(ctx->d_stats, 0, (size_t)nR * 64 * sizeof(double), st);
+    size_t sm = (size_t)npix * (sizeof(double) + 1) + 16;
+    cudaFuncSetAttribute(k_final_sig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    k_final_sig<<<ctx->n_slots, 256, sm, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask);
+    // scratch for the clip lives behind the 64 result doubles of every region
+    float *ss = (float *)(ctx->d_stats + (size_t)nR * 64);
+    char *rej = (char *)(ss + (size_t)nR * sz.n_stamps);
+    k_final_clip<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ss, rej, ctx->d_stats);
+    ctx->launches += 2;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "final sig kernels", __FILE__, __LINE__);
     return ZB_OK;
 }
 
-int zb_launch_region_stats(zb_ctx *ctx, cudaStream_t st) { (void)ctx; (void)st; return ZB_OK; }
+// ------------------------------------------------------------------ region statistics
+
+// stat index: 0 diff/GOOD, 1 noise/GOOD, 2 diff/OK, 3 noise/OK (the order main.c:1479-1535 runs them)
+__device__ static inline void qa_masks(int s, int &um, int &sm) {
+    if (s < 2) { um = 0x0; sm = 0xffff; } else { um = 0xff; sm = ZB_FLAG_OUTPUT_ISBAD; }
+}
+
+// The first 100 accepted random samples (functions.c:811-833), accepted in attempt order.
+__global__ void __launch_bounds__(256)
+k_qa_sample(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const float *__restrict__ rnoise,
+            const int32_t *__restrict__ omask, ZbQaStat *__restrict__ qa, const double *__restrict__ ran, int n_ran)
+{
+    const int s = blockIdx.x, r = blockIdx.y, tid = threadIdx.x;
+    const ZbRegion R = D->reg[r];
+    ZbQaStat &Q = qa[r * 4 + s];
+    __shared__ double work[100];
+    __shared__ int wsum[8];
+    __shared__ int s_acc;
+    if (R.skip) { if (tid == 0) { Q.phase = 2; Q.status = -1; } return; }
+    const int npts = R.rpx * R.rpy;
+    const float *data = ((s & 1) ? rnoise : rdiff) + R.off;
+    const int32_t *m = omask + R.off;
+    int um, sm; qa_masks(s, um, sm);
+    for (int k = tid; k < 256; k += 256) Q.bins[k] = 0;
+    if (tid < 100) work[tid] = 0.0;
+    if (tid == 0) s_acc = 0;
+    __syncthreads();
+    if (npts < 100) {
+        if (tid == 0) { Q.phase = 2; Q.status = 4; Q.mean = Q.sd = Q.mode = Q.median = Q.fwhm = Q.lfwhm = Q.sum = 0; }
+        return;
+    }
+    for (int base = 0; base < npts; base += 256) {
+        const int a = base + tid;
+        int flag = 0; double rdat = 0;
+        if (a < npts && 2 * a + 1 < n_ran) {
+            int xr = (int)floor(ran[2 * a] * R.rpx), yr = (int)floor(ran[2 * a + 1] * R.rpy);
+            rdat = data[xr + yr * R.rpx];
+            flag = !zb_excluded(m[xr + yr * R.rpx], rdat, um, sm);
+        }
+        unsigned bal = __ballot_sync(0xffffffffu, flag);
+        if ((tid & 31) == 0) wsum[tid >> 5] = __popc(bal);
+        __syncthreads();
+        int before = s_acc;
+        for (int w = 0; w < (tid >> 5); w++) before += wsum[w];
+        int pos = before + __popc(bal & ((1u << (tid & 31)) - 1u));
+        if (flag && pos < 100) work[pos] = rdat;
+        __syncthreads();
+        if (tid == 0) { int t = 0; for (int w = 0; w < 8; w++) t += wsum[w]; s_acc += t; }
+        __syncthreads();
+        if (s_acc >= 100) break;
+    }
+    if (tid == 0) {
+        int n = s_acc < 100 ? s_acc : 100;
+        for (int a = 1; a < n; a++) {
+            double v = work[a]; int b = a - 1;
+            while (b >= 0 && work[b] > v) { work[b + 1] = work[b]; b--; }
+            work[b + 1] = v;
+        }
+        Q.npts_s = n;
+        Q.samp_med = work[(int)(0.5f * n)];
+        Q.binsize = (work[(int)(0.9f * n)] - work[(int)(0.5f * n)]) / (float)100;
+        Q.bin1 = work[(int)(0.5f * n)] - 128. * Q.binsize;
+        Q.phase = 0; Q.status = 0; Q.maxiter = 5; Q.umask = um; Q.smask = sm; Q.use_noise = s & 1;
+        Q.ncrit = 0; Q.cnt_prev = 0; Q.tries = 0; Q.imax = 0;
+        Q.mean = Q.sd = Q.mode = Q.median = Q.fwhm = Q.lfwhm = Q.sum = 0;
+    }
+}
+
+struct QaShared {
+    int phase[4], ncrit[4];
+    double cm[4][8], ci[4][8], mean[4], isd[4], bin1[4], binsize[4];
+    int bins[4][256];
+    double ra[8], rb[8]; int rc[8];
+};
+
+__device__ static void qa_block_sum(QaShared &S, double &a, double &b, int &c) {
+    for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b += __shfl_xor_sync(0xffffffffu, b, o);
+        c += __shfl_xor_sync(0xffffffffu, c, o);
+    }
+    const int w = threadIdx.x >> 5;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) { S.ra[w] = a; S.rb[w] = b; S.rc[w] = c; }
+    __syncthreads();
+    double sa = 0, sb = 0; int sc = 0;
+    for (int k = 0; k < 8; k++) { sa += S.ra[k]; sb += S.rb[k]; sc += S.rc[k]; }
+    a = sa; b = sb; c = sc;
+}
+
+__global__ void __launch_bounds__(256)
+k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const float *__restrict__ rnoise,
+          int32_t *__restrict__ omask, int32_t *__restrict__ out_mask, ZbQaStat *__restrict__ qa,
+          ZbQaPart *__restrict__ part, int first)
+{
+    __shared__ QaShared S;
+    const int r = blockIdx.y, tid = threadIdx.x;
+    const ZbRegion R = D->reg[r];
+    if (R.skip) return;
+    if (tid < 4) {
+        const ZbQaStat &Q = qa[r * 4 + tid];
+        S.phase[tid] = Q.phase; S.ncrit[tid] = Q.ncrit;
+        for (int c = 0; c < 8; c++) { S.cm[tid][c] = Q.crit_mean[c]; S.ci[tid][c] = Q.crit_istd[c]; }
+        S.mean[tid] = Q.mean; S.isd[tid] = 1. / Q.sd; S.bin1[tid] = Q.bin1; S.binsize[tid] = Q.binsize;
+    }
+    for (int k = tid; k < 4 * 256; k += 256) (&S.bins[0][0])[k] = 0;
+    __syncthreads();
+    if (!first && S.phase[0] == 2 && S.phase[1] == 2 && S.phase[2] == 2 && S.phase[3] == 2) return;
+    const float statSig = D->p.stat_sig;
+    const int npix = R.rpx * R.rpy;
+    double a1[4] = {0, 0, 0, 0}, a2[4] = {0, 0, 0, 0}; int an[4] = {0, 0, 0, 0};
+    double nsum = 0; int nn = 0;
+    for (int k = blockIdx.x * 256 + tid; k < npix; k += ZB_QA_NBLK * 256) {
+        const float d = rdiff[R.off + k], nz = rnoise[R.off + k];
+        const int m0 = omask[R.off + k];
+        // NaN/Inf side effect of getStampStats3 (functions.c:857-861), in the order the runs happen
+        int ms[4] = {m0, m0, m0, m0}, mn = m0;
+        const bool nfd = ((double)d * 0.0 != 0.0), nfn = ((double)nz * 0.0 != 0.0);
+        if (nfd || nfn) {
+            const int mark = ZB_FLAG_INPUT_ISBAD | ZB_FLAG_ISNAN;
+            int m = m0;
+            if (nfd && !zb_excluded(m, d, 0x0, 0xffff)) m |= mark;
+            ms[1] = m;
+            if (nfn && !zb_excluded(m, nz, 0x0, 0xffff)) m |= mark;
+            mn = m; ms[2] = m;
+            if (nfd && !zb_excluded(m, d, 0xff, ZB_FLAG_OUTPUT_ISBAD)) m |= mark;
+            ms[3] = m;
+            if (nfn && !zb_excluded(m, nz, 0xff, ZB_FLAG_OUTPUT_ISBAD)) m |= mark;
+            if (first && m != m0) {
+                omask[R.off + k] = m;
+                const int y = k / R.rpx, x = k - y * R.rpx;
+                if (out_mask && x >= R.rx0 - R.bx0 && x <= R.own_x1 - R.bx0 && y >= R.ry0 - R.by0 && y <= R.own_y1 - R.by0)
+                    out_mask[(long long)(R.by0 + y) * D->nx + (R.bx0 + x)] = m;
+            }
+        }
+        if (first && !zb_excluded(mn, d, 0x0, 0xffff)) {           // getNoiseStats3, functions.c:719-761
+            float ndat = (float)(1. / nz);
+            nn++; nsum += (double)(d * d * ndat * ndat);
+        }
+#pragma unroll
+        for (int s = 0; s < 4; s++) {
+            if (S.phase[s] == 2) continue;
+            const float x = (s & 1) ? nz : d;
+            int um, sm; qa_masks(s, um, sm);
+            if (zb_excluded(ms[s], x, um, sm)) continue;
+            if ((double)x * 0.0 != 0.0) continue;
+            if (S.phase[s] == 0) {
+                bool rej = false;
+                for (int c = 0; c < S.ncrit[s]; c++) rej |= (fabs(x - S.cm[s][c]) * S.ci[s][c]) > statSig;
+                if (rej) continue;
+                a1[s] += x; a2[s] += (double)(x * x); an[s]++;
+            } else {
+                if ((fabs(x - S.mean[s]) * S.isd[s]) > statSig) continue;
+                int index = (int)(floor((x - S.bin1[s]) / S.binsize[s]) + 1);
+                index = (index < 0 ? 0 : index);
+                index = (index > 255 ? 255 : index);
+                atomicAdd(&S.bins[s][index], 1);
+                a1[s] += fabs((double)x); an[s]++;
+            }
+        }
+    }
+    for (int s = 0; s < 4; s++) {
+        if (S.phase[s] == 2) continue;
+        qa_block_sum(S, a1[s], a2[s], an[s]);
+        if (tid == 0) { ZbQaPart &P = part[(r * 5 + s) * ZB_QA_NBLK + blockIdx.x]; P.s1 = a1[s]; P.s2 = a2[s]; P.n = an[s]; }
+        if (S.phase[s] == 1) {
+            __syncthreads();
+            int v = S.bins[s][tid];
+            if (v) atomicAdd(&qa[r * 4 + s].bins[tid], v);
+        }
+    }
+    if (first) {
+        double z = 0;
+        qa_block_sum(S, nsum, z, nn);
+        if (tid == 0) { ZbQaPart &P = part[(r * 5 + 4) * ZB_QA_NBLK + blockIdx.x]; P.s1 = nsum; P.s2 = 0; P.n = nn; }
+    }
+}
+
+// The sequential decisions of sigma_clip (functions.c:1037-1107) and of the re-binning loop
+// (functions.c:879-1031) for one (region, stat); thread 4 finishes getNoiseStats3 on the first pass.
+__global__ void k_qa_decide(const ZbDev *__restrict__ D, ZbQaStat *__restrict__ qa, const ZbQaPart *__restrict__ part,
+                            double *__restrict__ q, int first)
+{
+    const int r = blockIdx.x, s = threadIdx.x;
+    if (D->reg[r].skip) return;
+    const ZbQaPart *P = part + (r * 5 + s) * ZB_QA_NBLK;
+    double s1 = 0, s2 = 0; long long n = 0;
+    if (s == 4) {
+        if (!first) return;
+        for (int b = 0; b < ZB_QA_NBLK; b++) { s1 += P[b].s1; n += P[b].n; }
+        q[(long long)r * 64 + 3] = (double)n;
+        q[(long long)r * 64 + 2] = (n > 1) ? s1 / (float)n : ZB_MAXVAL;
+        return;
+    }
+    ZbQaStat &Q = qa[r * 4 + s];
+    if (Q.phase == 2) return;
+    for (int b = 0; b < ZB_QA_NBLK; b++) { s1 += P[b].s1; s2 += P[b].s2; n += P[b].n; }
+    const int ncnt = (int)n;
+    if (Q.phase == 0) {
+        const int k = Q.ncrit;                          // passes done so far == iterations started
+        if (k == 0 && ncnt == 0) { Q.mean = 0; Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
+        if (ncnt != Q.cnt_prev && k < Q.maxiter) {
+            Q.cnt_prev = ncnt;
+            if (ncnt > 0) Q.mean = s1 / ncnt;
+            else { Q.mean = 0; Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
+            if (ncnt > 1) { double sd = s2 - ncnt * Q.mean * Q.mean; Q.sd = sqrt(sd / (double)(ncnt - 1)); }
+            else { Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
+            Q.crit_mean[k] = Q.mean; Q.crit_istd[k] = 1. / Q.sd; Q.ncrit = k + 1;
+            if (k + 1 >= Q.maxiter) Q.phase = 1;        // iter == maxiter ends the loop whatever the next count is
+        } else Q.phase = 1;
+        return;
+    }
+    // histogram phase: this pass filled Q.bins with the current bin1/binsize
+    const int goodcnt = ncnt;
+    if (goodcnt == 0) { Q.mode = Q.median = Q.samp_med; Q.fwhm = Q.lfwhm = 0.; Q.status = 2; Q.phase = 2; return; }
+    if (Q.binsize == 0.) { Q.mode = Q.median = Q.samp_med; Q.fwhm = Q.lfwhm = 0.; Q.status = 3; Q.phase = 2; return; }
+    HistOut o; int imax = Q.imax;
+    hist_analyse(Q.bins, goodcnt, Q.bin1, Q.binsize, imax, o);
+    Q.imax = imax; Q.mode = o.mode;
+    if (o.action == 0) { Q.sum = s1; Q.fwhm = o.fwhm; Q.lfwhm = o.lfwhm; Q.median = o.median; Q.status = 0; Q.phase = 2; return; }
+    if (o.action == 1) { Q.bin1 = Q.bin1 - 128. * Q.binsize; Q.binsize = Q.binsize * 2.; }
+    else { Q.binsize = Q.binsize / 3.; Q.bin1 = o.mode - 128. * Q.binsize; }
+    Q.tries++;
+    for (int b = 0; b < 256; b++) Q.bins[b] = 0;
+    if (Q.tries >= 5) { Q.status = 1; Q.phase = 2; }
+}
+
+__global__ void k_qa_finish(const ZbDev *__restrict__ D, const ZbQaStat *__restrict__ qa, double *__restrict__ q)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= D->n_regions || D->reg[r].skip) return;
+    const ZbQaStat *Q = qa + r * 4;
+    double *o = q + (long long)r * 64;
+    o[4] = Q[0].mean; o[5] = Q[0].sd; o[6] = Q[1].mean;
+    o[7] = Q[2].mean; o[8] = Q[2].sd; o[9] = Q[3].mean;
+    double nscalo = Q[0].sd / Q[1].mean;
+    if (D->p.rescale_ok) nscalo = (Q[2].sd / Q[3].mean) / nscalo;       // main.c:1557-1561
+    o[10] = nscalo;
+}
+
+// -okn: scale the noise of OK pixels (main.c:1563-1576); output pixels only
+__global__ void k_rescale_ok(const ZbDev *__restrict__ D, const int32_t *__restrict__ omask, const double *__restrict__ q,
+                             float *__restrict__ noise)
+{
+    const int r = blockIdx.y;
+    const ZbRegion R = D->reg[r];
+    if (R.skip) return;
+    const double diffrat = q[(long long)r * 64 + 10];
+    if (!(diffrat > 1)) return;
+    const int npix = R.rpx * R.rpy;
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < npix; k += gridDim.x * blockDim.x) {
+        const int m = omask[R.off + k];
+        if (!((m & 0xff) && !(m & ZB_FLAG_OUTPUT_ISBAD))) continue;
+        const int y = k / R.rpx, x = k - y * R.rpx;
+        if (x >= R.rx0 - R.bx0 && x <= R.own_x1 - R.bx0 && y >= R.ry0 - R.by0 && y <= R.own_y1 - R.by0) {
+            long long g = (long long)(R.by0 + y) * D->nx + (R.bx0 + x);
+            noise[g] = (float)((double)noise[g] * diffrat);
+        }
+    }
+}
+
+int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStream_t st)
+{
+    const int nR = ctx->sz.n_regions;
+    k_qa_sample<<<dim3(4, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, ctx->d_qa, ctx->d_ran, ctx->n_ran);
+    ctx->launches++;
+    // at most maxiter (5) clip passes + 5 histogram passes; finished regions fall through at once
+    for (int pass = 0; pass < 10; pass++) {
+        k_qa_pass<<<dim3(ZB_QA_NBLK, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
+                                                        ctx->d_qa, ctx->d_qpart, pass == 0);
+        k_qa_decide<<<nR, 5, 0, st>>>(ctx->d_dev, ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0);
+        ctx->launches += 2;
+    }
+    k_qa_finish<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_qa, ctx->d_stats);
+    ctx->launches++;
+    if (ctx->p.rescale_ok) {
+        k_rescale_ok<<<dim3(64, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_omask, ctx->d_stats, noise);
+        ctx->launches++;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "region stats kernels", __FILE__, __LINE__);
+    return ZB_OK;
+}

@@ -215,3 +215,17 @@ def quick_background_estimate(data, mask):
     bkg = np.median(bkgpix)
     bkgstd = 1.4826 * np.median(np.abs(bkgpix - bkg))
     return float(bkg), float(bkgstd)
+
+
+def params_for_pair(pair, nreg_side=3, hotpants_kws=None):
+    """zb_params for a synthetic pair exactly as the zuds command line would set them
+    (zuds/hotpants.py:38-93 -> hotpants/vargs.c)."""
+    ny, nx = pair.sci.shape
+    scibkg, scistd = quick_background_estimate(pair.sci, pair.sci_mask)
+    refbkg, refstd = quick_background_estimate(pair.ref, pair.ref_mask)
+    il, tl = scibkg - 10 * scistd, refbkg - 10 * refstd
+    cmd = hotpants_command("sci.fits", "ref.fits", "sub.fits", "sci.rms.fits", "ref.rms.fits", "bpm.fits",
+                           pair.seeing, nx, ny, il, tl, nreg_side=nreg_side, hotpants_kws=hotpants_kws)
+    a = parse_hotpants_args(cmd.split()[1:])
+    a.params.nx, a.params.ny = nx, ny
+    return a.params
