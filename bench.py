@@ -149,3 +149,263 @@ class Pool:
             t.join()
         for c in self.ctxs:
             c.close()
+
+
+# --------------------------------------------------------------------------- CPU side
+
+def write_pair_fits(pair, d):
+    import hp_helpers as H
+    return H.write_pair(pair, d)
+
+
+def reference_command(case, pair, names, outdir, tag):
+    import cases as CS
+    import hp_helpers as H
+    n = dict(names)
+    n["out"] = os.path.join(outdir, "sub_%s.fits" % tag)
+    exe = H.REF_BIN if os.path.exists(H.REF_BIN) else None
+    return exe, (CS.command(case, pair, n, exe=exe or "hotpants"))
+
+
+def run_cpu_once(case, pair, names, outdir, nproc):
+    """`nproc` concurrent single-threaded hotpants processes (how zuds runs it: srun -n 64 -c1,
+    nersc/controller.py:101), each on one full pair.  Returns wall seconds and the kind used."""
+    import hp_helpers as H
+    if os.path.exists(H.REF_BIN):
+        procs = []
+        t0 = time.perf_counter()
+        for k in range(nproc):
+            _, cmd = reference_command(case, pair, names, outdir, "p%d" % k)
+            procs.append(subprocess.Popen(cmd.split(), stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL))
+        rcs = [p.wait() for p in procs]
+        dt = time.perf_counter() - t0
+        if any(rcs):
+            raise RuntimeError("reference hotpants exited with %s" % rcs)
+        return dt, "reference"
+    # oracle port (single process, `nproc` threads: ctypes releases the GIL)
+    import cases as CS
+    lib = H.load_oracle()
+    p = CS.params_of(case, pair)
+    ins = CS.inputs_of(case, pair)
+    ths = [threading.Thread(target=H.run_oracle, args=(lib, p) + tuple(ins)) for _ in range(nproc)]
+    t0 = time.perf_counter()
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    return time.perf_counter() - t0, "port"
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def bench_reference(args):
+    """--impl reference: the reference's own CPU implementation on all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import cases as CS
+    case = workload_case()
+    pair = CS.make_pair(case)
+    import hp_helpers as H
+    nproc = args.cpu_procs or host_cores()
+    if not os.path.exists(H.REF_BIN):
+        nproc = 1                      # the oracle port keeps hotpants' global ran1 state: one thread only
+    with tempfile.TemporaryDirectory(prefix="zb_ref_") as d:
+        names = write_pair_fits(pair, d)
+        for _ in range(min(args.warmup, 1)):      # host code has no clocks/caches to warm beyond one pass
+            run_cpu_once(case, pair, names, d, nproc)
+        times = []
+        kind = "reference"
+        for _ in range(args.steps):
+            dt, kind = run_cpu_once(case, pair, names, d, nproc)
+            times.append(dt)
+    total = sum(times)
+    value = nproc * len(times) / total
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "c1: 3080x3072 quadrant pair, -c t -n i -r 10 -rss 24 -ko 2 -bgo 0, 3x3 regions x 10x10 stamps",
+                   "pairs_per_step": nproc},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": nproc, "kind": kind,
+                         "sample": "%d concurrent single-threaded hotpants processes per step, one full pair each (FITS in/out on local disk)" % nproc},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------- GPU side
+
+def bench_b200(args):
+    import torch
+    import torch.distributed as dist
+    import cases as CS
+    from zuds_pipeline_b200 import _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the subtraction path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    case = workload_case()
+    ny, nx = case.shape
+    npairs_distinct = 2
+    pairs, params, dev_in, pin_in = [], [], [], []
+    for k in range(npairs_distinct):
+        c = CS.Case(case.name, case.shape, case.seeing, case.nreg_side, case.hotpants_kws, case.synth_kws,
+                    seed=1000 + rank * npairs_distinct + k)
+        pair = CS.make_pair(c)
+        pairs.append(pair)
+        params.append(CS.params_of(c, pair))
+        ins = CS.inputs_of(c, pair)
+        pinned = [None if a is None else torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in ins]
+        pin_in.append(pinned)
+        dev_in.append([None if t is None else t.cuda(non_blocking=True) for t in pinned])
+    torch.cuda.synchronize()
+
+    W, B = args.workers, args.batch
+    pool = Pool(local, W)
+    dev_out = [(torch.empty((ny, nx), dtype=torch.float32, device="cuda"), torch.empty((ny, nx), dtype=torch.float32, device="cuda"),
+                torch.empty((ny, nx), dtype=torch.int32, device="cuda")) for _ in range(W)]
+    pin_out = [(torch.empty((ny, nx), dtype=torch.float32).pin_memory(), torch.empty((ny, nx), dtype=torch.float32).pin_memory(),
+                torch.empty((ny, nx), dtype=torch.int32).pin_memory()) for _ in range(W)]
+    slot_of = {id(c): i for i, c in enumerate(pool.ctxs)}
+
+    def dev_job(k):
+        def fn(ctx):
+            return ctx.subtract(params[k], *dev_in[k], out=dev_out[slot_of[id(ctx)]], stream=_NullStream())
+        return fn
+
+    def host_job(k):
+        def fn(ctx):
+            o = pin_out[slot_of[id(ctx)]]
+            ins = [None if t is None else t.numpy() for t in pin_in[k]]
+            return ctx.subtract_host(params[k], *ins, out=(o[0].numpy(), o[1].numpy(), o[2].numpy()))
+        return fn
+
+    def step(make_job):
+        return pool.run_batch([make_job(i % npairs_distinct) for i in range(B)])
+
+    # ---- device-resident throughput ("value")
+    for _ in range(args.warmup):
+        step(dev_job)
+    barrier()
+    clocks = ClockSampler(local)
+    clocks.start()
+    l0 = pool.launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    conv_ms = []
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        _, ms = step(dev_job)
+        conv_ms += ms
+    e1.record()
+    barrier()
+    wall = time.perf_counter() - t0
+    dev_s = e0.elapsed_time(e1) / 1e3
+    launches = pool.launches() - l0
+    clk = clocks.stop()
+    # ---- end to end through the host-buffer call ("e2e")
+    for _ in range(max(1, args.warmup // 2)):
+        step(host_job)
+    barrier()
+    h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    h0.record()
+    for _ in range(args.steps):
+        step(host_job)
+    h1.record()
+    barrier()
+    host_s = h0.elapsed_time(h1) / 1e3
+    # ---- the convolution kernel alone, one context, nothing else on the GPU (roofline)
+    serial_ms = []
+    for i in range(6):
+        pool.ctxs[0].subtract(params[i % npairs_distinct], *dev_in[i % npairs_distinct], out=dev_out[0], stream=_NullStream())
+        if i >= 2:
+            serial_ms.append(pool.ctxs[0].timings())
+    stage_ms = {k: statistics.mean(t[k] for t in serial_ms) for k in serial_ms[0]}
+
+    tmax = torch.tensor([dev_s, host_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    dev_s, host_s = float(tmax[0]), float(tmax[1])
+    pairs_total = world * args.steps * B
+    in_bytes = sum(t.numel() * t.element_size() for t in pin_in[0] if t is not None)
+    out_bytes = sum(t.numel() * t.element_size() for t in pin_out[0])
+    hbm_peak, peak_src = peaks()
+    alg_bytes = ALG_BYTES_PER_PIXEL * nx * ny
+    conv_s = stage_ms["k_convolve"] / 1e3
+    achieved = alg_bytes / conv_s / 1e9
+    line = {
+        "metric": METRIC, "value": pairs_total / dev_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "c1: 3080x3072 quadrant pair, -c t -n i -r 10 -rss 24 -ko 2 -bgo 0, 3x3 regions x 10x10 stamps (BASELINE configs[1])",
+                   "pairs_per_step_per_gpu": B, "contexts_per_gpu": W, "distinct_pairs_per_gpu": npairs_distinct,
+                   "l2": "inputs of one pair are 161 MB (> 126 MB L2) and consecutive jobs alternate pairs",
+                   "sharding": "by image pair, no collective"},
+        "e2e": {"value": pairs_total / host_s, "unit": UNIT, "h2d_bytes_per_step": in_bytes * B, "d2h_bytes_per_step": out_bytes * B},
+        "gpu_launches": launches,
+        "clocks": clk,
+        "roofline": {"kernel": "k_convolve", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                     "alg_bytes_per_launch": alg_bytes, "kernel_ms": stage_ms["k_convolve"],
+                     "kernel_ms_in_timed_region": statistics.mean(conv_ms) if conv_ms else None,
+                     "fp64_dfma_per_launch": 2 * (2 * params[0].hw_kernel + 1) ** 2 * nx * ny,
+                     "note": "compute-bound at hw=10 (2x441 FP64 FMA per pixel, reference semantics); HBM fraction reported as the north star asks"},
+        "stage_ms_serial": {k: round(v, 4) for k, v in stage_ms.items()},
+        "wall_s": wall,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu:
+        with tempfile.TemporaryDirectory(prefix="zb_cpu_") as d:
+            import hp_helpers as H
+            names = write_pair_fits(pairs[0], d)
+            dt, kind = run_cpu_once(case, pairs[0], names, d, 1)
+        line["cpu_baseline"] = {"value": 1.0 / dt, "unit": UNIT, "cores": 1, "kind": kind,
+                                "sample": "1 full 3080x3072 pair, one single-threaded hotpants process incl. FITS I/O (%.1f s)" % dt}
+    pool.close()
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+class _NullStream:
+    """Passes NULL as the stream: the ctx then runs on its own non-blocking stream."""
+    cuda_stream = 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workers", type=int, default=4, help="concurrent contexts (streams) per GPU")
+    ap.add_argument("--batch", type=int, default=8, help="pair subtractions per step per GPU")
+    ap.add_argument("--cpu-procs", type=int, default=0, help="reference arm: concurrent hotpants processes (0 = all cores)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        bench_reference(args)
+    else:
+        bench_b200(args)
+
+
+if __name__ == "__main__":
+    main()
