@@ -278,37 +278,56 @@ k_build_matrix(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, 
     }
 }
 
-// Right-looking LU with the reference's pivot rule (implicit scaling, ties: last row wins) and
-// substitution, one CTA per region.  For every element the subtractions a_ij -= l_ik*u_kj happen
-// for k ascending, unfused, exactly as in the Crout loops of alard.c:1495-1509.
-#define LU_NT 1024
-__global__ void __launch_bounds__(LU_NT)
-k_lu_solve(const ZbDev *__restrict__ D, ZbFit *__restrict__ fit, double *__restrict__ mat, double *__restrict__ sol,
-           double *__restrict__ vvs, int *__restrict__ indxs)
+// ---------------------------------------------------------------------------- LU
+// alard.c:1465-1552 ludcmp + lubksb, blocked so that the O(n^3) part runs on every SM while each
+// matrix element still receives exactly the reference's operations in the reference's order:
+// a_ij -= l_ik * u_kj for k ascending (product rounded, then the subtraction rounded), pivot = last
+// row among the maxima of vv[i]*|a_ik|, l_ik = a_ik * (1/a_kk).  A right-looking blocked LU applies
+// the k's panel by panel in ascending order, so the per-element sequence is unchanged and the
+// factors (and the solution) are bit-identical to the Crout loops of the reference.
+//   k_lu_init    row scale factors vv, singular test
+//   k_lu_panel   unblocked factorisation of one LU_NB-column panel in shared memory (one CTA per region)
+//   k_lu_swap_u  the panel's row swaps on the columns outside it + the U12 triangular solve
+//   k_lu_trail   A22 -= L21 * U12 on 32x32 tiles
+//   k_lu_subst   permutation, forward and back substitution
+#define LU_NB 32
+#define LU_PT 512
+
+__global__ void __launch_bounds__(128)
+k_lu_init(const ZbDev *__restrict__ D, ZbFit *__restrict__ fit, const double *__restrict__ mat, double *__restrict__ vvs)
 {
-    const int r = blockIdx.x;
+    const int r = blockIdx.y;
     if (!fit[r].active) return;
+    const int n = D->sz.mat_size, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double *row = mat + (long long)r * n * n + (long long)i * n;
+    double big = 0.0;
+    for (int j = 0; j < n; j++) { double t = fabs(row[j]); if (t > big) big = t; }
+    if (big == 0.) fit[r].singular = 1; else vvs[(long long)r * n + i] = 1.0 / big;
+}
+
+__global__ void __launch_bounds__(LU_PT)
+k_lu_panel(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, double *__restrict__ mat,
+           double *__restrict__ vvs, int *__restrict__ indxs, int k0)
+{
+    extern __shared__ __align__(16) unsigned char dyn[];
+    const int r = blockIdx.x;
+    if (!fit[r].active || fit[r].singular) return;
     const int n = D->sz.mat_size, tid = threadIdx.x;
+    const int nb = min(LU_NB, n - k0), m = n - k0, ld = LU_NB + 1;
     double *a = mat + (long long)r * n * n;
-    double *b = sol + (long long)r * (D->sz.n_comp_total + 1) + 1;
-    double *vv = vvs + (long long)r * n;
-    int *indx = indxs + (long long)r * n;
-    __shared__ int s_imax, s_sing;
-    if (tid == 0) s_sing = 0;
+    double *P = (double *)dyn;                    // [m][ld]: rows k0.., columns k0..k0+nb-1
+    double *vv = P + (size_t)m * ld;              // [m]
+    __shared__ double s_v[LU_PT / 32]; __shared__ int s_i[LU_PT / 32];
+    __shared__ int s_imax;
+    for (int e = tid; e < m * nb; e += LU_PT) { int i = e / nb, c = e - i * nb; P[i * ld + c] = a[(long long)(k0 + i) * n + k0 + c]; }
+    for (int i = tid; i < m; i += LU_PT) vv[i] = vvs[(long long)r * n + k0 + i];
     __syncthreads();
-    for (int i = tid; i < n; i += LU_NT) {
-        double big = 0.0;
-        for (int j = 0; j < n; j++) { double t = fabs(a[(long long)i * n + j]); if (t > big) big = t; }
-        if (big == 0.) s_sing = 1; else vv[i] = 1.0 / big;
-    }
-    __syncthreads();
-    if (s_sing) { if (tid == 0) fit[r].singular = 1; return; }   // ludcmp returns 1, solution is meaningless
-    for (int k = 0; k < n; k++) {
-        // pivot: max of vv[i]*|a[i][k]| over i >= k, last index on ties.  The products are >= 0,
-        // so their IEEE bit patterns order like the values.
+    for (int kk = 0; kk < nb; kk++) {
+        // pivot: products are >= 0, ties -> the larger row index (the reference scans upward with >=)
         double bestv = -1.0; int besti = -1;
-        for (int i = k + tid; i < n; i += LU_NT) {
-            double dum = vv[i] * fabs(a[(long long)i * n + k]);
+        for (int i = kk + tid; i < m; i += LU_PT) {
+            double dum = vv[i] * fabs(P[i * ld + kk]);
             if (dum >= bestv) { bestv = dum; besti = i; }
         }
         for (int o = 16; o > 0; o >>= 1) {
@@ -316,59 +335,174 @@ k_lu_solve(const ZbDev *__restrict__ D, ZbFit *__restrict__ fit, double *__restr
             int oi = __shfl_xor_sync(0xffffffffu, besti, o);
             if (ov > bestv || (ov == bestv && oi > besti)) { bestv = ov; besti = oi; }
         }
-        __shared__ double s_v[LU_NT / 32]; __shared__ int s_i[LU_NT / 32];
         if ((tid & 31) == 0) { s_v[tid >> 5] = bestv; s_i[tid >> 5] = besti; }
         __syncthreads();
-        if (tid == 0) {
-            double bv = -1.0; int bi = -1;
-            for (int w = 0; w < LU_NT / 32; w++)
-                if (s_v[w] > bv || (s_v[w] == bv && s_i[w] > bi)) { bv = s_v[w]; bi = s_i[w]; }
-            s_imax = bi;
+        if (tid < 32) {
+            double bv = tid < LU_PT / 32 ? s_v[tid] : -1.0; int bi = tid < LU_PT / 32 ? s_i[tid] : -1;
+            for (int o = 16; o > 0; o >>= 1) {
+                double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ov > bv || (ov == bv && oi > bi)) { bv = ov; bi = oi; }
+            }
+            if (tid == 0) s_imax = bi;
         }
         __syncthreads();
         const int imax = s_imax;
-        if (imax != k) {
-            for (int c = tid; c < n; c += LU_NT) {
-                double t = a[(long long)imax * n + c];
-                a[(long long)imax * n + c] = a[(long long)k * n + c];
-                a[(long long)k * n + c] = t;
-            }
-        }
-        __syncthreads();
+        if (imax != kk && tid < nb) { double t = P[imax * ld + tid]; P[imax * ld + tid] = P[kk * ld + tid]; P[kk * ld + tid] = t; }
         if (tid == 0) {
-            if (imax != k) vv[imax] = vv[k];
-            indx[k] = imax;
-            if (a[(long long)k * n + k] == 0.0) a[(long long)k * n + k] = 1.0e-20;
+            if (imax != kk) vv[imax] = vv[kk];
+            indxs[(long long)r * n + k0 + kk] = k0 + imax;
         }
         __syncthreads();
-        if (k != n - 1) {
-            const double dum = 1.0 / a[(long long)k * n + k];
-            for (int i = k + 1 + tid; i < n; i += LU_NT) a[(long long)i * n + k] *= dum;
+        if (tid == 0 && P[kk * ld + kk] == 0.0) P[kk * ld + kk] = 1.0e-20;
+        __syncthreads();
+        if (k0 + kk != n - 1) {
+            const double dum = 1.0 / P[kk * ld + kk];
+            // scale the column and update the rest of the panel row by row: thread -> (row, column)
+            const int w = nb - kk - 1;            // columns to the right inside the panel
+            for (int i = kk + 1 + tid; i < m; i += LU_PT) P[i * ld + kk] *= dum;
             __syncthreads();
-            const int m = n - k - 1;
-            for (int e = tid; e < m * m; e += LU_NT) {
-                int i = k + 1 + e / m, j = k + 1 + e % m;
-                a[(long long)i * n + j] -= a[(long long)i * n + k] * a[(long long)k * n + j];
-            }
+            if (w > 0)
+                for (int e = tid; e < (m - kk - 1) * w; e += LU_PT) {
+                    int i = kk + 1 + e / w, c = kk + 1 + e % w;
+                    P[i * ld + c] -= P[i * ld + kk] * P[kk * ld + c];
+                }
             __syncthreads();
         }
     }
-    // lubksb: permutation, forward substitution (column sweep keeps j ascending per row), back substitution
+    for (int e = tid; e < m * nb; e += LU_PT) { int i = e / nb, c = e - i * nb; a[(long long)(k0 + i) * n + k0 + c] = P[i * ld + c]; }
+    for (int i = tid; i < m; i += LU_PT) vvs[(long long)r * n + k0 + i] = vv[i];
+}
+
+// One thread per column outside the panel: the panel's row swaps in order, then (right of the panel)
+// u_kj = a_kj - sum_{k'<k in panel} l_kk' u_k'j.
+__global__ void __launch_bounds__(128)
+k_lu_swap_u(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, double *__restrict__ mat,
+            const int *__restrict__ indxs, int k0)
+{
+    __shared__ double L[LU_NB][LU_NB + 1];
+    __shared__ int piv[LU_NB];
+    const int r = blockIdx.y;
+    if (!fit[r].active || fit[r].singular) return;
+    const int n = D->sz.mat_size, nb = min(LU_NB, n - k0);
+    double *a = mat + (long long)r * n * n;
+    for (int e = threadIdx.x; e < nb * nb; e += blockDim.x) { int i = e / nb, c = e - i * nb; L[i][c] = a[(long long)(k0 + i) * n + k0 + c]; }
+    if (threadIdx.x < nb) piv[threadIdx.x] = indxs[(long long)r * n + k0 + threadIdx.x];
+    __syncthreads();
+    int j = blockIdx.x * blockDim.x + threadIdx.x;           // index among the n - nb outside columns
+    if (j >= n - nb) return;
+    if (j >= k0) j += nb;
+    for (int kk = 0; kk < nb; kk++) {
+        const int ip = piv[kk];
+        if (ip != k0 + kk) { double t = a[(long long)ip * n + j]; a[(long long)ip * n + j] = a[(long long)(k0 + kk) * n + j]; a[(long long)(k0 + kk) * n + j] = t; }
+    }
+    if (j < k0) return;
+    double u[LU_NB];
+#pragma unroll
+    for (int kk = 0; kk < LU_NB; kk++) {
+        if (kk < nb) {
+            double sum = a[(long long)(k0 + kk) * n + j];
+#pragma unroll
+            for (int q = 0; q < LU_NB; q++) if (q < kk) sum -= L[kk][q] * u[q];
+            u[kk] = sum;
+            a[(long long)(k0 + kk) * n + j] = sum;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_lu_trail(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, double *__restrict__ mat, int k0)
+{
+    __shared__ double Ls[32][LU_NB + 1];         // rows of the tile x panel columns
+    __shared__ double Us[LU_NB][32 + 1];         // panel rows x columns of the tile
+    const int r = blockIdx.z;
+    if (!fit[r].active || fit[r].singular) return;
+    const int n = D->sz.mat_size, nb = min(LU_NB, n - k0), t0 = k0 + nb;
+    const int i0 = t0 + blockIdx.y * 32, j0 = t0 + blockIdx.x * 32;
+    if (i0 >= n || j0 >= n) return;
+    double *a = mat + (long long)r * n * n;
+    const int tid = threadIdx.x;
+    for (int e = tid; e < 32 * LU_NB; e += 256) {
+        int i = e / LU_NB, c = e - i * LU_NB;
+        Ls[i][c] = (i0 + i < n && c < nb) ? a[(long long)(i0 + i) * n + k0 + c] : 0.0;
+        int kk = e / 32, jj = e - kk * 32;
+        Us[kk][jj] = (j0 + jj < n && kk < nb) ? a[(long long)(k0 + kk) * n + j0 + jj] : 0.0;
+    }
+    __syncthreads();
+    const int jj = tid & 31, ib = tid >> 5;       // 8 row groups x 32 columns, 4 rows each
+    if (j0 + jj >= n) return;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const int i = ib * 4 + q;
+        if (i0 + i >= n) break;
+        double v = a[(long long)(i0 + i) * n + j0 + jj];
+        for (int kk = 0; kk < nb; kk++) v -= Ls[i][kk] * Us[kk][jj];
+        a[(long long)(i0 + i) * n + j0 + jj] = v;
+    }
+}
+
+// lubksb.  Forward: column sweep in blocks of 32 (per row the terms are subtracted for j ascending).
+// Back: the reference subtracts a_ij*x_j for j ascending from i+1, so row i cannot start before
+// x_{i+1} exists: a chain of n^2/2 dependent subtractions.  One thread runs the chain on products
+// that the rest of the CTA prepares one row ahead (every x_j with j > i+1 is already known).
+#define LU_ST 256
+__global__ void __launch_bounds__(LU_ST)
+k_lu_subst(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, const double *__restrict__ mat,
+           const int *__restrict__ indxs, double *__restrict__ sol)
+{
+    extern __shared__ __align__(16) unsigned char dyn[];
+    const int r = blockIdx.x;
+    if (!fit[r].active || fit[r].singular) return;
+    const int n = D->sz.mat_size, tid = threadIdx.x;
+    const double *a = mat + (long long)r * n * n;
+    double *bg = sol + (long long)r * (D->sz.n_comp_total + 1) + 1;
+    const int *indx = indxs + (long long)r * n;
+    double *b = (double *)dyn;                    // [n]
+    double *prod = b + n;                         // [2][n]
+    __shared__ double Lb[32][33];
+    for (int i = tid; i < n; i += LU_ST) b[i] = bg[i];
+    __syncthreads();
     if (tid == 0)
         for (int i = 0; i < n; i++) { int ip = indx[i]; double t = b[ip]; b[ip] = b[i]; b[i] = t; }
     __syncthreads();
-    for (int j = 0; j < n - 1; j++) {
-        const double bj = b[j];
-        for (int i = j + 1 + tid; i < n; i += LU_NT) b[i] -= a[(long long)i * n + j] * bj;
+    for (int j0 = 0; j0 < n; j0 += 32) {
+        const int w = min(32, n - j0);
+        for (int e = tid; e < w * w; e += LU_ST) { int i = e / w, c = e - i * w; Lb[i][c] = a[(long long)(j0 + i) * n + j0 + c]; }
+        __syncthreads();
+        if (tid < 32)                              // the diagonal block, one warp in lock step
+            for (int c = 0; c < w - 1; c++) {
+                const double bj = b[j0 + c];
+                if (tid > c && tid < w) b[j0 + tid] -= Lb[tid][c] * bj;
+                __syncwarp();
+            }
+        __syncthreads();
+        for (int i = j0 + w + tid; i < n; i += LU_ST) {
+            const double *row = a + (long long)i * n + j0;
+            double v = b[i];
+            for (int c = 0; c < w; c++) v -= row[c] * b[j0 + c];
+            b[i] = v;
+        }
         __syncthreads();
     }
-    if (tid == 0)
-        for (int i = n - 1; i >= 0; i--) {
-            double sum = b[i];
+    // back substitution
+    for (int i = n - 1; i >= 0; i--) {
+        double *p = prod + (size_t)(i & 1) * n;    // products of row i for j >= i+2, prepared during row i+1
+        if (i == n - 1) { /* nothing to subtract */ }
+        if (tid == 0) {
             const double *row = a + (long long)i * n;
-            for (int j = i + 1; j < n; j++) sum -= row[j] * b[j];
+            double sum = b[i];
+            if (i + 1 < n) sum -= row[i + 1] * b[i + 1];
+            for (int j = i + 2; j < n; j++) sum -= p[j];
             b[i] = sum / row[i];
+        } else if (i >= 1) {
+            // prepare row i-1: products with x_j, j >= i+1 (all known while thread 0 works on row i)
+            const double *rown = a + (long long)(i - 1) * n;
+            double *pn = prod + (size_t)((i - 1) & 1) * n;
+            for (int j = i + 1 + (tid - 1); j < n; j += LU_ST - 1) pn[j] = rown[j] * b[j];
         }
+        __syncthreads();
+    }
+    for (int i = tid; i < n; i += LU_ST) bg[i] = b[i];
 }
 
 // ------------------------------------------------------------ model and clipping
@@ -525,7 +659,29 @@ int zb_launch_fit_iteration(zb_ctx *ctx, const float *conv_img, const float *ref
     k_wxy<<<(ctx->n_slots + 127) / 128, 128, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->n_slots, ctx->d_wxy);
     dim3 gb((n + 1 + 15) / 16, (n + 15) / 16, nR);
     k_build_matrix<<<gb, dim3(16, 16), 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_rhs, ctx->d_wxy, ctx->d_mat, ctx->d_sol);
-    k_lu_solve<<<nR, LU_NT, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_sol, ctx->d_vv, ctx->d_indx);
+    {
+        k_lu_init<<<dim3((n + 127) / 128, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv);
+        const size_t smp = ((size_t)n * (LU_NB + 1) + n) * sizeof(double);
+        if (smp > 220 * 1024) { snprintf(ctx->err, sizeof ctx->err, "normal matrix of %d rows too large for the LU panel kernel", n); return ZB_ERR_UNSUPPORTED; }
+        cudaFuncSetAttribute(k_lu_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smp);
+        for (int k0 = 0; k0 < n; k0 += LU_NB) {
+            const int nb = n - k0 < LU_NB ? n - k0 : LU_NB, rest = n - k0 - nb;
+            k_lu_panel<<<nR, LU_PT, ((size_t)(n - k0) * (LU_NB + 1) + (n - k0)) * sizeof(double), st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv, ctx->d_indx, k0);
+            ctx->launches++;
+            if (n - nb > 0) {
+                k_lu_swap_u<<<dim3((n - nb + 127) / 128, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, k0);
+                ctx->launches++;
+            }
+            if (rest > 0) {
+                k_lu_trail<<<dim3((rest + 31) / 32, (rest + 31) / 32, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, k0);
+                ctx->launches++;
+            }
+        }
+        const size_t sms = (size_t)3 * n * sizeof(double);
+        cudaFuncSetAttribute(k_lu_subst, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sms);
+        k_lu_subst<<<nR, LU_ST, sms, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, ctx->d_sol);
+        ctx->launches++;
+    }
     size_t sm = (size_t)npix * (sizeof(double) + 1) + (size_t)sz.n_comp_ker * sizeof(double) + 16;
     cudaFuncSetAttribute(k_stamp_sig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     k_stamp_sig<<<ctx->n_slots, 256, sm, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_vec, ctx->d_kref, ctx->d_sol,

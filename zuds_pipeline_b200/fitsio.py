@@ -54,7 +54,14 @@ class Header:
         return Header(self.cards)
 
 
+class Raw(str):
+    """A pre-formatted numeric value field (written right-justified, unquoted), for cards whose
+    number format is dictated by the reference (cfitsio's %G / %E key writers)."""
+
+
 def _fmt_value(v):
+    if isinstance(v, Raw):
+        return "%20s" % str(v)
     if isinstance(v, (bool, np.bool_)):
         return "%20s" % ("T" if v else "F")
     if isinstance(v, (int, np.integer)):
