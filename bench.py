@@ -23,7 +23,6 @@ from __future__ import annotations
 import argparse
 import json
 import os
-import queue
 import statistics
 import subprocess
 import sys
@@ -100,55 +99,6 @@ class ClockSampler:
                     reasons.add(n)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": sorted(reasons), "samples": len(sm)}
-
-
-# --------------------------------------------------------------------------- worker pool
-
-class Pool:
-    """`n` host threads, each owning one zb_ctx (one stream + workspace) on the same GPU.  ctypes
-    releases the GIL inside the C call, so the contexts overlap on the device."""
-
-    def __init__(self, device, n):
-        from zuds_pipeline_b200 import _lib
-        self.ctxs = [_lib.Context(device) for _ in range(n)]
-        self.q = queue.Queue()
-        self.done = queue.Queue()
-        self.threads = [threading.Thread(target=self._run, args=(c,), daemon=True) for c in self.ctxs]
-        for t in self.threads:
-            t.start()
-
-    def _run(self, ctx):
-        while True:
-            job = self.q.get()
-            if job is None:
-                return
-            try:
-                self.done.put((job[0], job[1](ctx), ctx.timings().get("k_convolve", 0.0)))
-            except Exception as e:       # surface worker failures in the main thread
-                self.done.put((job[0], e, 0.0))
-
-    def run_batch(self, fns):
-        for i, fn in enumerate(fns):
-            self.q.put((i, fn))
-        out, conv_ms = [None] * len(fns), []
-        for _ in fns:
-            i, r, ms = self.done.get()
-            if isinstance(r, Exception):
-                raise r
-            out[i] = r
-            conv_ms.append(ms)
-        return out, conv_ms
-
-    def launches(self):
-        return sum(c.launch_count() for c in self.ctxs)
-
-    def close(self):
-        for _ in self.threads:
-            self.q.put(None)
-        for t in self.threads:
-            t.join()
-        for c in self.ctxs:
-            c.close()
 
 
 # --------------------------------------------------------------------------- CPU side
@@ -279,7 +229,8 @@ def bench_b200(args):
     torch.cuda.synchronize()
 
     W, B = args.workers, args.batch
-    pool = Pool(local, W)
+    from zuds_pipeline_b200.batch import GpuPool
+    pool = GpuPool(local, W)
     dev_out = [(torch.empty((ny, nx), dtype=torch.float32, device="cuda"), torch.empty((ny, nx), dtype=torch.float32, device="cuda"),
                 torch.empty((ny, nx), dtype=torch.int32, device="cuda")) for _ in range(W)]
     pin_out = [(torch.empty((ny, nx), dtype=torch.float32).pin_memory(), torch.empty((ny, nx), dtype=torch.float32).pin_memory(),
@@ -299,7 +250,8 @@ def bench_b200(args):
         return fn
 
     def step(make_job):
-        return pool.run_batch([make_job(i % npairs_distinct) for i in range(B)])
+        res, tim = pool.run([make_job(i % npairs_distinct) for i in range(B)])
+        return res, [t.get("k_convolve", 0.0) for t in tim]
 
     # ---- device-resident throughput ("value")
     for _ in range(args.warmup):

@@ -217,10 +217,13 @@ _ctx_cache = {}
 
 
 def _context(device):
+    """One zb_ctx per (device, host thread): a ctx serves one thread at a time (include/zb200.h)."""
+    import threading
     from . import _lib
-    if device not in _ctx_cache:
-        _ctx_cache[device] = _lib.Context(device)
-    return _ctx_cache[device]
+    key = (device, threading.get_ident())
+    if key not in _ctx_cache:
+        _ctx_cache[key] = _lib.Context(device)
+    return _ctx_cache[key]
 
 
 def _read_float(path):
