@@ -346,7 +346,7 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
     P.o_invgain = ct ? iinv : tinv; P.o_quad = ct ? iq : tq;
 
     dim3 gk((nbx_max * nby_max + 1 + MK_NB - 1) / MK_NB + 1, nR);
-    k_make_kernels<<<gk, 256, 0, st>>>(ctx->d_dev, ctx->d_sol, ctx->d_kvec, ctx->d_kern, ctx->d_kstat, nbx_max, nby_max);
+    k_make_kernels<<<gk, 256, 0, st>>>(ctx->d_dev, ctx->d_sol, ctx->d_kvec, ctx->d_kern, ctx->d_kstat, nbx_max, nby_max); ZB_DBG("k_make_kernels");
 
     const int ncg = (B + TX - 1) / TX;
     int tpb = ((B * ncg + 31) / 32) * 32;
@@ -356,14 +356,14 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
     int W = NB * B + fw - 1 + (fwp - fw) + TX; while ((W & 7) != 1) W++;
     const int TH = B + fw - 1;
     size_t smem = (size_t)TH * W * sizeof(double2) + (size_t)NB * fw * fwp * sizeof(double2) + (size_t)TH * W;
-    if (smem > 220 * 1024) { snprintf(ctx->err, sizeof ctx->err, "convolution tile needs %zu bytes of shared memory", smem); return ZB_ERR_UNSUPPORTED; }
-    cudaFuncSetAttribute(k_convolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > ZB_SMEM_OPTIN) { snprintf(ctx->err, sizeof ctx->err, "convolution tile needs %zu bytes of shared memory", smem); return ZB_ERR_UNSUPPORTED; }
+    cudaFuncSetAttribute(k_convolve, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
     dim3 gc((nbx_max + NB - 1) / NB, nby_max, nR);
     cudaEventRecord(ctx->ev[10], st);          // k_convolve alone: the kernel bench.py's roofline is quoted on
     k_convolve<<<gc, NB * tpb, smem, st>>>(ctx->d_dev, P, ctx->d_sol, ctx->d_kern, ctx->d_kstat, nbx_max, nby_max, NB, tpb,
-                                           ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask);
+                                           ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask); ZB_DBG("k_convolve");
     cudaEventRecord(ctx->ev[11], st);
-    k_region_frame<<<dim3(64, nR), 256, 0, st>>>(ctx->d_dev, P, ctx->d_sol, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask);
+    k_region_frame<<<dim3(64, nR), 256, 0, st>>>(ctx->d_dev, P, ctx->d_sol, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask); ZB_DBG("k_region_frame");
     ctx->launches += 3;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "convolution kernels", __FILE__, __LINE__);

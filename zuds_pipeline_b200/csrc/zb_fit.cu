@@ -94,10 +94,17 @@ k_fill_post(const ZbDev *__restrict__ D, const float *__restrict__ refimg, const
     }
 }
 
-// Gram matrix of the stamp's vectors, lower triangle: G[i(i+1)/2+j] = sum_k v_i[k] v_j[k], k ascending.
+// Gram matrix of the stamp's vectors, lower triangle: G[i(i+1)/2+j] = sum_k v_i[k] v_j[k], k ascending
+// (alard.c:405-431 sums the pixels in storage order).  One CTA per stamp; a thread owns a 4x4 tile of
+// (i, j) pairs and keeps its 16 running sums in registers; products and sums are separate roundings
+// (-fmad=false) so each G element sees exactly the reference's operation sequence.  Chunks of GRAM_KC
+// pixels of all vectors are staged in shared memory, the next chunk is prefetched into registers
+// while the current one is consumed.
 #define GRAM_KC 32
-#define GRAM_ITEMS 6
-__global__ void __launch_bounds__(256)
+#define GRAM_T 4
+#define GRAM_NT 128
+#define GRAM_PF 16            // prefetch registers per thread: GRAM_NT*GRAM_PF >= GRAM_KC*nvec_pad (nvec <= 64)
+__global__ void __launch_bounds__(GRAM_NT)
 k_gram(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const int *__restrict__ jobs,
        const double *__restrict__ vec, double *__restrict__ gram)
 {
@@ -106,50 +113,83 @@ k_gram(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const in
     const ZbStamp &S = stamps[slot];
     if (S.sscnt >= S.nss) return;
     const int fwss = D->sz.fw_ksstamp, npix = fwss * fwss;
-    const int nvec = D->sz.n_comp_ker + D->sz.n_bg_vectors, npair = nvec * (nvec + 1) / 2;
+    const int nvec = D->sz.n_comp_ker + D->sz.n_bg_vectors;
+    const int nt4 = (nvec + GRAM_T - 1) / GRAM_T, ld = nt4 * GRAM_T;       // padded vector count
+    const int ntile = nt4 * (nt4 + 1) / 2;
     const double *v = vec + (long long)slot * nvec * npix;
-    double *g = gram + (long long)slot * npair;
-    double *s = (double *)dyn;                         // [GRAM_KC][nvec]
-    const int tid = threadIdx.x, nt = blockDim.x;
-    for (int base = 0; base < npair; base += nt * GRAM_ITEMS) {
-        int ii[GRAM_ITEMS], jj[GRAM_ITEMS]; double acc[GRAM_ITEMS];
+    double *g = gram + (long long)slot * (nvec * (nvec + 1) / 2);
+    double *s = (double *)dyn;                         // [GRAM_KC][ld]
+    const int tid = threadIdx.x;
+    for (int tbase = 0; tbase < ntile; tbase += GRAM_NT) {
+        const int tile = tbase + tid;
+        int ti = -1, tj = 0;
+        if (tile < ntile) {
+            ti = (int)((sqrt(8.0 * tile + 1.0) - 1.0) * 0.5);
+            while (ti * (ti + 1) / 2 > tile) ti--;
+            while ((ti + 1) * (ti + 2) / 2 <= tile) ti++;
+            tj = tile - ti * (ti + 1) / 2;
+        }
+        double acc[GRAM_T][GRAM_T];
 #pragma unroll
-        for (int q = 0; q < GRAM_ITEMS; q++) {
-            int e = base + q * nt + tid;
-            acc[q] = 0.0; ii[q] = -1; jj[q] = 0;
-            if (e < npair) {
-                int i = (int)((sqrt(8.0 * e + 1.0) - 1.0) * 0.5);
-                while (i * (i + 1) / 2 > e) i--;
-                while ((i + 1) * (i + 2) / 2 <= e) i++;
-                ii[q] = i; jj[q] = e - i * (i + 1) / 2;
-            }
+        for (int a = 0; a < GRAM_T; a++)
+#pragma unroll
+            for (int c = 0; c < GRAM_T; c++) acc[a][c] = 0.0;
+        double pf[GRAM_PF];
+        const int nelem = GRAM_KC * ld;
+        // prefetch chunk 0
+#pragma unroll
+        for (int q = 0; q < GRAM_PF; q++) {
+            int e = q * GRAM_NT + tid; pf[q] = 0.0;
+            if (e < nelem) { int n = e / GRAM_KC, kk = e - n * GRAM_KC; if (n < nvec && kk < npix) pf[q] = v[(long long)n * npix + kk]; }
         }
         for (int k0 = 0; k0 < npix; k0 += GRAM_KC) {
-            int kc = min(GRAM_KC, npix - k0);
-            __syncthreads();
-            for (int idx = tid; idx < nvec * GRAM_KC; idx += nt) {
-                int n = idx / GRAM_KC, kk = idx - n * GRAM_KC;
-                s[kk * nvec + n] = (kk < kc) ? v[(long long)n * npix + k0 + kk] : 0.0;
-            }
             __syncthreads();
 #pragma unroll
-            for (int q = 0; q < GRAM_ITEMS; q++) {
-                if (ii[q] < 0) continue;
-                double a = acc[q];
-                for (int kk = 0; kk < kc; kk++) a += s[kk * nvec + ii[q]] * s[kk * nvec + jj[q]];
-                acc[q] = a;
+            for (int q = 0; q < GRAM_PF; q++) {
+                int e = q * GRAM_NT + tid;
+                if (e < nelem) { int n = e / GRAM_KC, kk = e - n * GRAM_KC; s[kk * ld + n] = pf[q]; }
+            }
+            __syncthreads();
+            const int k1 = k0 + GRAM_KC;
+            if (k1 < npix) {
+#pragma unroll
+                for (int q = 0; q < GRAM_PF; q++) {
+                    int e = q * GRAM_NT + tid; pf[q] = 0.0;
+                    if (e < nelem) { int n = e / GRAM_KC, kk = e - n * GRAM_KC; if (n < nvec && k1 + kk < npix) pf[q] = v[(long long)n * npix + k1 + kk]; }
+                }
+            }
+            if (ti >= 0) {
+                const int kc = min(GRAM_KC, npix - k0);
+                for (int kk = 0; kk < kc; kk++) {
+                    const double2 a01 = *(const double2 *)&s[kk * ld + ti * GRAM_T], a23 = *(const double2 *)&s[kk * ld + ti * GRAM_T + 2];
+                    const double2 b01 = *(const double2 *)&s[kk * ld + tj * GRAM_T], b23 = *(const double2 *)&s[kk * ld + tj * GRAM_T + 2];
+                    const double av[4] = {a01.x, a01.y, a23.x, a23.y}, bv[4] = {b01.x, b01.y, b23.x, b23.y};
+#pragma unroll
+                    for (int a = 0; a < GRAM_T; a++)
+#pragma unroll
+                        for (int c = 0; c < GRAM_T; c++) acc[a][c] += av[a] * bv[c];
+                }
             }
         }
+        if (ti >= 0) {
 #pragma unroll
-        for (int q = 0; q < GRAM_ITEMS; q++) {
-            int e = base + q * nt + tid;
-            if (e < npair) g[e] = acc[q];
+            for (int a = 0; a < GRAM_T; a++)
+#pragma unroll
+                for (int c = 0; c < GRAM_T; c++) {
+                    const int i = ti * GRAM_T + a, j = tj * GRAM_T + c;
+                    if (i < nvec && j <= i) g[i * (i + 1) / 2 + j] = acc[a][c];
+                }
         }
     }
 }
 
-// rhs[i] = sum over the sub-stamp of v_i * imRef, x outer / y inner (alard.c:459-466)
-__global__ void __launch_bounds__(128)
+// rhs[i] = sum over the sub-stamp of v_i * imRef with x outer / y inner (alard.c:459-466): one chain of
+// fwss^2 dependent additions per vector.  A warp owns one vector: all lanes fetch 4 columns at a time
+// (32-byte segments of every row), form the products and park them in shared memory in chain order;
+// lane 0 then adds them in that order while the warp already fetches the next columns.
+#define RHS_WARPS 8
+#define RHS_COLS 4
+__global__ void __launch_bounds__(RHS_WARPS * 32)
 k_rhs(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const int *__restrict__ jobs,
       const double *__restrict__ vec, const double *__restrict__ kref, double *__restrict__ rhs)
 {
@@ -159,18 +199,44 @@ k_rhs(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const int
     if (S.sscnt >= S.nss) return;
     const int fwss = D->sz.fw_ksstamp, npix = fwss * fwss;
     const int nvec = D->sz.n_comp_ker + D->sz.n_bg_vectors;
-    double *kr = (double *)dyn;
+    const int chunk = RHS_COLS * fwss;
+    double *kr = (double *)dyn;                          // [npix], row-major like kref
+    double *bufs = kr + npix;                            // [RHS_WARPS][2][chunk]
     const double *krg = kref + (long long)slot * npix;
     for (int k = threadIdx.x; k < npix; k += blockDim.x) kr[k] = krg[k];
     __syncthreads();
-    for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
-        const double *v = vec + ((long long)slot * nvec + i) * npix;
-        double p0 = 0.0;
-        for (int xc = 0; xc < fwss; xc++)
-            for (int yc = 0; yc < fwss; yc++)
-                p0 += v[xc + fwss * yc] * kr[xc + fwss * yc];   // kref holds the float pixel exactly
-        rhs[(long long)slot * nvec + i] = p0;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int i = blockIdx.y * RHS_WARPS + warp;
+    if (i >= nvec) return;
+    const double *v = vec + ((long long)slot * nvec + i) * npix;
+    double *buf = bufs + (size_t)warp * 2 * chunk;
+    const int per = (chunk + 31) / 32;                   // elements per lane per chunk (<= 8 for fwss <= 63)
+    double pr[8];
+    // element e of a chunk starting at column x0: row yc = e / RHS_COLS, column x0 + e % RHS_COLS
+#define RHS_FETCH(x0) \
+    _Pragma("unroll") for (int q = 0; q < 8; q++) { \
+        int e = q * 32 + lane; pr[q] = 0.0; \
+        if (q < per && e < chunk) { int yc = e / RHS_COLS, xc = (x0) + (e - yc * RHS_COLS); \
+            if (xc < fwss) pr[q] = v[xc + fwss * yc] * kr[xc + fwss * yc]; } }
+    RHS_FETCH(0)
+    double p0 = 0.0;
+    int par = 0;
+    for (int x0 = 0; x0 < fwss; x0 += RHS_COLS, par ^= 1) {
+        double *b = buf + par * chunk;
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            int e = q * 32 + lane;
+            if (q < per && e < chunk) { int yc = e / RHS_COLS, dx = e - yc * RHS_COLS; b[dx * fwss + yc] = pr[q]; }   // chain order
+        }
+        __syncwarp();
+        if (x0 + RHS_COLS < fwss) { RHS_FETCH(x0 + RHS_COLS) }
+        if (lane == 0) {
+            const int cnt = min(RHS_COLS, fwss - x0) * fwss;
+            for (int t = 0; t < cnt; t++) p0 += b[t];
+        }
     }
+#undef RHS_FETCH
+    if (lane == 0) rhs[(long long)slot * nvec + i] = p0;
 }
 
 int zb_launch_fill(zb_ctx *ctx, const float *conv_img, const float *ref_img, const int *d_jobs, int n_jobs, cudaStream_t st)
@@ -180,19 +246,24 @@ int zb_launch_fill(zb_ctx *ctx, const float *conv_img, const float *ref_img, con
     const int fw = sz.fw_kernel, fwss = sz.fw_ksstamp, sw = fwss + fw - 1, npix = fwss * fwss;
     const int nvec = sz.n_comp_ker + sz.n_bg_vectors;
     size_t sm1 = 2 * fw * sizeof(double) + ((size_t)sw * sw + (size_t)sw * fwss) * sizeof(float);
-    size_t sm3 = (size_t)GRAM_KC * nvec * sizeof(double);
-    size_t sm4 = (size_t)npix * sizeof(double);
-    if (sm1 > 200 * 1024 || sm3 > 200 * 1024 || sm4 > 200 * 1024) {
+    const int ldv = ((nvec + GRAM_T - 1) / GRAM_T) * GRAM_T;
+    size_t sm3 = (size_t)GRAM_KC * ldv * sizeof(double);
+    size_t sm4 = ((size_t)npix + (size_t)RHS_WARPS * 2 * RHS_COLS * fwss) * sizeof(double);
+    if (GRAM_KC * ldv > GRAM_NT * GRAM_PF || RHS_COLS * fwss > 256) {
+        snprintf(ctx->err, sizeof ctx->err, "%d basis vectors / sub-stamp width %d exceed the fit kernels' limits", nvec, fwss);
+        return ZB_ERR_UNSUPPORTED;
+    }
+    if (sm1 > ZB_SMEM_OPTIN || sm3 > ZB_SMEM_OPTIN || sm4 > ZB_SMEM_OPTIN) {
         snprintf(ctx->err, sizeof ctx->err, "sub-stamp of %d pixels too large for shared memory", fwss);
         return ZB_ERR_UNSUPPORTED;
     }
-    cudaFuncSetAttribute(k_fill_conv, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
-    cudaFuncSetAttribute(k_gram, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm3);
-    cudaFuncSetAttribute(k_rhs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm4);
-    k_fill_conv<<<dim3(n_jobs, sz.n_comp_ker), 256, sm1, st>>>(ctx->d_dev, conv_img, ctx->d_stamps, d_jobs, ctx->d_fx, ctx->d_fy, ctx->d_vec);
-    k_fill_post<<<n_jobs, 256, 0, st>>>(ctx->d_dev, ref_img, ctx->d_stamps, d_jobs, ctx->d_ren, ctx->d_vec, ctx->d_kref);
-    k_gram<<<n_jobs, 256, sm3, st>>>(ctx->d_dev, ctx->d_stamps, d_jobs, ctx->d_vec, ctx->d_gram);
-    k_rhs<<<n_jobs, 128, sm4, st>>>(ctx->d_dev, ctx->d_stamps, d_jobs, ctx->d_vec, ctx->d_kref, ctx->d_rhs);
+    cudaFuncSetAttribute(k_fill_conv, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
+    cudaFuncSetAttribute(k_gram, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
+    cudaFuncSetAttribute(k_rhs, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
+    k_fill_conv<<<dim3(n_jobs, sz.n_comp_ker), 256, sm1, st>>>(ctx->d_dev, conv_img, ctx->d_stamps, d_jobs, ctx->d_fx, ctx->d_fy, ctx->d_vec); ZB_DBG("k_fill_conv");
+    k_fill_post<<<n_jobs, 256, 0, st>>>(ctx->d_dev, ref_img, ctx->d_stamps, d_jobs, ctx->d_ren, ctx->d_vec, ctx->d_kref); ZB_DBG("k_fill_post");
+    k_gram<<<n_jobs, GRAM_NT, sm3, st>>>(ctx->d_dev, ctx->d_stamps, d_jobs, ctx->d_vec, ctx->d_gram); ZB_DBG("k_gram");
+    k_rhs<<<dim3(n_jobs, (nvec + RHS_WARPS - 1) / RHS_WARPS), RHS_WARPS * 32, sm4, st>>>(ctx->d_dev, ctx->d_stamps, d_jobs, ctx->d_vec, ctx->d_kref, ctx->d_rhs); ZB_DBG("k_rhs");
     ctx->launches += 4;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "fill kernels", __FILE__, __LINE__);
@@ -656,39 +727,39 @@ int zb_launch_fit_iteration(zb_ctx *ctx, const float *conv_img, const float *ref
     const zb_sizes &sz = ctx->sz;
     const int n = sz.mat_size, nR = sz.n_regions, npix = sz.fw_ksstamp * sz.fw_ksstamp;
     (void)conv_img; (void)ref_img;
-    k_wxy<<<(ctx->n_slots + 127) / 128, 128, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->n_slots, ctx->d_wxy);
+    k_wxy<<<(ctx->n_slots + 127) / 128, 128, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->n_slots, ctx->d_wxy); ZB_DBG("k_wxy");
     dim3 gb((n + 1 + 15) / 16, (n + 15) / 16, nR);
-    k_build_matrix<<<gb, dim3(16, 16), 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_rhs, ctx->d_wxy, ctx->d_mat, ctx->d_sol);
+    k_build_matrix<<<gb, dim3(16, 16), 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_rhs, ctx->d_wxy, ctx->d_mat, ctx->d_sol); ZB_DBG("k_build_matrix");
     {
-        k_lu_init<<<dim3((n + 127) / 128, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv);
+        k_lu_init<<<dim3((n + 127) / 128, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv); ZB_DBG("k_lu_init");
         const size_t smp = ((size_t)n * (LU_NB + 1) + n) * sizeof(double);
-        if (smp > 220 * 1024) { snprintf(ctx->err, sizeof ctx->err, "normal matrix of %d rows too large for the LU panel kernel", n); return ZB_ERR_UNSUPPORTED; }
-        cudaFuncSetAttribute(k_lu_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smp);
+        if (smp > ZB_SMEM_OPTIN) { snprintf(ctx->err, sizeof ctx->err, "normal matrix of %d rows too large for the LU panel kernel", n); return ZB_ERR_UNSUPPORTED; }
+        cudaFuncSetAttribute(k_lu_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
         for (int k0 = 0; k0 < n; k0 += LU_NB) {
             const int nb = n - k0 < LU_NB ? n - k0 : LU_NB, rest = n - k0 - nb;
-            k_lu_panel<<<nR, LU_PT, ((size_t)(n - k0) * (LU_NB + 1) + (n - k0)) * sizeof(double), st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv, ctx->d_indx, k0);
+            k_lu_panel<<<nR, LU_PT, ((size_t)(n - k0) * (LU_NB + 1) + (n - k0)) * sizeof(double), st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv, ctx->d_indx, k0); ZB_DBG("k_lu_panel");
             ctx->launches++;
             if (n - nb > 0) {
-                k_lu_swap_u<<<dim3((n - nb + 127) / 128, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, k0);
+                k_lu_swap_u<<<dim3((n - nb + 127) / 128, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, k0); ZB_DBG("k_lu_swap_u");
                 ctx->launches++;
             }
             if (rest > 0) {
-                k_lu_trail<<<dim3((rest + 31) / 32, (rest + 31) / 32, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, k0);
+                k_lu_trail<<<dim3((rest + 31) / 32, (rest + 31) / 32, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, k0); ZB_DBG("k_lu_trail");
                 ctx->launches++;
             }
         }
         const size_t sms = (size_t)3 * n * sizeof(double);
-        cudaFuncSetAttribute(k_lu_subst, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sms);
-        k_lu_subst<<<nR, LU_ST, sms, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, ctx->d_sol);
+        cudaFuncSetAttribute(k_lu_subst, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
+        k_lu_subst<<<nR, LU_ST, sms, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, ctx->d_sol); ZB_DBG("k_lu_subst");
         ctx->launches++;
     }
     size_t sm = (size_t)npix * (sizeof(double) + 1) + (size_t)sz.n_comp_ker * sizeof(double) + 16;
-    cudaFuncSetAttribute(k_stamp_sig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    cudaFuncSetAttribute(k_stamp_sig, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
     k_stamp_sig<<<ctx->n_slots, 256, sm, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_vec, ctx->d_kref, ctx->d_sol,
-                                                sci, ref, sci_rms, ref_rms, ctx->d_min);
+                                                sci, ref, sci_rms, ref_rms, ctx->d_min); ZB_DBG("k_stamp_sig");
     cudaMemsetAsync(ctx->d_njobs, 0, sizeof(int), st);
     k_clip<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, (float *)ctx->d_stats, (char *)(ctx->d_stats) + (size_t)nR * sz.n_stamps * sizeof(float),
-                                          ctx->d_jobs, ctx->d_njobs);
+                                          ctx->d_jobs, ctx->d_njobs); ZB_DBG("k_clip");
     ctx->launches += 5;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "fit iteration", __FILE__, __LINE__);

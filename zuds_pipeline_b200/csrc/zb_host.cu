@@ -19,6 +19,16 @@ int zb_cuda_fail(zb_ctx *ctx, cudaError_t e, const char *what, const char *file,
     return ZB_ERR_CUDA;
 }
 
+int zb_dbg_sync(zb_ctx *ctx, cudaStream_t st, const char *what) {
+    static int on = -1;
+    if (on < 0) { const char *e = getenv("ZB_DEBUG_SYNC"); on = (e && e[0] && e[0] != '0') ? 1 : 0; }
+    if (!on) return ZB_OK;
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) return zb_cuda_fail(ctx, e, what, __FILE__, __LINE__);
+    return ZB_OK;
+}
+
 // hotpants/vargs.c:55-128 + defaults.h:27-80
 extern "C" void zb_params_default(zb_params *p) {
     static const double sig[3] = {0.7, 1.5, 3.0};
@@ -222,7 +232,7 @@ extern "C" const char *zb_last_error(const zb_ctx *ctx) { return ctx ? ctx->err 
 extern "C" long long zb_launch_count(const zb_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
 static const char *k_stage_names[ZB_NSTAGES] = {"input_mask", "stamp_search", "stamp_resolve", "fill_stamps", "fit_loop",
-                                                "make_kernels+convolve", "final_sig", "region_stats", "readback", "k_convolve", "", ""};
+                                                "make_kernels+convolve", "final_sig", "region_stats", "readback", "k_convolve", "search_stats_kclk", "search_scan_kclk"};
 extern "C" const char *zb_stage_name(int i) { return (i >= 0 && i < ZB_NSTAGES) ? k_stage_names[i] : ""; }
 extern "C" int zb_last_timings(const zb_ctx *ctx, float *ms, int n) {
     if (!ctx || !ms) return ZB_ERR_PARAM;
@@ -274,7 +284,8 @@ static int configure(zb_ctx *ctx, const zb_params *p) {
         if (!tmp) return ZB_ERR_NOMEM;
         zb_host_ran1_stream(tmp, ctx->n_ran);
         DMALLOC(ctx->d_ran, (size_t)ctx->n_ran * sizeof(double));
-        cudaMemcpy(ctx->d_ran, tmp, (size_t)ctx->n_ran * sizeof(double), cudaMemcpyHostToDevice);
+        cudaMemcpyAsync(ctx->d_ran, tmp, (size_t)ctx->n_ran * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+        cudaStreamSynchronize(ctx->stream);
         free(tmp);
     }
     const int fw = sz.fw_kernel, nK = sz.n_comp_ker, nvec = nK + sz.n_bg_vectors, npix = sz.fw_ksstamp * sz.fw_ksstamp;
@@ -287,10 +298,11 @@ static int configure(zb_ctx *ctx, const zb_params *p) {
         DMALLOC(ctx->d_fx, (size_t)nK * fw * sizeof(double));
         DMALLOC(ctx->d_fy, (size_t)nK * fw * sizeof(double));
         DMALLOC(ctx->d_ren, (size_t)nK * sizeof(int));
-        cudaMemcpy(ctx->d_kvec, kv, (size_t)nK * fw * fw * sizeof(double), cudaMemcpyHostToDevice);
-        cudaMemcpy(ctx->d_fx, fx, (size_t)nK * fw * sizeof(double), cudaMemcpyHostToDevice);
-        cudaMemcpy(ctx->d_fy, fy, (size_t)nK * fw * sizeof(double), cudaMemcpyHostToDevice);
-        cudaMemcpy(ctx->d_ren, ren, (size_t)nK * sizeof(int), cudaMemcpyHostToDevice);
+        cudaMemcpyAsync(ctx->d_kvec, kv, (size_t)nK * fw * fw * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+        cudaMemcpyAsync(ctx->d_fx, fx, (size_t)nK * fw * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+        cudaMemcpyAsync(ctx->d_fy, fy, (size_t)nK * fw * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+        cudaMemcpyAsync(ctx->d_ren, ren, (size_t)nK * sizeof(int), cudaMemcpyHostToDevice, ctx->stream);
+        cudaStreamSynchronize(ctx->stream);
         free(kv); free(fx); free(fy); free(ren);
     }
     ctx->n_cells = sz.n_regions * sz.n_stamps;
@@ -315,11 +327,12 @@ static int configure(zb_ctx *ctx, const zb_params *p) {
     DMALLOC(ctx->d_kstat, (size_t)sz.n_regions * 4 * sizeof(double));
     const size_t stat_bytes = (size_t)sz.n_regions * ((size_t)sz.n_comp_total + 512) * sizeof(double) + ns * 8;
     DMALLOC(ctx->d_stats, stat_bytes);   HMALLOC(ctx->h_stats, stat_bytes);
-    cudaMemset(ctx->d_stats, 0, stat_bytes);
+    cudaMemsetAsync(ctx->d_stats, 0, stat_bytes, ctx->stream);
     DMALLOC(ctx->d_qa, (size_t)sz.n_regions * 4 * sizeof(ZbQaStat));
     DMALLOC(ctx->d_qpart, (size_t)sz.n_regions * 5 * ZB_QA_NBLK * sizeof(ZbQaPart));
-    cudaMemcpy(ctx->d_dev, H, sizeof(ZbDev), cudaMemcpyHostToDevice);
-    cudaError_t e = cudaGetLastError();
+    cudaMemcpyAsync(ctx->d_dev, H, sizeof(ZbDev), cudaMemcpyHostToDevice, ctx->stream);
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) { free_workspace(ctx); return zb_cuda_fail(ctx, e, "configure", __FILE__, __LINE__); }
     ctx->configured = 1;
     return ZB_OK;
@@ -397,6 +410,7 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
     const float *conv_img = ct ? ref : sci, *ref_img = ct ? sci : ref;
     ctx->err[0] = 0;
     memset(ctx->ms, 0, sizeof ctx->ms);
+    float cell_kclk[2] = {0, 0};
 
     // ---- stage 0: input masks
     STAGE(0);
@@ -410,6 +424,11 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
     CHECK_RC(zb_launch_stamp_search(ctx, conv_img, 0, ctx->n_cells, st));
     cudaMemcpyAsync(ctx->h_cells, ctx->d_cells, (size_t)ctx->n_cells * sizeof(ZbCell), cudaMemcpyDeviceToHost, st);
     SYNC("stamp search");
+    {   // diagnostics: mean SM kilo-cycles per grid cell in the two halves of k_stamp_search
+        double a = 0, b = 0;
+        for (int c = 0; c < ctx->n_cells; c++) { a += ctx->h_cells[c].clk_stats; b += ctx->h_cells[c].clk_search; }
+        cell_kclk[0] = (float)(a / ctx->n_cells / 1e3); cell_kclk[1] = (float)(b / ctx->n_cells / 1e3);
+    }
 
     // ---- stage 2: compaction, stale-slot fix-ups, one retry at a lower threshold (main.c:909-998)
     STAGE(2);
@@ -519,6 +538,7 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
     SYNC("final read-back");
     for (int i = 0; i < 9; i++) cudaEventElapsedTime(&ctx->ms[i], ctx->ev[i], ctx->ev[i + 1]);
     if (njobs > 0) cudaEventElapsedTime(&ctx->ms[9], ctx->ev[10], ctx->ev[11]);
+    ctx->ms[10] = cell_kclk[0]; ctx->ms[11] = cell_kclk[1];
     for (int r = 0; r < nR; r++) {
         zb_region_info *ri = &regions[r];
         const ZbFit &F = ctx->h_fit[r];

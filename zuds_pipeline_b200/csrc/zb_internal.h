@@ -10,6 +10,9 @@
 
 #define ZB_MAXVAL  1e10      // hotpants/defaults.h:24
 #define ZB_ZEROVAL 1e-10     // hotpants/defaults.h:25
+// Dynamic shared memory opt-in, the SAME constant for every kernel and every launch: contexts on
+// other host threads set it concurrently, and a per-launch value would race with their launches.
+#define ZB_SMEM_OPTIN (216 * 1024)
 #define ZB_MAX_REGIONS 64
 #define ZB_MAX_BASIS   160   // nCompKer + nBGVectors upper bound handled by the fit kernels
 #define ZB_MAX_COMP    32    // (ko+1)(ko+2)/2 upper bound (ko <= 6)
@@ -42,6 +45,7 @@ struct ZbCell {
     int sx0, sy0, spx, spy;      // stamp origin (region coords) and size
     float kft;                   // kerFitThresh in force (may be halved on retry)
     int  stat_status;            // getStampStats3 return code
+    int  clk_stats, clk_search;  // SM clock cycles spent in the two halves of k_stamp_search (diagnostics)
     int  nss;
     int  xss[ZB_MAX_KSS], yss[ZB_MAX_KSS];    // region coords
     double in_mode, in_fwhm;     // slot contents before this cell ran (stale-slot quirk)
@@ -76,7 +80,9 @@ struct ZbQaStat {
     int phase;                   // 0 sigma-clip passes, 1 histogram passes, 2 done
     int status;                  // getStampStats3 return code
     int maxiter, umask, smask, use_noise;
-    int ncrit, cnt_prev, tries, imax, npts_s, pad;
+    int ncrit, cnt_prev, tries, imax, npts_s, ticket;
+    int exact, pad;                // exact: keep the double clip test (degenerate mean / sd)
+    float clo, chi, llo, lhi;      // accepted float interval: all criteria so far / the last criterion
     double crit_mean[8], crit_istd[8];
     double mean, sd, bin1, binsize, samp_med;
     double sum, median, mode, fwhm, lfwhm;
@@ -127,6 +133,9 @@ struct zb_ctx {
 };
 
 int zb_cuda_fail(zb_ctx *ctx, cudaError_t e, const char *what, const char *file, int line);
+// ZB_DEBUG_SYNC=1 in the environment: synchronise after every kernel so a fault names its kernel
+int zb_dbg_sync(zb_ctx *ctx, cudaStream_t st, const char *what);
+#define ZB_DBG(what) do { int rc_d = zb_dbg_sync(ctx, st, what); if (rc_d != ZB_OK) return rc_d; } while (0)
 
 // kernel launchers (each returns a zb_status)
 int zb_launch_input_mask(zb_ctx *ctx, const float *sci, const float *ref, const void *smask, int sdt,

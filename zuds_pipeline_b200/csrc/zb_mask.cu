@@ -85,17 +85,17 @@ int zb_launch_input_mask(zb_ctx *ctx, const float *sci, const float *ref, const 
 {
     const zb_sizes &sz = ctx->sz;
     dim3 g1((sz.max_rpix_x + 255) / 256, sz.max_rpix_y, sz.n_regions);
-    k_input_mask<<<g1, 256, 0, st>>>(ctx->d_dev, sci, ref, smask, sdt, tmask, tdt, ctx->d_min);
+    k_input_mask<<<g1, 256, 0, st>>>(ctx->d_dev, sci, ref, smask, sdt, tmask, tdt, ctx->d_min); ZB_DBG("k_input_mask");
     ctx->launches++;
     int width = (int)(ctx->p.hw_kernel * ctx->p.kf_spread_mask1);
     int w2 = width > 0 ? width / 2 : 0;
     int tw = TILE + 2 * w2;
     size_t smem = (size_t)tw * tw + (size_t)tw * TILE;
-    if (smem > 200 * 1024) { snprintf(ctx->err, sizeof ctx->err, "spread width %d too large", width); return ZB_ERR_UNSUPPORTED; }
-    if (smem > 48 * 1024) cudaFuncSetAttribute(k_spread_mask, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > ZB_SMEM_OPTIN) { snprintf(ctx->err, sizeof ctx->err, "spread width %d too large", width); return ZB_ERR_UNSUPPORTED; }
+    if (smem > 48 * 1024) cudaFuncSetAttribute(k_spread_mask, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
     dim3 g2((sz.max_rpix_x + TILE - 1) / TILE, (sz.max_rpix_y + TILE - 1) / TILE, sz.n_regions);
     // width <= 0: spreadMask returns at once (functions.c:1362-1364) but the frame is still drawn
-    k_spread_mask<<<g2, dim3(TILE, 8), smem, st>>>(ctx->d_dev, ctx->d_min, width > 0 ? w2 : 0, sz.s_border);
+    k_spread_mask<<<g2, dim3(TILE, 8), smem, st>>>(ctx->d_dev, ctx->d_min, width > 0 ? w2 : 0, sz.s_border); ZB_DBG("k_spread_mask");
     ctx->launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "input mask kernels", __FILE__, __LINE__);

@@ -14,6 +14,8 @@
 #include "zb_hist.cuh"
 
 #define NT 256
+#define ZB_NFAIL 96          // remembered failed sub-stamp centres per grid cell (more are simply re-checked)
+#define NW (NT / 32)     // candidates evaluated concurrently by the sub-stamp search
 
 struct RedBuf { double a[NT / 32]; double b[NT / 32]; int c[NT / 32]; double ra, rb; int rc; };
 
@@ -43,7 +45,7 @@ __device__ static inline bool excluded(int mdat, double rdat, int umask, int sma
 
 struct Shared {
     RedBuf rb;
-    double work[100];
+    double work[100], work2[100];
     int bins[256];
     double mean, sd, binsize, bin1, mode, median, fwhm, lfwhm, sum;
     int status, npts_s, cont, imax;
@@ -51,8 +53,10 @@ struct Shared {
     int cand, pcnt, brk;
     int xloc[2 * ZB_MAX_KSS], yloc[2 * ZB_MAX_KSS];
     double peaks[2 * ZB_MAX_KSS];
-    unsigned long long best;
-    int anybad;
+    int cands[NW], ncand;
+    int c_ok[NW], c_x[NW], c_y[NW], c_new[NW];
+    int failed[ZB_NFAIL], nfail;
+    double c_sum[NW];
 };
 
 // getStampStats3 on the shared-memory stamp.  Returns the reference's status code; fields of
@@ -65,26 +69,44 @@ __device__ static int stats3_block(Shared &S, const float *pix, int *msk, unsign
     const int tid = threadIdx.x;
     const int npix = nPixX * nPixY;
     if (npix < 100) return 4;
-    if (tid == 0) {
-        int i, goodcnt = 0, r = 0;
-        for (i = 0; i < 100; i++) S.work[i] = 0.0;
-        for (i = 0; (i < 100) && (goodcnt < npix) && (r + 1 < n_ran); i++, goodcnt++) {
-            int xr = (int)floor(ran[r++] * nPixX);
-            int yr = (int)floor(ran[r++] * nPixY);
-            double rdat = pix[xr + yr * nPixX];
-            int mdat = msk[xr + yr * nPixX];
-            if (excluded(mdat, rdat, umask, smask)) i--;
-            else S.work[i] = rdat;
+    // the first 100 accepted random samples, in attempt order (functions.c:811-833): attempt a uses
+    // ran[2a], ran[2a+1]; acceptance does not depend on earlier attempts, so they are tested NT at a time
+    if (tid < 100) { S.work[tid] = 0.0; S.work2[tid] = 0.0; }
+    if (tid == 0) S.npts_s = 0;
+    __syncthreads();
+    for (int base = 0; base < npix; base += NT) {
+        const int a = base + tid;
+        int flag = 0; double rdat = 0;
+        if (a < npix && 2 * a + 1 < n_ran) {
+            int xr = (int)floor(ran[2 * a] * nPixX), yr = (int)floor(ran[2 * a + 1] * nPixY);
+            rdat = pix[xr + yr * nPixX];
+            flag = !excluded(msk[xr + yr * nPixX], rdat, umask, smask);
         }
-        int n = i;
-        for (int a = 1; a < n; a++) {            // ascending sort of the n samples
-            double v = S.work[a]; int b = a - 1;
-            while (b >= 0 && S.work[b] > v) { S.work[b + 1] = S.work[b]; b--; }
-            S.work[b + 1] = v;
+        const unsigned bal = __ballot_sync(0xffffffffu, flag);
+        if ((tid & 31) == 0) S.rb.c[tid >> 5] = __popc(bal);
+        __syncthreads();
+        int before = S.npts_s;
+        for (int w = 0; w < (tid >> 5); w++) before += S.rb.c[w];
+        const int pos = before + __popc(bal & ((1u << (tid & 31)) - 1u));
+        if (flag && pos < 100) S.work2[pos] = rdat;
+        __syncthreads();
+        if (tid == 0) { int t = 0; for (int w = 0; w < NT / 32; w++) t += S.rb.c[w]; S.npts_s += t; }
+        __syncthreads();
+        if (S.npts_s >= 100) break;
+    }
+    {
+        const int n = S.npts_s < 100 ? S.npts_s : 100;
+        if (tid < n) {                               // rank sort (ascending; equal values keep any order)
+            const double v = S.work2[tid]; int rank = 0;
+            for (int q = 0; q < n; q++) { double u = S.work2[q]; rank += (u < v) || (u == v && q < tid); }
+            S.work[rank] = v;
         }
-        S.npts_s = n;
-        S.binsize = (S.work[(int)(0.9f * n)] - S.work[(int)(0.5f * n)]) / (float)100;
-        S.bin1 = S.work[(int)(0.5f * n)] - 128. * S.binsize;
+        __syncthreads();
+        if (tid == 0) {
+            S.npts_s = n;
+            S.binsize = (S.work[(int)(0.9f * n)] - S.work[(int)(0.5f * n)]) / (float)100;
+            S.bin1 = S.work[(int)(0.5f * n)] - 128. * S.binsize;
+        }
     }
     // valid pixels (NaN/Inf pixels get 0x88, functions.c:857-861)
     int cnt_local = 0;
@@ -207,6 +229,7 @@ k_stamp_search(const ZbDev *__restrict__ D, const float *__restrict__ img, int32
     float *pix = (float *)dyn;
     int *msk = (int *)(pix + npix);
     unsigned char *state = (unsigned char *)(msk + npix);
+    unsigned *cbm = (unsigned *)(state + ((npix + 15) & ~15));      // candidate bitmap of the current pass
     int32_t *gm = m_in + R.off;
 
     for (int k = tid; k < npix; k += NT) {
@@ -219,6 +242,7 @@ k_stamp_search(const ZbDev *__restrict__ D, const float *__restrict__ img, int32
         S.median = C.median; S.lfwhm = C.lfwhm; S.sum = C.sum;
     }
     __syncthreads();
+    const long long t_begin = clock64();
     int status = stats3_block(S, pix, msk, state, xLen, yLen, 0x0, 0xffff, 3, D->p.stat_sig, ran, n_ran,
                               gm, C.sx0, C.sy0, R.rpx);
     __syncthreads();
@@ -233,84 +257,139 @@ k_stamp_search(const ZbDev *__restrict__ D, const float *__restrict__ img, int32
     const float skyf = (float)sky, invdskyf = (float)invdsky;     // checkPsfCenter takes them as floats
     const double floor_ = sky + kft * S.fwhm;
     float dfrac = 0.9f;
-    if (tid == 0) { S.pcnt = 0; S.brk = 0; }
+    // Raster-greedy search, NW candidates at a time.  A candidate that fails changes nothing, so the
+    // next NW candidates (in raster order, against the current mask) are evaluated concurrently, one
+    // warp each; the first one that succeeds claims its box, the ones after it are re-evaluated.
+    const int bw = 2 * hwss + 1, nbox = bw * bw;
+    const int nwords = (npix + 31) >> 5;
+    const int warp = tid >> 5, lane = tid & 31;
+    // per-pixel tests that do not depend on the mask, evaluated once with the reference's expressions
+    // (functions.c:574-581 and checkPsfCenter :476-490): bit0 usable for centring (below hiThresh and
+    // >= kerFitThresh sigma in double), bit1 counted by checkPsfCenter (float sky / 1/fwhm), bit2 >= hiThresh
+    unsigned char *fl = state;
+    for (int k = tid; k < npix; k += NT) {
+        const double dpt = pix[k];
+        unsigned char f = 0;
+        const bool hi = dpt >= hiThresh;
+        if (!hi && !(((dpt - sky) * invdsky) < kft)) f |= 1;
+        if (((dpt - skyf) * invdskyf) > kft) f |= 2;
+        if (hi) f |= 4;
+        fl[k] = f;
+    }
+    if (tid == 0) { S.pcnt = 0; S.nfail = 0; }
+    const long long t_search0 = clock64();
     __syncthreads();
     for (;;) {
         if (S.pcnt >= fcnt) break;
         double loPsf = sky + (hiThresh - sky) * dfrac;
         loPsf = (loPsf > floor_) ? loPsf : floor_;
         int start = 0;
+        bool rebuild = true;
         for (;;) {
-            // first raster index >= start that is a candidate
-            if (tid == 0) S.cand = npix;
-            __syncthreads();
-            int mine = npix;
-            for (int k = start + tid; k < npix; k += NT) {
-                if (msk[k] & bbit) continue;
-                double dpt = pix[k];
-                if (dpt >= hiThresh) continue;
-                if (((dpt - sky) * invdsky) < kft) continue;
-                if (dpt > loPsf) { mine = k; break; }
-            }
-            if (mine < npix) atomicMin(&S.cand, mine);
-            __syncthreads();
-            const int cand = S.cand;
-            if (cand >= npix) break;
-            const int j = cand / xLen, i = cand - j * xLen;
-            // centre on the peak flux in the +-hwss box (first pixel in raster order that holds the maximum)
-            if (tid == 0) S.best = 0ull;
-            __syncthreads();
-            {
-                const int bw = 2 * hwss + 1;
-                unsigned long long best = 0ull;
-                for (int q = tid; q < bw * bw; q += NT) {
-                    int l = j - hwss + q / bw, k = i - hwss + q % bw;
-                    if (l < 0 || l >= yLen || k < 0 || k >= xLen) continue;
-                    int n2 = k + l * xLen;
-                    if (msk[n2] & bbit) continue;
-                    double dpt2 = pix[n2];
-                    if (dpt2 >= hiThresh) continue;
-                    if (((dpt2 - sky) * invdsky) < kft) continue;
-                    if (dpt2 > (double)pix[cand]) {
-                        // order-preserving key: larger value first, then smaller raster index
-                        unsigned int fb = __float_as_uint(pix[n2]);
-                        fb = (fb & 0x80000000u) ? ~fb : (fb | 0x80000000u);
-                        unsigned long long key = ((unsigned long long)fb << 32) | (unsigned int)(0x7fffffff - n2);
-                        if (key > best) best = key;
+            if (rebuild) {
+                for (int base = 0; base < npix; base += NT) {           // one ballot = one 32-pixel word
+                    const int k = base + tid;
+                    int c = 0;
+                    if (k < npix && !(msk[k] & bbit)) {
+                        const double dpt = pix[k];
+                        c = (dpt < hiThresh) && !(((dpt - sky) * invdsky) < kft) && (dpt > loPsf);
                     }
+                    const unsigned bits = __ballot_sync(0xffffffffu, c);
+                    if (lane == 0 && (k >> 5) < nwords) cbm[k >> 5] = bits;
                 }
-                if (best) atomicMax(&S.best, best);
+                rebuild = false;
+                __syncthreads();
+            }
+            // warp 0 lists the next NW candidates at or after `start`
+            if (warp == 0) {
+                int found = 0;
+                for (int w0 = start >> 5; w0 < nwords && found < NW; w0 += 32) {
+                    const int w = w0 + lane;
+                    unsigned bits = w < nwords ? cbm[w] : 0u;
+                    if (w == (start >> 5)) bits &= ~0u << (start & 31);
+                    int c = __popc(bits), inc = c;
+                    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+                    int ord = found + inc - c;                       // ordinal of this word's first candidate
+                    while (bits && ord < NW) { int bpos = __ffs(bits) - 1; S.cands[ord++] = (w << 5) + bpos; bits &= bits - 1; }
+                    found += __shfl_sync(0xffffffffu, inc, 31);
+                }
+                if (lane == 0) S.ncand = found < NW ? found : NW;
             }
             __syncthreads();
-            int imax = i, jmax = j;
-            if (S.best) { int n2 = 0x7fffffff - (int)(S.best & 0xffffffffu); jmax = n2 / xLen; imax = n2 - jmax * xLen; }
-            // checkPsfCenter: any masked / saturated pixel in the box (inside the stamp) kills the candidate
-            if (tid == 0) S.anybad = 0;
+            const int ncand = S.ncand;
+            if (ncand == 0) break;
+            if (warp < ncand) {
+                const int cand = S.cands[warp];
+                const int j = cand / xLen, i = cand - j * xLen;
+                const float cval = pix[cand];
+                const int l0 = max(j - hwss, 0), l1 = min(j + hwss, yLen - 1);
+                const int k0 = max(i - hwss, 0), k1 = min(i + hwss, xLen - 1);
+                // centre on the peak flux in the +-hwss box: first pixel in raster order holding the maximum
+                unsigned long long best = 0ull;
+                for (int l = l0; l <= l1; l++)
+                    for (int k = k0 + lane; k <= k1; k += 32) {
+                        const int n2 = k + l * xLen;
+                        if (!(fl[n2] & 1) || (msk[n2] & bbit)) continue;
+                        const float v2 = pix[n2];
+                        if (v2 > cval) {
+                            unsigned int fb = __float_as_uint(v2);
+                            fb = (fb & 0x80000000u) ? ~fb : (fb | 0x80000000u);
+                            unsigned long long key = ((unsigned long long)fb << 32) | (unsigned int)(0x7fffffff - n2);
+                            if (key > best) best = key;
+                        }
+                    }
+                for (int o = 16; o > 0; o >>= 1) { unsigned long long t = __shfl_xor_sync(0xffffffffu, best, o); if (t > best) best = t; }
+                int imax = i, jmax = j;
+                if (best) { int n2 = 0x7fffffff - (int)(best & 0xffffffffu); jmax = n2 / xLen; imax = n2 - jmax * xLen; }
+                // a centre that failed once fails again: pixel values are fixed and mask bits are only ever added
+                const int cpos = imax + jmax * xLen;
+                int known = 0;
+                for (int q = lane; q < S.nfail; q += 32) known |= (S.failed[q] == cpos);
+                known = __any_sync(0xffffffffu, known);
+                double dsum = 0; int bad = known;
+                if (!known) {
+                    // checkPsfCenter: any masked / saturated pixel of the box (inside the stamp) kills the candidate
+                    const int m0 = max(jmax - hwss, 0), m1 = min(jmax + hwss, yLen - 1);
+                    const int q0 = max(imax - hwss, 0), q1 = min(imax + hwss, xLen - 1);
+                    for (int l = m0; l <= m1 && !bad; l++)
+                        for (int k = q0 + lane; k <= q1; k += 32) {
+                            const int n2 = k + l * xLen;
+                            const unsigned char f = fl[n2];
+                            if ((msk[n2] & bbit) || (f & 4)) { bad = 1; break; }
+                            if (f & 2) dsum += (double)pix[n2];
+                        }
+                    bad = __any_sync(0xffffffffu, bad);
+                    for (int o = 16; o > 0; o >>= 1) dsum += __shfl_xor_sync(0xffffffffu, dsum, o);
+                }
+                if (lane == 0) { S.c_ok[warp] = (!bad && dsum != 0.); S.c_x[warp] = imax; S.c_y[warp] = jmax; S.c_sum[warp] = dsum;
+                                 S.c_new[warp] = !known; }
+            }
             __syncthreads();
-            double dsum = 0, z = 0; int bad = 0;
+            int hit = -1;
+            for (int w = 0; w < ncand; w++) if (S.c_ok[w]) { hit = w; break; }
+            if (tid == 0) {                                  // remember the centres that failed before the hit
+                const int lim = hit < 0 ? ncand : hit;
+                for (int w = 0; w < lim; w++)
+                    if (S.c_new[w] && S.nfail < ZB_NFAIL) {
+                        const int cpos = S.c_x[w] + S.c_y[w] * xLen; bool dup = false;
+                        for (int q = 0; q < S.nfail; q++) dup |= (S.failed[q] == cpos);
+                        if (!dup) S.failed[S.nfail++] = cpos;
+                    }
+            }
+            if (hit < 0) { start = S.cands[ncand - 1] + 1; __syncthreads(); continue; }
             {
-                const int bw = 2 * hwss + 1;
-                for (int q = tid; q < bw * bw; q += NT) {
-                    int l = jmax - hwss + q / bw, k = imax - hwss + q % bw;
-                    if (l < 0 || l >= yLen || k < 0 || k >= xLen) continue;
-                    int n2 = k + l * xLen;
-                    double dpt2 = pix[n2];
-                    if ((msk[n2] & bbit) || dpt2 >= hiThresh) { bad = 1; continue; }
-                    if (((dpt2 - skyf) * invdskyf) > kft) dsum += dpt2;
-                }
-            }
-            block_sum(S.rb, dsum, z, bad);
-            if (!bad && dsum != 0.) {
-                if (tid == 0) { S.xloc[S.pcnt] = imax; S.yloc[S.pcnt] = jmax; S.peaks[S.pcnt] = dsum; S.pcnt++; }
-                const int bw = 2 * hwss + 1;
-                for (int q = tid; q < bw * bw; q += NT) {
-                    int l = jmax - hwss + q / bw, k = imax - hwss + q % bw;
+                const int imax = S.c_x[hit], jmax = S.c_y[hit];
+                for (int q = tid; q < nbox; q += NT) {
+                    const int l = jmax - hwss + q / bw, k = imax - hwss + q % bw;
                     if ((k > 0) && (k < xLen) && (l > 0) && (l < yLen)) msk[k + l * xLen] |= bbit2;
                 }
+                start = S.cands[hit] + 1;
+                __syncthreads();
+                if (tid == 0) { S.xloc[S.pcnt] = imax; S.yloc[S.pcnt] = jmax; S.peaks[S.pcnt] = S.c_sum[hit]; S.pcnt++; }
+                rebuild = true;
+                __syncthreads();
+                if (S.pcnt >= fcnt) break;
             }
-            __syncthreads();
-            if (S.pcnt >= fcnt) break;
-            start = cand + 1;
         }
         if (S.pcnt >= fcnt) break;
         if (loPsf == floor_) break;
@@ -319,6 +398,7 @@ k_stamp_search(const ZbDev *__restrict__ D, const float *__restrict__ img, int32
     __syncthreads();
     if (tid == 0) {
         C.stat_status = status;
+        C.clk_stats = (int)(t_search0 - t_begin); C.clk_search = (int)(clock64() - t_search0);
         C.mean = S.mean; C.sd = S.sd; C.mode = S.mode; C.fwhm = S.fwhm; C.median = S.median; C.lfwhm = S.lfwhm; C.sum = S.sum;
         int pcnt = S.pcnt, nss = 0;
         if (pcnt > 0) {
@@ -338,13 +418,13 @@ int zb_launch_stamp_search(zb_ctx *ctx, const float *conv_img, int first_cell, i
 {
     if (n_cells <= 0) return ZB_OK;
     size_t npx = (size_t)ctx->sz.fw_stamp * ctx->sz.fw_stamp;
-    size_t smem = npx * (sizeof(float) + sizeof(int) + 1) + 16;
-    if (smem > 200 * 1024) {
+    size_t smem = npx * (sizeof(float) + sizeof(int) + 1) + 32 + ((npx + 31) / 32) * sizeof(unsigned);
+    if (smem > ZB_SMEM_OPTIN) {
         snprintf(ctx->err, sizeof ctx->err, "stamp of %d x %d pixels does not fit shared memory", ctx->sz.fw_stamp, ctx->sz.fw_stamp);
         return ZB_ERR_UNSUPPORTED;
     }
-    cudaFuncSetAttribute(k_stamp_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_stamp_search<<<n_cells, NT, smem, st>>>(ctx->d_dev, conv_img, ctx->d_min, ctx->d_cells, first_cell, ctx->d_ran, ctx->n_ran);
+    cudaFuncSetAttribute(k_stamp_search, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
+    k_stamp_search<<<n_cells, NT, smem, st>>>(ctx->d_dev, conv_img, ctx->d_min, ctx->d_cells, first_cell, ctx->d_ran, ctx->n_ran); ZB_DBG("k_stamp_search");
     ctx->launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "k_stamp_search", __FILE__, __LINE__);

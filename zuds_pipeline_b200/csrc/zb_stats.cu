@@ -90,12 +90,12 @@ int zb_launch_final_sig(zb_ctx *ctx, cudaStream_t st) {
     const int nR = sz.n_regions, npix = sz.fw_ksstamp * sz.fw_ksstamp;
     cudaMemsetAsync(ctx->d_stats, 0, (size_t)nR * 64 * sizeof(double), st);
     size_t sm = (size_t)npix * (sizeof(double) + 1) + 16;
-    cudaFuncSetAttribute(k_final_sig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    k_final_sig<<<ctx->n_slots, 256, sm, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask);
+    cudaFuncSetAttribute(k_final_sig, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
+    k_final_sig<<<ctx->n_slots, 256, sm, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask); ZB_DBG("k_final_sig");
     // scratch for the clip lives behind the 64 result doubles of every region
     float *ss = (float *)(ctx->d_stats + (size_t)nR * 64);
     char *rej = (char *)(ss + (size_t)nR * sz.n_stamps);
-    k_final_clip<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ss, rej, ctx->d_stats);
+    k_final_clip<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ss, rej, ctx->d_stats); ZB_DBG("k_final_clip");
     ctx->launches += 2;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "final sig kernels", __FILE__, __LINE__);
@@ -165,13 +165,15 @@ k_qa_sample(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const 
         Q.binsize = (work[(int)(0.9f * n)] - work[(int)(0.5f * n)]) / (float)100;
         Q.bin1 = work[(int)(0.5f * n)] - 128. * Q.binsize;
         Q.phase = 0; Q.status = 0; Q.maxiter = 5; Q.umask = um; Q.smask = sm; Q.use_noise = s & 1;
-        Q.ncrit = 0; Q.cnt_prev = 0; Q.tries = 0; Q.imax = 0;
+        Q.ncrit = 0; Q.cnt_prev = 0; Q.tries = 0; Q.imax = 0; Q.ticket = 0; Q.exact = 0;
+        Q.clo = Q.llo = -3.402823466e38f; Q.chi = Q.lhi = 3.402823466e38f;
         Q.mean = Q.sd = Q.mode = Q.median = Q.fwhm = Q.lfwhm = Q.sum = 0;
     }
 }
 
 struct QaShared {
-    int phase[4], ncrit[4];
+    int phase[4], ncrit[4], exact[4];
+    float flo[4], fhi[4];
     double cm[4][8], ci[4][8], mean[4], isd[4], bin1[4], binsize[4];
     int bins[4][256];
     double ra[8], rb[8]; int rc[8];
@@ -192,20 +194,101 @@ __device__ static void qa_block_sum(QaShared &S, double &a, double &b, int &c) {
     a = sa; b = sb; c = sc;
 }
 
+// ---- float intervals for the clip test --------------------------------------------------------
+// The reference rejects a pixel when (fabs((double)x - mean) * istd) > statSig.  For finite mean and
+// finite positive istd that predicate is monotone in x on either side of the mean, so the accepted
+// floats form one interval [lo, hi]; its end points are found by bisection over the float ordering
+// with the reference's own double expression, and the per-pixel test becomes two float compares
+// with identical outcomes.
+__device__ static inline int qa_f2o(float f) { int i = __float_as_int(f); return i >= 0 ? i : (int)0x80000000 - i; }
+__device__ static inline float qa_o2f(int o) { return __int_as_float(o >= 0 ? o : (int)0x80000000 - o); }
+__device__ static inline bool qa_keep(float x, double mean, double istd, float sig) { return !((fabs((double)x - mean) * istd) > sig); }
+
+__device__ static bool qa_interval(double mean, double istd, float sig, float &lo, float &hi)
+{
+    if (!(istd > 0.) || istd * 0.0 != 0.0 || mean * 0.0 != 0.0 || !(fabs(mean) < 1e38)) return false;   // caller keeps the double test
+    const float c = (float)mean;
+    if (!qa_keep(c, mean, istd, sig)) { lo = 1.f; hi = -1.f; return true; }       // nothing passes
+    int a = qa_f2o(c), b = qa_f2o(3.402823466e38f);
+    if (qa_keep(qa_o2f(b), mean, istd, sig)) a = b;
+    while (b - a > 1) { int m = a + (b - a) / 2; if (qa_keep(qa_o2f(m), mean, istd, sig)) a = m; else b = m; }
+    hi = qa_o2f(a);
+    a = qa_f2o(c); b = qa_f2o(-3.402823466e38f);
+    if (qa_keep(qa_o2f(b), mean, istd, sig)) a = b;
+    while (a - b > 1) { int m = b + (a - b) / 2; if (qa_keep(qa_o2f(m), mean, istd, sig)) a = m; else b = m; }
+    lo = qa_o2f(a);
+    return true;
+}
+
+// The sequential decisions of sigma_clip (functions.c:1037-1107) and of the re-binning loop
+// (functions.c:879-1031) for one (region, stat); s == 4 finishes getNoiseStats3 on the first pass.
+// Runs in the last CTA of a pass to finish (see k_qa_pass).
+__device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *part, double *q, int r, int s, int first, const int *bins)
+{
+    const volatile ZbQaPart *P = part + (r * 5 + s) * ZB_QA_NBLK;
+    double s1 = 0, s2 = 0; long long n = 0;
+    if (s == 4) {
+        if (!first) return;
+        for (int b = 0; b < ZB_QA_NBLK; b++) { s1 += P[b].s1; n += P[b].n; }
+        q[(long long)r * 64 + 3] = (double)n;
+        q[(long long)r * 64 + 2] = (n > 1) ? s1 / (float)n : ZB_MAXVAL;
+        return;
+    }
+    ZbQaStat &Q = qa[r * 4 + s];
+    if (Q.phase == 2) return;
+    for (int b = 0; b < ZB_QA_NBLK; b++) { s1 += P[b].s1; s2 += P[b].s2; n += P[b].n; }
+    const int ncnt = (int)n;
+    const float sig = D->p.stat_sig;
+    if (Q.phase == 0) {
+        const int k = Q.ncrit;                          // passes done so far == iterations started
+        if (k == 0 && ncnt == 0) { Q.mean = 0; Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
+        if (ncnt != Q.cnt_prev && k < Q.maxiter) {
+            Q.cnt_prev = ncnt;
+            if (ncnt > 0) Q.mean = s1 / ncnt;
+            else { Q.mean = 0; Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
+            if (ncnt > 1) { double sd = s2 - ncnt * Q.mean * Q.mean; Q.sd = sqrt(sd / (double)(ncnt - 1)); }
+            else { Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
+            Q.crit_mean[k] = Q.mean; Q.crit_istd[k] = 1. / Q.sd; Q.ncrit = k + 1;
+            float lo, hi;
+            if (!Q.exact && qa_interval(Q.mean, 1. / Q.sd, sig, lo, hi)) {
+                Q.llo = lo; Q.lhi = hi;
+                Q.clo = fmaxf(Q.clo, lo); Q.chi = fminf(Q.chi, hi);
+            } else Q.exact = 1;
+            if (k + 1 >= Q.maxiter) Q.phase = 1;        // iter == maxiter ends the loop whatever the next count is
+        } else Q.phase = 1;
+        return;
+    }
+    // histogram phase: this pass filled the bins with the current bin1/binsize
+    const int goodcnt = ncnt;
+    if (goodcnt == 0) { Q.mode = Q.median = Q.samp_med; Q.fwhm = Q.lfwhm = 0.; Q.status = 2; Q.phase = 2; return; }
+    if (Q.binsize == 0.) { Q.mode = Q.median = Q.samp_med; Q.fwhm = Q.lfwhm = 0.; Q.status = 3; Q.phase = 2; return; }
+    HistOut o; int imax = Q.imax;
+    hist_analyse(bins, goodcnt, Q.bin1, Q.binsize, imax, o);
+    Q.imax = imax; Q.mode = o.mode;
+    if (o.action == 0) { Q.sum = s1; Q.fwhm = o.fwhm; Q.lfwhm = o.lfwhm; Q.median = o.median; Q.status = 0; Q.phase = 2; return; }
+    if (o.action == 1) { Q.bin1 = Q.bin1 - 128. * Q.binsize; Q.binsize = Q.binsize * 2.; }
+    else { Q.binsize = Q.binsize / 3.; Q.bin1 = o.mode - 128. * Q.binsize; }
+    Q.tries++;
+    for (int b = 0; b < 256; b++) Q.bins[b] = 0;
+    if (Q.tries >= 5) { Q.status = 1; Q.phase = 2; }
+}
+
 __global__ void __launch_bounds__(256)
 k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const float *__restrict__ rnoise,
-          int32_t *__restrict__ omask, int32_t *__restrict__ out_mask, ZbQaStat *__restrict__ qa,
-          ZbQaPart *__restrict__ part, int first)
+          int32_t *__restrict__ omask, int32_t *__restrict__ out_mask, ZbQaStat *qa,
+          ZbQaPart *part, double *__restrict__ q, int first)
 {
     __shared__ QaShared S;
+    __shared__ int s_last;
     const int r = blockIdx.y, tid = threadIdx.x;
     const ZbRegion R = D->reg[r];
     if (R.skip) return;
     if (tid < 4) {
         const ZbQaStat &Q = qa[r * 4 + tid];
-        S.phase[tid] = Q.phase; S.ncrit[tid] = Q.ncrit;
+        S.phase[tid] = Q.phase; S.ncrit[tid] = Q.ncrit; S.exact[tid] = Q.exact;
         for (int c = 0; c < 8; c++) { S.cm[tid][c] = Q.crit_mean[c]; S.ci[tid][c] = Q.crit_istd[c]; }
         S.mean[tid] = Q.mean; S.isd[tid] = 1. / Q.sd; S.bin1[tid] = Q.bin1; S.binsize[tid] = Q.binsize;
+        S.flo[tid] = Q.phase == 0 ? Q.clo : Q.llo; S.fhi[tid] = Q.phase == 0 ? Q.chi : Q.lhi;
     }
     for (int k = tid; k < 4 * 256; k += 256) (&S.bins[0][0])[k] = 0;
     __syncthreads();
@@ -219,7 +302,7 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
         const int m0 = omask[R.off + k];
         // NaN/Inf side effect of getStampStats3 (functions.c:857-861), in the order the runs happen
         int ms[4] = {m0, m0, m0, m0}, mn = m0;
-        const bool nfd = ((double)d * 0.0 != 0.0), nfn = ((double)nz * 0.0 != 0.0);
+        const bool nfd = (d * 0.0f != 0.0f), nfn = (nz * 0.0f != 0.0f);
         if (nfd || nfn) {
             const int mark = ZB_FLAG_INPUT_ISBAD | ZB_FLAG_ISNAN;
             int m = m0;
@@ -247,14 +330,18 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
             const float x = (s & 1) ? nz : d;
             int um, sm; qa_masks(s, um, sm);
             if (zb_excluded(ms[s], x, um, sm)) continue;
-            if ((double)x * 0.0 != 0.0) continue;
+            if (x * 0.0f != 0.0f) continue;
             if (S.phase[s] == 0) {
-                bool rej = false;
-                for (int c = 0; c < S.ncrit[s]; c++) rej |= (fabs(x - S.cm[s][c]) * S.ci[s][c]) > statSig;
-                if (rej) continue;
+                if (!S.exact[s]) { if (x < S.flo[s] || x > S.fhi[s]) continue; }
+                else {
+                    bool rej = false;
+                    for (int c = 0; c < S.ncrit[s]; c++) rej |= (fabs(x - S.cm[s][c]) * S.ci[s][c]) > statSig;
+                    if (rej) continue;
+                }
                 a1[s] += x; a2[s] += (double)(x * x); an[s]++;
             } else {
-                if ((fabs(x - S.mean[s]) * S.isd[s]) > statSig) continue;
+                if (!S.exact[s]) { if (x < S.flo[s] || x > S.fhi[s]) continue; }
+                else if ((fabs(x - S.mean[s]) * S.isd[s]) > statSig) continue;
                 int index = (int)(floor((x - S.bin1[s]) / S.binsize[s]) + 1);
                 index = (index < 0 ? 0 : index);
                 index = (index > 255 ? 255 : index);
@@ -278,55 +365,17 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
         qa_block_sum(S, nsum, z, nn);
         if (tid == 0) { ZbQaPart &P = part[(r * 5 + 4) * ZB_QA_NBLK + blockIdx.x]; P.s1 = nsum; P.s2 = 0; P.n = nn; }
     }
-}
-
-// The sequential decisions of sigma_clip (functions.c:1037-1107) and of the re-binning loop
-// (functions.c:879-1031) for one (region, stat); thread 4 finishes getNoiseStats3 on the first pass.
-__global__ void k_qa_decide(const ZbDev *__restrict__ D, ZbQaStat *__restrict__ qa, const ZbQaPart *__restrict__ part,
-                            double *__restrict__ q, int first)
-{
-    const int r = blockIdx.x, s = threadIdx.x;
-    if (D->reg[r].skip) return;
-    const ZbQaPart *P = part + (r * 5 + s) * ZB_QA_NBLK;
-    double s1 = 0, s2 = 0; long long n = 0;
-    if (s == 4) {
-        if (!first) return;
-        for (int b = 0; b < ZB_QA_NBLK; b++) { s1 += P[b].s1; n += P[b].n; }
-        q[(long long)r * 64 + 3] = (double)n;
-        q[(long long)r * 64 + 2] = (n > 1) ? s1 / (float)n : ZB_MAXVAL;
-        return;
-    }
-    ZbQaStat &Q = qa[r * 4 + s];
-    if (Q.phase == 2) return;
-    for (int b = 0; b < ZB_QA_NBLK; b++) { s1 += P[b].s1; s2 += P[b].s2; n += P[b].n; }
-    const int ncnt = (int)n;
-    if (Q.phase == 0) {
-        const int k = Q.ncrit;                          // passes done so far == iterations started
-        if (k == 0 && ncnt == 0) { Q.mean = 0; Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
-        if (ncnt != Q.cnt_prev && k < Q.maxiter) {
-            Q.cnt_prev = ncnt;
-            if (ncnt > 0) Q.mean = s1 / ncnt;
-            else { Q.mean = 0; Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
-            if (ncnt > 1) { double sd = s2 - ncnt * Q.mean * Q.mean; Q.sd = sqrt(sd / (double)(ncnt - 1)); }
-            else { Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
-            Q.crit_mean[k] = Q.mean; Q.crit_istd[k] = 1. / Q.sd; Q.ncrit = k + 1;
-            if (k + 1 >= Q.maxiter) Q.phase = 1;        // iter == maxiter ends the loop whatever the next count is
-        } else Q.phase = 1;
-        return;
-    }
-    // histogram phase: this pass filled Q.bins with the current bin1/binsize
-    const int goodcnt = ncnt;
-    if (goodcnt == 0) { Q.mode = Q.median = Q.samp_med; Q.fwhm = Q.lfwhm = 0.; Q.status = 2; Q.phase = 2; return; }
-    if (Q.binsize == 0.) { Q.mode = Q.median = Q.samp_med; Q.fwhm = Q.lfwhm = 0.; Q.status = 3; Q.phase = 2; return; }
-    HistOut o; int imax = Q.imax;
-    hist_analyse(Q.bins, goodcnt, Q.bin1, Q.binsize, imax, o);
-    Q.imax = imax; Q.mode = o.mode;
-    if (o.action == 0) { Q.sum = s1; Q.fwhm = o.fwhm; Q.lfwhm = o.lfwhm; Q.median = o.median; Q.status = 0; Q.phase = 2; return; }
-    if (o.action == 1) { Q.bin1 = Q.bin1 - 128. * Q.binsize; Q.binsize = Q.binsize * 2.; }
-    else { Q.binsize = Q.binsize / 3.; Q.bin1 = o.mode - 128. * Q.binsize; }
-    Q.tries++;
-    for (int b = 0; b < 256; b++) Q.bins[b] = 0;
-    if (Q.tries >= 5) { Q.status = 1; Q.phase = 2; }
+    // the last CTA of this region to get here takes the decisions for the next pass
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = (atomicAdd(&qa[r * 4].ticket, 1) == ZB_QA_NBLK - 1);
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    for (int k = tid; k < 4 * 256; k += 256) (&S.bins[0][0])[k] = __ldcg(&qa[r * 4 + (k >> 8)].bins[k & 255]);
+    __syncthreads();
+    if (tid < 5) qa_decide(D, qa, part, q, r, tid, first, tid < 4 ? S.bins[tid] : S.bins[0]);
+    if (tid == 0) qa[r * 4].ticket = 0;
 }
 
 __global__ void k_qa_finish(const ZbDev *__restrict__ D, const ZbQaStat *__restrict__ qa, double *__restrict__ q)
@@ -366,19 +415,18 @@ __global__ void k_rescale_ok(const ZbDev *__restrict__ D, const int32_t *__restr
 int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStream_t st)
 {
     const int nR = ctx->sz.n_regions;
-    k_qa_sample<<<dim3(4, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, ctx->d_qa, ctx->d_ran, ctx->n_ran);
+    k_qa_sample<<<dim3(4, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, ctx->d_qa, ctx->d_ran, ctx->n_ran); ZB_DBG("k_qa_sample");
     ctx->launches++;
     // at most maxiter (5) clip passes + 5 histogram passes; finished regions fall through at once
     for (int pass = 0; pass < 10; pass++) {
         k_qa_pass<<<dim3(ZB_QA_NBLK, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
-                                                        ctx->d_qa, ctx->d_qpart, pass == 0);
-        k_qa_decide<<<nR, 5, 0, st>>>(ctx->d_dev, ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0);
-        ctx->launches += 2;
+                                                        ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0); ZB_DBG("k_qa_pass");
+        ctx->launches++;
     }
-    k_qa_finish<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_qa, ctx->d_stats);
+    k_qa_finish<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_qa, ctx->d_stats); ZB_DBG("k_qa_finish");
     ctx->launches++;
     if (ctx->p.rescale_ok) {
-        k_rescale_ok<<<dim3(64, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_omask, ctx->d_stats, noise);
+        k_rescale_ok<<<dim3(64, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_omask, ctx->d_stats, noise); ZB_DBG("k_rescale_ok");
         ctx->launches++;
     }
     cudaError_t e = cudaGetLastError();
