@@ -258,16 +258,22 @@ def bench_b200(args):
         step(dev_job)
     barrier()
     clocks = ClockSampler(local)
-    clocks.start()
+    if not args.no_clocks:
+        clocks.start()
     l0 = pool.launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     conv_ms = []
     t0 = time.perf_counter()
+    step_ms = []
     for _ in range(args.steps):
+        ts = time.perf_counter()
         _, ms = step(dev_job)
+        step_ms.append(1e3 * (time.perf_counter() - ts))
         conv_ms += ms
     e1.record()
+    if args.verbose and rank == 0:
+        sys.stderr.write("device-resident step ms: %s\n" % " ".join("%.1f" % t for t in step_ms))
     barrier()
     wall = time.perf_counter() - t0
     dev_s = e0.elapsed_time(e1) / 1e3
@@ -352,6 +358,8 @@ def main():
     ap.add_argument("--batch", type=int, default=8, help="pair subtractions per step per GPU")
     ap.add_argument("--cpu-procs", type=int, default=0, help="reference arm: concurrent hotpants processes (0 = all cores)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-clocks", action="store_true", help="(diagnostics) do not sample clocks during the timed region")
+    ap.add_argument("--verbose", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         bench_reference(args)

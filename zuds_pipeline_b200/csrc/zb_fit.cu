@@ -369,11 +369,13 @@ k_lu_init(const ZbDev *__restrict__ D, ZbFit *__restrict__ fit, const double *__
 {
     const int r = blockIdx.y;
     if (!fit[r].active) return;
-    const int n = D->sz.mat_size, i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = D->sz.mat_size, i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (i >= n) return;
     const double *row = mat + (long long)r * n * n + (long long)i * n;
     double big = 0.0;
-    for (int j = 0; j < n; j++) { double t = fabs(row[j]); if (t > big) big = t; }
+    for (int j = lane; j < n; j += 32) { double t = fabs(row[j]); if (t > big) big = t; }
+    for (int o = 16; o > 0; o >>= 1) { double t = __shfl_xor_sync(0xffffffffu, big, o); if (t > big) big = t; }
+    if (lane) return;
     if (big == 0.) fit[r].singular = 1; else vvs[(long long)r * n + i] = 1.0 / big;
 }
 
@@ -384,13 +386,12 @@ k_lu_panel(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, double *_
     extern __shared__ __align__(16) unsigned char dyn[];
     const int r = blockIdx.x;
     if (!fit[r].active || fit[r].singular) return;
-    const int n = D->sz.mat_size, tid = threadIdx.x;
+    const int n = D->sz.mat_size, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nb = min(LU_NB, n - k0), m = n - k0, ld = LU_NB + 1;
     double *a = mat + (long long)r * n * n;
     double *P = (double *)dyn;                    // [m][ld]: rows k0.., columns k0..k0+nb-1
     double *vv = P + (size_t)m * ld;              // [m]
-    __shared__ double s_v[LU_PT / 32]; __shared__ int s_i[LU_PT / 32];
-    __shared__ int s_imax;
+    __shared__ double s_v[2][LU_PT / 32]; __shared__ int s_i[2][LU_PT / 32];
     for (int e = tid; e < m * nb; e += LU_PT) { int i = e / nb, c = e - i * nb; P[i * ld + c] = a[(long long)(k0 + i) * n + k0 + c]; }
     for (int i = tid; i < m; i += LU_PT) vv[i] = vvs[(long long)r * n + k0 + i];
     __syncthreads();
@@ -406,73 +407,95 @@ k_lu_panel(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, double *_
             int oi = __shfl_xor_sync(0xffffffffu, besti, o);
             if (ov > bestv || (ov == bestv && oi > besti)) { bestv = ov; besti = oi; }
         }
-        if ((tid & 31) == 0) { s_v[tid >> 5] = bestv; s_i[tid >> 5] = besti; }
+        const int par = kk & 1;                   // double-buffered partials: one barrier per reduction
+        if (lane == 0) { s_v[par][warp] = bestv; s_i[par][warp] = besti; }
         __syncthreads();
-        if (tid < 32) {
-            double bv = tid < LU_PT / 32 ? s_v[tid] : -1.0; int bi = tid < LU_PT / 32 ? s_i[tid] : -1;
-            for (int o = 16; o > 0; o >>= 1) {
-                double ov = __shfl_xor_sync(0xffffffffu, bv, o);
-                int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-                if (ov > bv || (ov == bv && oi > bi)) { bv = ov; bi = oi; }
-            }
-            if (tid == 0) s_imax = bi;
+        // every warp finishes the reduction for itself
+        double bv = lane < LU_PT / 32 ? s_v[par][lane] : -1.0; int bi = lane < LU_PT / 32 ? s_i[par][lane] : -1;
+        for (int o = 16; o > 0; o >>= 1) {
+            double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi > bi)) { bv = ov; bi = oi; }
         }
-        __syncthreads();
-        const int imax = s_imax;
+        const int imax = bi;
         if (imax != kk && tid < nb) { double t = P[imax * ld + tid]; P[imax * ld + tid] = P[kk * ld + tid]; P[kk * ld + tid] = t; }
-        if (tid == 0) {
+        if (tid == LU_PT - 1) {
             if (imax != kk) vv[imax] = vv[kk];
             indxs[(long long)r * n + k0 + kk] = k0 + imax;
         }
         __syncthreads();
-        if (tid == 0 && P[kk * ld + kk] == 0.0) P[kk * ld + kk] = 1.0e-20;
-        __syncthreads();
+        double piv = P[kk * ld + kk];
+        if (piv == 0.0) { piv = 1.0e-20; if (tid == 0) P[kk * ld + kk] = piv; }   // row kk is not read again as a row operand
         if (k0 + kk != n - 1) {
-            const double dum = 1.0 / P[kk * ld + kk];
-            // scale the column and update the rest of the panel row by row: thread -> (row, column)
-            const int w = nb - kk - 1;            // columns to the right inside the panel
-            for (int i = kk + 1 + tid; i < m; i += LU_PT) P[i * ld + kk] *= dum;
-            __syncthreads();
-            if (w > 0)
-                for (int e = tid; e < (m - kk - 1) * w; e += LU_PT) {
-                    int i = kk + 1 + e / w, c = kk + 1 + e % w;
-                    P[i * ld + c] -= P[i * ld + kk] * P[kk * ld + c];
-                }
-            __syncthreads();
+            const double dum = 1.0 / piv;
+            // a thread owns whole rows: scale l_ik, then update the rest of its panel row
+            for (int i = kk + 1 + tid; i < m; i += LU_PT) {
+                double *row = P + i * ld;
+                const double l = row[kk] * dum;
+                row[kk] = l;
+                for (int c = kk + 1; c < nb; c++) row[c] -= l * P[kk * ld + c];
+            }
         }
+        __syncthreads();
     }
     for (int e = tid; e < m * nb; e += LU_PT) { int i = e / nb, c = e - i * nb; a[(long long)(k0 + i) * n + k0 + c] = P[i * ld + c]; }
     for (int i = tid; i < m; i += LU_PT) vvs[(long long)r * n + k0 + i] = vv[i];
 }
 
-// One thread per column outside the panel: the panel's row swaps in order, then (right of the panel)
-// u_kj = a_kj - sum_{k'<k in panel} l_kk' u_k'j.
+// The panel's row interchanges on the columns outside it, then (right of the panel) the U12 solve
+// u_kj = a_kj - sum_{k'<k in panel} l_kk' u_k'j.  The LU_NB interchanges are composed into one
+// permutation of the <= 2*LU_NB rows involved, so a column's loads are all independent.
 __global__ void __launch_bounds__(128)
 k_lu_swap_u(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, double *__restrict__ mat,
             const int *__restrict__ indxs, int k0)
 {
     __shared__ double L[LU_NB][LU_NB + 1];
-    __shared__ int piv[LU_NB];
+    __shared__ int rows[2 * LU_NB], src[2 * LU_NB], s_nrow;
     const int r = blockIdx.y;
     if (!fit[r].active || fit[r].singular) return;
     const int n = D->sz.mat_size, nb = min(LU_NB, n - k0);
     double *a = mat + (long long)r * n * n;
     for (int e = threadIdx.x; e < nb * nb; e += blockDim.x) { int i = e / nb, c = e - i * nb; L[i][c] = a[(long long)(k0 + i) * n + k0 + c]; }
-    if (threadIdx.x < nb) piv[threadIdx.x] = indxs[(long long)r * n + k0 + threadIdx.x];
+    if (threadIdx.x == 0) {
+        // positions 0..nb-1 are the panel rows; pivots outside the panel are appended once each
+        int nrow = nb;
+        for (int q = 0; q < nb; q++) { rows[q] = k0 + q; src[q] = q; }
+        for (int kk = 0; kk < nb; kk++) {
+            const int ip = indxs[(long long)r * n + k0 + kk];
+            int pos = -1;
+            if (ip < k0 + nb) pos = ip - k0;
+            else { for (int q = nb; q < nrow; q++) if (rows[q] == ip) pos = q; if (pos < 0) { pos = nrow; rows[nrow] = ip; src[nrow] = nrow; nrow++; } }
+            const int t = src[pos]; src[pos] = src[kk]; src[kk] = t;      // after all swaps position p holds original row rows[src[p]]
+        }
+        s_nrow = nrow;
+    }
     __syncthreads();
     int j = blockIdx.x * blockDim.x + threadIdx.x;           // index among the n - nb outside columns
     if (j >= n - nb) return;
     if (j >= k0) j += nb;
-    for (int kk = 0; kk < nb; kk++) {
-        const int ip = piv[kk];
-        if (ip != k0 + kk) { double t = a[(long long)ip * n + j]; a[(long long)ip * n + j] = a[(long long)(k0 + kk) * n + j]; a[(long long)(k0 + kk) * n + j] = t; }
-    }
-    if (j < k0) return;
+    const int nrow = s_nrow;
+    double val[2 * LU_NB];
+#pragma unroll
+    for (int q = 0; q < 2 * LU_NB; q++) val[q] = q < nrow ? a[(long long)rows[q] * n + j] : 0.0;
+    // scatter through shared-free register shuffle: write position p <- val[src[p]] (dynamic index => local memory is fine here)
     double u[LU_NB];
+#pragma unroll
+    for (int q = 0; q < 2 * LU_NB; q++) {
+        if (q < nrow) {
+            const double x = val[src[q]];
+            if (q >= nb) a[(long long)rows[q] * n + j] = x;
+            else u[q] = x;
+        }
+    }
+    if (j < k0) {
+#pragma unroll
+        for (int kk = 0; kk < LU_NB; kk++) if (kk < nb) a[(long long)(k0 + kk) * n + j] = u[kk];
+        return;
+    }
 #pragma unroll
     for (int kk = 0; kk < LU_NB; kk++) {
         if (kk < nb) {
-            double sum = a[(long long)(k0 + kk) * n + j];
+            double sum = u[kk];
 #pragma unroll
             for (int q = 0; q < LU_NB; q++) if (q < kk) sum -= L[kk][q] * u[q];
             u[kk] = sum;
@@ -530,8 +553,13 @@ k_lu_subst(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, const dou
     const int *indx = indxs + (long long)r * n;
     double *b = (double *)dyn;                    // [n]
     double *prod = b + n;                         // [2][n]
+    double *dg = prod + 2 * n, *sd1 = dg + n;     // diagonal and first super-diagonal of U
     __shared__ double Lb[32][33];
-    for (int i = tid; i < n; i += LU_ST) b[i] = bg[i];
+    for (int i = tid; i < n; i += LU_ST) {
+        b[i] = bg[i];
+        dg[i] = a[(long long)i * n + i];
+        sd1[i] = i + 1 < n ? a[(long long)i * n + i + 1] : 0.0;
+    }
     __syncthreads();
     if (tid == 0)
         for (int i = 0; i < n; i++) { int ip = indx[i]; double t = b[ip]; b[ip] = b[i]; b[i] = t; }
@@ -560,11 +588,11 @@ k_lu_subst(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, const dou
         double *p = prod + (size_t)(i & 1) * n;    // products of row i for j >= i+2, prepared during row i+1
         if (i == n - 1) { /* nothing to subtract */ }
         if (tid == 0) {
-            const double *row = a + (long long)i * n;
             double sum = b[i];
-            if (i + 1 < n) sum -= row[i + 1] * b[i + 1];
+            if (i + 1 < n) sum -= sd1[i] * b[i + 1];
+#pragma unroll 8
             for (int j = i + 2; j < n; j++) sum -= p[j];
-            b[i] = sum / row[i];
+            b[i] = sum / dg[i];
         } else if (i >= 1) {
             // prepare row i-1: products with x_j, j >= i+1 (all known while thread 0 works on row i)
             const double *rown = a + (long long)(i - 1) * n;
@@ -590,6 +618,7 @@ __device__ static inline float approx_var(const ZbDev *D, const float *sci, cons
     return o + e;
 }
 
+#define SIG_PX 10
 __global__ void __launch_bounds__(256)
 k_stamp_sig(const ZbDev *__restrict__ D, ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
             const double *__restrict__ vec, const double *__restrict__ kref, const double *__restrict__ sols,
@@ -638,21 +667,37 @@ k_stamp_sig(const ZbDev *__restrict__ D, ZbStamp *__restrict__ stamps, const ZbF
     const double *v = vec + (long long)slot * nvec * npix;
     const double *kr = kref + (long long)slot * npix;
     int32_t *gm = m_in + R.off;
-    for (int k = threadIdx.x; k < npix; k += blockDim.x) {
-        float m = 0.0f;
-        for (int n = 0; n < nK; n++) m = (float)((double)m + coef[n] * v[(long long)n * npix + k]);   // model kept in float
-        int j = k / fwss, i = k - j * fwss;
-        int x2 = xR - hwss + i, y2 = yR - hwss + j;
-        double tdat = m, idat = kr[k];
-        double ndat = approx_var(D, sci, ref, sci_rms, ref_rms, (long long)(R.by0 + y2) * D->nx + (R.bx0 + x2));
-        double diff = tdat - idat + bg;
-        signed char f = 0;
-        if (!((gm[(long long)y2 * R.rpx + x2] & ZB_FLAG_INPUT_ISBAD) || (fabs(idat) <= ZB_ZEROVAL))) {
-            if ((tdat * 0.0 != 0.0) || (idat * 0.0 != 0.0))
-                atomicOr(&gm[(long long)y2 * R.rpx + x2], ZB_FLAG_INPUT_ISBAD | ZB_FLAG_ISNAN);
-            else { f = 1; term[k] = diff * diff / ndat; }
+    // make_model keeps its running model in the reference's FLOAT scratch (alard.c:1441-1459): the sum over
+    // the bases is rounded to float after every term.  SIG_PX pixels per thread advance together so the
+    // 49 dependent rounding steps of one pixel overlap with those of the others.
+    for (int kbase = 0; kbase < npix; kbase += 256 * SIG_PX) {
+        float m[SIG_PX];
+#pragma unroll
+        for (int q = 0; q < SIG_PX; q++) m[q] = 0.0f;
+        for (int n = 0; n < nK; n++) {
+            const double c = coef[n];
+            const double *vn = v + (long long)n * npix + kbase + threadIdx.x;
+#pragma unroll
+            for (int q = 0; q < SIG_PX; q++)
+                if (kbase + threadIdx.x + 256 * q < npix) m[q] = (float)((double)m[q] + c * vn[256 * q]);
         }
-        ok[k] = f;
+#pragma unroll
+        for (int q = 0; q < SIG_PX; q++) {
+            const int k = kbase + threadIdx.x + 256 * q;
+            if (k >= npix) continue;
+            int j = k / fwss, i = k - j * fwss;
+            int x2 = xR - hwss + i, y2 = yR - hwss + j;
+            double tdat = m[q], idat = kr[k];
+            double ndat = approx_var(D, sci, ref, sci_rms, ref_rms, (long long)(R.by0 + y2) * D->nx + (R.bx0 + x2));
+            double diff = tdat - idat + bg;
+            signed char f = 0;
+            if (!((gm[(long long)y2 * R.rpx + x2] & ZB_FLAG_INPUT_ISBAD) || (fabs(idat) <= ZB_ZEROVAL))) {
+                if ((tdat * 0.0 != 0.0) || (idat * 0.0 != 0.0))
+                    atomicOr(&gm[(long long)y2 * R.rpx + x2], ZB_FLAG_INPUT_ISBAD | ZB_FLAG_ISNAN);
+                else { f = 1; term[k] = diff * diff / ndat; }
+            }
+            ok[k] = f;
+        }
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -731,7 +776,7 @@ int zb_launch_fit_iteration(zb_ctx *ctx, const float *conv_img, const float *ref
     dim3 gb((n + 1 + 15) / 16, (n + 15) / 16, nR);
     k_build_matrix<<<gb, dim3(16, 16), 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_rhs, ctx->d_wxy, ctx->d_mat, ctx->d_sol); ZB_DBG("k_build_matrix");
     {
-        k_lu_init<<<dim3((n + 127) / 128, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv); ZB_DBG("k_lu_init");
+        k_lu_init<<<dim3((n + 3) / 4, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv); ZB_DBG("k_lu_init");
         const size_t smp = ((size_t)n * (LU_NB + 1) + n) * sizeof(double);
         if (smp > ZB_SMEM_OPTIN) { snprintf(ctx->err, sizeof ctx->err, "normal matrix of %d rows too large for the LU panel kernel", n); return ZB_ERR_UNSUPPORTED; }
         cudaFuncSetAttribute(k_lu_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
@@ -748,7 +793,7 @@ int zb_launch_fit_iteration(zb_ctx *ctx, const float *conv_img, const float *ref
                 ctx->launches++;
             }
         }
-        const size_t sms = (size_t)3 * n * sizeof(double);
+        const size_t sms = (size_t)5 * n * sizeof(double);
         cudaFuncSetAttribute(k_lu_subst, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
         k_lu_subst<<<nR, LU_ST, sms, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, ctx->d_sol); ZB_DBG("k_lu_subst");
         ctx->launches++;

@@ -245,11 +245,34 @@ extern "C" int zb_last_timings(const zb_ctx *ctx, float *ms, int n) {
 #define HMALLOC(ptr, bytes) do { if (cudaMallocHost((void **)&(ptr), (size_t)(bytes) ? (size_t)(bytes) : 16) != cudaSuccess) { \
     snprintf(ctx->err, sizeof ctx->err, "cudaMallocHost of %zu bytes failed (%s)", (size_t)(bytes), #ptr); free_workspace(ctx); return ZB_ERR_NOMEM; } } while (0)
 
-// (Re)build the workspace for a parameter set; cheap no-op when the parameters did not change.
+// The parameters that size the workspace or enter the precomputed tables (basis, region grid).
+// Everything else (thresholds, gains, clipping constants, directions) only travels in ZbDev.
+static bool same_geometry(const zb_params *a, const zb_params *b) {
+    if (a->nx != b->nx || a->ny != b->ny || a->hw_kernel != b->hw_kernel || a->hw_ksstamp != b->hw_ksstamp ||
+        a->n_ksstamps != b->n_ksstamps || a->ker_order != b->ker_order || a->bg_order != b->bg_order ||
+        a->nreg_x != b->nreg_x || a->nreg_y != b->nreg_y || a->nstamp_x != b->nstamp_x || a->nstamp_y != b->nstamp_y ||
+        a->kc_step != b->kc_step || a->ngauss != b->ngauss) return false;
+    for (int i = 0; i < a->ngauss && i < ZB_MAX_GAUSS; i++)
+        if (a->deg[i] != b->deg[i] || a->beta[i] != b->beta[i]) return false;
+    return true;
+}
+
+static void set_scalars(zb_ctx *ctx, const zb_params *p) {
+    ZbDev *H = ctx->h_dev;
+    ctx->p = *p;
+    H->p = *p;
+    H->conv_template = (p->force_convolve == 't');
+    H->tU = p->t_uthresh - p->t_pedestal; H->tUK = p->t_ukthresh - p->t_pedestal; H->tL = p->t_lthresh - p->t_pedestal;
+    H->iU = p->i_uthresh - p->i_pedestal; H->iUK = p->i_ukthresh - p->i_pedestal; H->iL = p->i_lthresh - p->i_pedestal;
+}
+
+// (Re)build the workspace for a parameter set.  Pairs of one survey share the geometry and differ
+// only in thresholds, so the usual call just refreshes the scalars.
 static int configure(zb_ctx *ctx, const zb_params *p) {
     if (ctx->configured && memcmp(&ctx->p, p, sizeof *p) == 0) return ZB_OK;
     int rc = zb_params_check(p, ctx->err, (int)sizeof ctx->err);
     if (rc != ZB_OK) return rc;
+    if (ctx->configured && same_geometry(&ctx->p, p)) { set_scalars(ctx, p); return ZB_OK; }
     cudaStreamSynchronize(ctx->stream);
     free_workspace(ctx);
     ctx->p = *p;
@@ -258,10 +281,8 @@ static int configure(zb_ctx *ctx, const zb_params *p) {
     HMALLOC(ctx->h_dev, sizeof(ZbDev));
     ZbDev *H = ctx->h_dev;
     memset(H, 0, sizeof *H);
-    H->p = *p; H->sz = sz; H->nx = p->nx; H->ny = p->ny; H->n_regions = sz.n_regions;
-    H->conv_template = (p->force_convolve == 't');
-    H->tU = p->t_uthresh - p->t_pedestal; H->tUK = p->t_ukthresh - p->t_pedestal; H->tL = p->t_lthresh - p->t_pedestal;
-    H->iU = p->i_uthresh - p->i_pedestal; H->iUK = p->i_ukthresh - p->i_pedestal; H->iL = p->i_lthresh - p->i_pedestal;
+    set_scalars(ctx, p);
+    H->sz = sz; H->nx = p->nx; H->ny = p->ny; H->n_regions = sz.n_regions;
     long long off = 0; int nR = 0;
     for (int j = 0; j < p->nreg_y; j++)
         for (int i = 0; i < p->nreg_x; i++, nR++) {
@@ -414,7 +435,8 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
 
     // ---- stage 0: input masks
     STAGE(0);
-    for (int r = 0; r < nR; r++) { H->reg[r].skip = 0; }
+    for (int r = 0; r < nR; r++) { H->reg[r].skip = 0; H->reg[r].own_x1 = H->reg[r].rx1; H->reg[r].own_y1 = H->reg[r].ry1; }
+    cudaMemcpyAsync(ctx->d_dev, H, sizeof(ZbDev), cudaMemcpyHostToDevice, st);     // scalars of THIS call
     CHECK_RC(zb_launch_input_mask(ctx, sci, ref, sci_mask, sci_mask_dtype, ref_mask, ref_mask_dtype, st));
 
     // ---- stage 1: stamp statistics + sub-stamp search, all grid cells of all regions at once

@@ -223,9 +223,9 @@ __device__ static bool qa_interval(double mean, double istd, float sig, float &l
 // The sequential decisions of sigma_clip (functions.c:1037-1107) and of the re-binning loop
 // (functions.c:879-1031) for one (region, stat); s == 4 finishes getNoiseStats3 on the first pass.
 // Runs in the last CTA of a pass to finish (see k_qa_pass).
-__device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *part, double *q, int r, int s, int first, const int *bins)
+__device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *part /* [5][ZB_QA_NBLK] */, double *q, int r, int s, int first, const int *bins)
 {
-    const volatile ZbQaPart *P = part + (r * 5 + s) * ZB_QA_NBLK;
+    const ZbQaPart *P = part + s * ZB_QA_NBLK;          // this region's partial sums, staged in shared memory
     double s1 = 0, s2 = 0; long long n = 0;
     if (s == 4) {
         if (!first) return;
@@ -297,13 +297,53 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
     const int npix = R.rpx * R.rpy;
     double a1[4] = {0, 0, 0, 0}, a2[4] = {0, 0, 0, 0}; int an[4] = {0, 0, 0, 0};
     double nsum = 0; int nn = 0;
-    for (int k = blockIdx.x * 256 + tid; k < npix; k += ZB_QA_NBLK * 256) {
-        const float d = rdiff[R.off + k], nz = rnoise[R.off + k];
-        const int m0 = omask[R.off + k];
-        // NaN/Inf side effect of getStampStats3 (functions.c:857-861), in the order the runs happen
-        int ms[4] = {m0, m0, m0, m0}, mn = m0;
-        const bool nfd = (d * 0.0f != 0.0f), nfn = (nz * 0.0f != 0.0f);
-        if (nfd || nfn) {
+    // one statistic's share of a pixel; `s` is a compile-time constant at every call site
+#define QA_ACC(s, xv, mk) do { \
+        if (S.phase[s] != 2) { int um_, sm_; qa_masks(s, um_, sm_); \
+            if (!zb_excluded(mk, xv, um_, sm_) && !((xv) * 0.0f != 0.0f)) { \
+                bool keep_; \
+                if (!S.exact[s]) keep_ = !((xv) < S.flo[s] || (xv) > S.fhi[s]); \
+                else if (S.phase[s] == 0) { keep_ = true; for (int c_ = 0; c_ < S.ncrit[s]; c_++) keep_ &= !((fabs((xv) - S.cm[s][c_]) * S.ci[s][c_]) > statSig); } \
+                else keep_ = !((fabs((xv) - S.mean[s]) * S.isd[s]) > statSig); \
+                if (keep_) { \
+                    if (S.phase[s] == 0) { a1[s] += (xv); a2[s] += (double)((xv) * (xv)); an[s]++; } \
+                    else { \
+                        int index = (int)(floor(((xv) - S.bin1[s]) / S.binsize[s]) + 1); \
+                        index = (index < 0 ? 0 : index); index = (index > 255 ? 255 : index); \
+                        const unsigned peers = __match_any_sync(__activemask(), index); \
+                        if ((int)(__ffs(peers) - 1) == (threadIdx.x & 31)) atomicAdd(&S.bins[s][index], __popc(peers)); \
+                        a1[s] += fabs((double)(xv)); an[s]++; } } } } } while (0)
+    const int stride = ZB_QA_NBLK * 256;
+    for (int kb = blockIdx.x * 256 + tid; kb < npix; kb += 4 * stride) {
+        float dv[4], nv[4]; int mv[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {                   // 12 independent loads in flight per thread
+            const int k = kb + u * stride;
+            if (k < npix) { dv[u] = rdiff[R.off + k]; nv[u] = rnoise[R.off + k]; mv[u] = omask[R.off + k]; }
+            else { dv[u] = 0.f; nv[u] = 0.f; mv[u] = 0xffff; }      // excluded from everything
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int k = kb + u * stride;
+            if (k >= npix) break;
+            const float d = dv[u], nz = nv[u];
+            const int m0 = mv[u];
+            const bool nfd = (d * 0.0f != 0.0f), nfn = (nz * 0.0f != 0.0f);
+            if (!(nfd || nfn)) {
+                // GOOD pixels (no mask bit at all) and OK pixels (a bit in 0xff, not OUTPUT_ISBAD) are disjoint
+                if ((m0 & 0xffff) == 0) {
+                    if (first && !(fabsf(d) < 1e-10f)) {        // getNoiseStats3, functions.c:719-761
+                        float ndat = (float)(1. / nz);
+                        nn++; nsum += (double)(d * d * ndat * ndat);
+                    }
+                    QA_ACC(0, d, m0); QA_ACC(1, nz, m0);
+                } else if ((m0 & 0xff) && !(m0 & ZB_FLAG_OUTPUT_ISBAD)) {
+                    QA_ACC(2, d, m0); QA_ACC(3, nz, m0);
+                }
+                continue;
+            }
+            // NaN/Inf side effect of getStampStats3 (functions.c:857-861), in the order the runs happen
+            int ms[4] = {m0, m0, m0, m0}, mn = m0;
             const int mark = ZB_FLAG_INPUT_ISBAD | ZB_FLAG_ISNAN;
             int m = m0;
             if (nfd && !zb_excluded(m, d, 0x0, 0xffff)) m |= mark;
@@ -319,37 +359,15 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
                 if (out_mask && x >= R.rx0 - R.bx0 && x <= R.own_x1 - R.bx0 && y >= R.ry0 - R.by0 && y <= R.own_y1 - R.by0)
                     out_mask[(long long)(R.by0 + y) * D->nx + (R.bx0 + x)] = m;
             }
-        }
-        if (first && !zb_excluded(mn, d, 0x0, 0xffff)) {           // getNoiseStats3, functions.c:719-761
-            float ndat = (float)(1. / nz);
-            nn++; nsum += (double)(d * d * ndat * ndat);
-        }
-#pragma unroll
-        for (int s = 0; s < 4; s++) {
-            if (S.phase[s] == 2) continue;
-            const float x = (s & 1) ? nz : d;
-            int um, sm; qa_masks(s, um, sm);
-            if (zb_excluded(ms[s], x, um, sm)) continue;
-            if (x * 0.0f != 0.0f) continue;
-            if (S.phase[s] == 0) {
-                if (!S.exact[s]) { if (x < S.flo[s] || x > S.fhi[s]) continue; }
-                else {
-                    bool rej = false;
-                    for (int c = 0; c < S.ncrit[s]; c++) rej |= (fabs(x - S.cm[s][c]) * S.ci[s][c]) > statSig;
-                    if (rej) continue;
-                }
-                a1[s] += x; a2[s] += (double)(x * x); an[s]++;
-            } else {
-                if (!S.exact[s]) { if (x < S.flo[s] || x > S.fhi[s]) continue; }
-                else if ((fabs(x - S.mean[s]) * S.isd[s]) > statSig) continue;
-                int index = (int)(floor((x - S.bin1[s]) / S.binsize[s]) + 1);
-                index = (index < 0 ? 0 : index);
-                index = (index > 255 ? 255 : index);
-                atomicAdd(&S.bins[s][index], 1);
-                a1[s] += fabs((double)x); an[s]++;
+            if (first && !zb_excluded(mn, d, 0x0, 0xffff)) {
+                float ndat = (float)(1. / nz);
+                nn++; nsum += (double)(d * d * ndat * ndat);
             }
+            QA_ACC(0, d, ms[0]); QA_ACC(1, nz, ms[1]); QA_ACC(2, d, ms[2]); QA_ACC(3, nz, ms[3]);
         }
     }
+#undef QA_ACC
+#pragma unroll                                   // static indices keep a1/a2/an in registers
     for (int s = 0; s < 4; s++) {
         if (S.phase[s] == 2) continue;
         qa_block_sum(S, a1[s], a2[s], an[s]);
@@ -373,8 +391,13 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
     if (!s_last) return;
     __threadfence();
     for (int k = tid; k < 4 * 256; k += 256) (&S.bins[0][0])[k] = __ldcg(&qa[r * 4 + (k >> 8)].bins[k & 255]);
+    __shared__ ZbQaPart s_part[5 * ZB_QA_NBLK];
+    for (int k = tid; k < 5 * ZB_QA_NBLK; k += 256) {
+        const ZbQaPart *g = part + (size_t)r * 5 * ZB_QA_NBLK + k;
+        s_part[k].s1 = __ldcg(&g->s1); s_part[k].s2 = __ldcg(&g->s2); s_part[k].n = __ldcg(&g->n);
+    }
     __syncthreads();
-    if (tid < 5) qa_decide(D, qa, part, q, r, tid, first, tid < 4 ? S.bins[tid] : S.bins[0]);
+    if (tid < 5) qa_decide(D, qa, s_part, q, r, tid, first, tid < 4 ? S.bins[tid] : S.bins[0]);
     if (tid == 0) qa[r * 4].ticket = 0;
 }
 
