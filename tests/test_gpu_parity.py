@@ -120,9 +120,10 @@ def test_nan_and_constant_inputs(oracle, gpu_ctx):
     assert (np.abs(o.diff.astype(np.float64) - g.diff)[fin] / sig[fin]).max() <= TOL_SIGMA
 
 
-@pytest.mark.parametrize("name", ["c1", "c1b"])
+@pytest.mark.parametrize("name", ["c1", "c1b", "c4"])
 def test_full_size_quadrant(name, oracle, gpu_ctx):
-    """BASELINE.json configs[0]/[1] (and the zuds-actual variant) at 3080x3072 against the oracle."""
+    """BASELINE.json configs[0]/[1] (and the zuds-actual variant) and configs[3] (hw 15, order 4,
+    convolve-science, 32x32 stamp grid) at 3080x3072 against the oracle."""
     case = CS.FULL[name]
     pair = CS.make_pair(case)
     p = CS.params_of(case, pair)

@@ -120,7 +120,8 @@ struct zb_ctx {
     double  *d_vv; int *d_indx;  // LU scratch
     ZbFit   *d_fit, *h_fit;
     int     *d_jobs, *d_njobs, *h_njobs;
-    double  *d_kern;             // [region][blocks][2*fw*fw]  (K, K^2) per convolution block
+    double  *d_kern;             // [region][blocks+1][fw*fw]  K per convolution block (+ the region-centre kernel)
+    double  *d_kaks;             // [region][blocks+1]  sum |K| per block in the reference's tap order
     double  *d_kstat;            // per-region: ksum, aks
     double  *d_stats;  double *h_stats;   // region QA scratch
     ZbQaStat *d_qa;              // [region][4]
