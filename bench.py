@@ -40,6 +40,9 @@ METRIC = "ZTF quadrant subtractions/sec"
 UNIT = "quadrant-pairs/s"
 SHAPE = (3080, 3072)
 ALG_BYTES_PER_PIXEL = 29          # 4 float inputs + 1 mask byte in, 2 floats + int32 mask out
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_convolve launch at C1, from the ncu --set full
+# capture summarised in profiles/r01_ncu_k_convolve_s16.txt (251.70 MB + 190.47 MB); None for other shapes
+NCU_CONV_TRAFFIC_BYTES = 442164736
 
 
 def workload_case():
@@ -321,7 +324,7 @@ def bench_b200(args):
         "gpu_launches": launches,
         "clocks": clk,
         "roofline": {"kernel": "k_convolve", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / hbm_peak, "traffic": NCU_CONV_TRAFFIC_BYTES, "peak_source": peak_src,
                      "alg_bytes_per_launch": alg_bytes, "kernel_ms": stage_ms["k_convolve"],
                      "kernel_ms_in_timed_region": statistics.mean(conv_ms) if conv_ms else None,
                      "fp64_dfma_per_launch": 2 * (2 * params[0].hw_kernel + 1) ** 2 * nx * ny,

@@ -186,6 +186,77 @@ long long zb_launch_count(const zb_ctx *ctx);
    lets a binding verify its own struct mirror before the first call */
 int zb_abi_sizeof(int which);
 
+/* ------------------------------------------------------------------------------------------
+ * Row-tile sessions: ONE oversized frame fitted by a single region (nreg_x == nreg_y == 1,
+ * BASELINE.json configs[4]) split over `world` GPUs by image rows, one process (rank) per GPU.
+ * The reference has no counterpart (one single-threaded process per frame, zuds/mpi.py:36-64);
+ * the arithmetic per pixel / per stamp is that of zb_subtract and the results are bit-identical
+ * to zb_subtract on the whole frame, whatever `world` is.
+ *
+ * Every rank keeps full-size [ny*nx] device arrays but only needs rows [in_row0, in_row1) of the
+ * inputs: it loads its own rows [row0, row1) and receives the halo rows from its neighbours
+ * (P2P exchange, done by the caller).  Stamp-grid rows [cell_row0, cell_row1) and convolution
+ * block rows [blk_row0, blk_row1) are the rank's; it writes output rows [out_row0, out_row1).
+ * Data crossing ranks, all summed with zeros elsewhere so that one all-reduce(SUM) merges them bit
+ * for bit: the stamp-search records, the per-stamp normal equations and the per-stamp figures of
+ * merit.  The global normal matrix is then built and solved on every rank from the same per-stamp
+ * terms in the reference's stamp order (alard.c:843-1025), so no rank-dependent summation order
+ * enters the solution.  Mask rows changed by the stamp search travel with a second halo exchange.
+ *
+ *   zb_tile_plan          pure host arithmetic: who owns what (no GPU needed)
+ *   zb_tile_begin         configure, input masks of the needed rows, stamp search of the own grid cells
+ *   zb_tile_cells_export/import   search records as int32 words, zero outside the rank's cells
+ *   zb_tile_resolve       replicated on every rank: stale-slot fix-ups, threshold retry, stamp compaction.
+ *                         *action: 0 done | 1 cell *cell must be searched again: every rank calls
+ *                         zb_tile_research(cell) (a no-op except on its owner), then the records are
+ *                         merged again | 2 every rank calls zb_tile_begin_retry, then merges again
+ *   zb_tile_rows          copy rows [r0, r1) of a per-region work array out of / into the context:
+ *                         the input-stage mask (after resolve, for the mask halo exchange) and the
+ *                         pre-output-masking difference / noise / mask the QA statistics read
+ *   zb_tile_fill          fill the rank's own stamps (vectors, per-stamp normal equations)
+ *   zb_tile_normal_export/import  per-stamp Gram matrices + right-hand sides (device doubles)
+ *   zb_tile_solve         replicated global fit; figure of merit of the rank's own stamps
+ *   zb_tile_sig_export/import     per-stamp figure of merit (device doubles)
+ *   zb_tile_clip          replicated check_again; refills own replaced stamps; *active: another pass
+ *   zb_tile_convolve      the rank's block rows of the fused convolution/output pass
+ *   zb_tile_finish        rank 0, after the rows were gathered: FSIG, region statistics, records
+ * Every call runs on the stream given to zb_tile_begin (pass the stream the collectives use).
+ */
+typedef struct zb_tile_info {
+    int32_t rank, world;
+    int32_t cell_row0, cell_row1;     /* stamp-grid rows */
+    int32_t row0, row1;               /* image rows this rank loads / is authoritative for */
+    int32_t in_row0, in_row1;         /* image rows it needs (own + halo) */
+    int32_t blk_row0, blk_row1;       /* convolution block rows */
+    int32_t out_row0, out_row1;       /* output rows it writes */
+    int32_t halo;                     /* max(row0 - in_row0, in_row1 - row1) */
+    int32_t n_cells, cell_words;      /* grid cells of the frame, int32 words per search record */
+    int32_t n_slots, gram_len, rhs_len;  /* stamp slots; doubles per slot in the exported normal equations */
+} zb_tile_info;
+
+enum { ZB_TILE_MASK_IN = 0, ZB_TILE_RDIFF = 1, ZB_TILE_RNOISE = 2, ZB_TILE_OMASK = 3 };
+
+int zb_tile_plan(const zb_params *p, int world, int rank, zb_tile_info *out);
+int zb_tile_begin(zb_ctx *ctx, const zb_params *p, int world, int rank,
+                  const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
+                  const void *sci_mask, int sci_mask_dtype, const void *ref_mask, int ref_mask_dtype,
+                  float *diff, float *noise, int32_t *out_mask, void *stream);
+int zb_tile_begin_retry(zb_ctx *ctx);
+int zb_tile_cells_export(zb_ctx *ctx, int32_t *words /* host [n_cells*cell_words] */);
+int zb_tile_cells_import(zb_ctx *ctx, const int32_t *words);
+int zb_tile_resolve(zb_ctx *ctx, int *action, int *cell);
+int zb_tile_research(zb_ctx *ctx, int cell);
+int zb_tile_rows(zb_ctx *ctx, int which, int import, int r0, int r1, void *buf /* device [(r1-r0)*nx] 4-byte elements */);
+int zb_tile_fill(zb_ctx *ctx);
+int zb_tile_normal_export(zb_ctx *ctx, double *gram /* device [n_slots*gram_len] */, double *rhs /* device [n_slots*rhs_len] */);
+int zb_tile_normal_import(zb_ctx *ctx, const double *gram, const double *rhs);
+int zb_tile_solve(zb_ctx *ctx);
+int zb_tile_sig_export(zb_ctx *ctx, double *sig /* device [n_slots] */);
+int zb_tile_sig_import(zb_ctx *ctx, const double *sig);
+int zb_tile_clip(zb_ctx *ctx, int *active);
+int zb_tile_convolve(zb_ctx *ctx);
+int zb_tile_finish(zb_ctx *ctx, zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps);
+
 #ifdef __cplusplus
 }
 #endif

@@ -53,6 +53,8 @@ FULL = {
     "c1b": Case("c1b", (3080, 3072), 2.0, 3, {}),
     "c4": Case("c4", (3080, 3072), 6.0, 1, {"ko": 4, "nsx": 32, "nsy": 32, "r": 15, "rss": 15},
                replace={"-c": "i"}),
+    # coadd-scale frame, one global fit: the row-tile configuration (BASELINE.json configs[4])
+    "c5": Case("c5", (6160, 6144), 4.0, 1, {"ko": 2, "nsx": 20, "nsy": 20}),
 }
 
 

@@ -34,6 +34,8 @@ def test_struct_layouts_match_header():
     assert lib.zb_abi_sizeof(1) == C.sizeof(P.ZbSizes)
     assert lib.zb_abi_sizeof(2) == C.sizeof(P.ZbRegionInfo)
     assert lib.zb_abi_sizeof(3) == C.sizeof(P.ZbStampInfo)
+    from zuds_pipeline_b200 import tiles
+    assert lib.zb_abi_sizeof(4) == C.sizeof(tiles.ZbTileInfo)
 
 
 def test_defaults_match_python_and_oracle(oracle):

@@ -15,7 +15,12 @@ ZB_NSTAGES = 12
 MASK_DTYPES = {"uint8": 1, "bool": 1, "int16": 2, "int32": 4}
 
 EXPORTS = ("zb_version", "zb_params_default", "zb_params_check", "zb_sizes_of", "zb_create", "zb_destroy",
-           "zb_last_error", "zb_subtract", "zb_subtract_host", "zb_last_timings", "zb_stage_name", "zb_launch_count", "zb_abi_sizeof")
+           "zb_last_error", "zb_subtract", "zb_subtract_host", "zb_last_timings", "zb_stage_name", "zb_launch_count", "zb_abi_sizeof",
+           # row-tile sessions (bound by tiles.py)
+           "zb_tile_plan", "zb_tile_begin", "zb_tile_begin_retry", "zb_tile_cells_export", "zb_tile_cells_import",
+           "zb_tile_resolve", "zb_tile_research", "zb_tile_rows", "zb_tile_fill", "zb_tile_normal_export",
+           "zb_tile_normal_import", "zb_tile_solve", "zb_tile_sig_export", "zb_tile_sig_import", "zb_tile_clip",
+           "zb_tile_convolve", "zb_tile_finish")
 
 
 class ZbError(RuntimeError):

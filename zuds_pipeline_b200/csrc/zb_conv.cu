@@ -237,7 +237,7 @@ template <int TX, int TY, int CH, bool EXACT /* fw % CH == 0 */, bool KKONLY /* 
 __global__ void __launch_bounds__(256)
 k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sols, const double *__restrict__ kern,
            const double *__restrict__ ksums, const double *__restrict__ kaks,
-           int nbx_max, int nby_max, int NBX, int NBY, int GX, int GY, int W, int TH,
+           int nbx_max, int nby_max, int NBX, int NBY, int GX, int GY, int W, int TH, int blk_row0, int blk_row1,
            float *__restrict__ rdiff, float *__restrict__ rnoise, int32_t *__restrict__ omask,
            float *__restrict__ diff, float *__restrict__ noise, int32_t *__restrict__ out_mask)
 {
@@ -246,8 +246,8 @@ k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sol
     const ZbRegion R = D->reg[r];
     if (R.skip) return;
     const int hw = D->p.hw_kernel, fw = D->sz.fw_kernel, fw2 = fw * fw, B = D->sz.kc_step;
-    const int nbx = (R.rpx + B - 1) / B, nby = (R.rpy + B - 1) / B;
-    const int bx0 = blockIdx.x * NBX, by0 = blockIdx.y * NBY;
+    const int nbx = (R.rpx + B - 1) / B, nby = min((R.rpy + B - 1) / B, blk_row1);   // block rows [blk_row0, blk_row1): row-tile window
+    const int bx0 = blockIdx.x * NBX, by0 = blk_row0 + blockIdx.y * NBY;
     if (by0 >= nby || bx0 >= nbx) return;
     const int i00 = bx0 * B + hw, j00 = by0 * B + hw;         // first output pixel of the CTA (region coords)
     if (j00 >= R.rpy - hw || i00 >= R.rpx - hw) return;
@@ -421,7 +421,7 @@ k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sol
     const double o_qq = __fmul_rn(P.o_quad, P.o_quad);
     const float kfm = D->p.ker_frac_mask, fill_noise = D->p.fill_val_noise;
     const bool mask_out = D->p.kf_spread_mask2 >= 0;
-    const int ox_lim = min(OW, R.rpx - hw - i00), oy_lim = min(OH, R.rpy - hw - j00);
+    const int ox_lim = min(OW, R.rpx - hw - i00), oy_lim = min(min(OH, (nby - by0) * B), R.rpy - hw - j00);
     const int own_x0 = R.rx0 - R.bx0 - i00, own_x1 = R.own_x1 - R.bx0 - i00;   // ownership window, CTA coords
     const int own_y0 = R.ry0 - R.by0 - j00, own_y1 = R.own_y1 - R.by0 - j00;
     const long long gout = (long long)(R.by0 + j00) * nxi + (R.bx0 + i00);
@@ -503,7 +503,7 @@ k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sol
 __global__ void __launch_bounds__(256)
 k_region_frame(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sols,
                float *__restrict__ rdiff, float *__restrict__ rnoise, int32_t *__restrict__ omask,
-               float *__restrict__ diff, float *__restrict__ noise, int32_t *__restrict__ out_mask)
+               float *__restrict__ diff, float *__restrict__ noise, int32_t *__restrict__ out_mask, int row0, int row1)
 {
     const int r = blockIdx.y;
     const ZbRegion R = D->reg[r];
@@ -514,6 +514,7 @@ k_region_frame(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__
         int x, y;
         if (k < nrow) { int q = k / R.rpx; x = k - q * R.rpx; y = q < hw ? q : R.rpy - 2 * hw + q; }
         else { int kk = k - nrow, q = kk / (2 * hw), c = kk - q * 2 * hw; y = hw + q; x = c < hw ? c : R.rpx - 2 * hw + c; }
+        if (y < row0 || y >= row1) continue;                       // row-tile window (whole region: 0 .. INT_MAX)
         // vData is calloc'ed: the convolved variance is 0 on the frame (alard.c:1264)
         finish_pixel(D, R, P, sols + (long long)r * (D->sz.n_comp_total + 1), x, y, false, 0.f, 0.f, 0, 1.0, false,
                      rdiff, rnoise, omask, diff, noise, out_mask);
@@ -522,7 +523,8 @@ k_region_frame(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__
 
 int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
                        const void *smask, int sdt, const void *tmask, int tdt,
-                       float *diff, float *noise, int32_t *out_mask, cudaStream_t st)
+                       float *diff, float *noise, int32_t *out_mask, cudaStream_t st,
+                       int blk_row0, int blk_row1, int row0, int row1)
 {
     const zb_sizes &sz = ctx->sz;
     const zb_params &p = ctx->p;
@@ -576,12 +578,14 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
         threads = ((NBX * NBY * tpb + 31) / 32) * 32;
     }
     if (smem > ZB_SMEM_OPTIN) { snprintf(ctx->err, sizeof ctx->err, "convolution tile needs %zu bytes of shared memory", smem); return ZB_ERR_UNSUPPORTED; }
-    dim3 gc((nbx_max + NBX - 1) / NBX, (nby_max + NBY - 1) / NBY, nR);
+    if (blk_row1 > nby_max) blk_row1 = nby_max;
+    if (blk_row0 < 0) blk_row0 = 0;
+    dim3 gc((nbx_max + NBX - 1) / NBX, (blk_row1 - blk_row0 + NBY - 1) / NBY, nR);
     cudaEventRecord(ctx->ev[10], st);          // k_convolve alone: the kernel bench.py's roofline is quoted on
 #define ZB_CONV_LAUNCH2(TX_, TY_, CH_, EX_, KK_) do { \
         cudaFuncSetAttribute(k_convolve<TX_, TY_, CH_, EX_, KK_>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN); \
         k_convolve<TX_, TY_, CH_, EX_, KK_><<<gc, threads, smem, st>>>(ctx->d_dev, P, ctx->d_sol, ctx->d_kern, ctx->d_kstat, ctx->d_kaks, nbx_max, nby_max, \
-            NBX, NBY, GX, GY, W, TH, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask); } while (0)
+            NBX, NBY, GX, GY, W, TH, blk_row0, blk_row1, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask); } while (0)
 #define ZB_CONV_LAUNCH(TX_, TY_, CH_) do { \
         const bool ex_ = (fw % CH_) == 0, kk_ = p.convolve_variance != 0; \
         if (ex_ && !kk_) ZB_CONV_LAUNCH2(TX_, TY_, CH_, true, false); \
@@ -594,7 +598,7 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
 #undef ZB_CONV_LAUNCH
     ZB_DBG("k_convolve");
     cudaEventRecord(ctx->ev[11], st);
-    k_region_frame<<<dim3(64, nR), 256, 0, st>>>(ctx->d_dev, P, ctx->d_sol, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask); ZB_DBG("k_region_frame");
+    k_region_frame<<<dim3(64, nR), 256, 0, st>>>(ctx->d_dev, P, ctx->d_sol, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask, row0, row1); ZB_DBG("k_region_frame");
     ctx->launches += 3;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "convolution kernels", __FILE__, __LINE__);

@@ -623,10 +623,10 @@ __global__ void __launch_bounds__(256)
 k_stamp_sig(const ZbDev *__restrict__ D, ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
             const double *__restrict__ vec, const double *__restrict__ kref, const double *__restrict__ sols,
             const float *__restrict__ sci, const float *__restrict__ ref,
-            const float *__restrict__ sci_rms, const float *__restrict__ ref_rms, int32_t *__restrict__ m_in)
+            const float *__restrict__ sci_rms, const float *__restrict__ ref_rms, int32_t *__restrict__ m_in, int slot0)
 {
     extern __shared__ __align__(16) unsigned char dyn[];
-    const int slot = blockIdx.x;
+    const int slot = slot0 + blockIdx.x;
     ZbStamp &S = stamps[slot];
     if (S.nss <= 0 || S.sscnt >= S.nss) return;
     if (!fit[S.region].active) return;
@@ -766,47 +766,78 @@ __global__ void k_clip(const ZbDev *__restrict__ D, ZbStamp *__restrict__ stamps
     F.active = check;
 }
 
-int zb_launch_fit_iteration(zb_ctx *ctx, const float *conv_img, const float *ref_img,
-                            const float *sci, const float *ref, const float *sci_rms, const float *ref_rms, cudaStream_t st)
+// wxy + global normal equations + LU solve (alard.c:343-360) for every active region
+int zb_launch_fit_solve(zb_ctx *ctx, cudaStream_t st)
 {
     const zb_sizes &sz = ctx->sz;
-    const int n = sz.mat_size, nR = sz.n_regions, npix = sz.fw_ksstamp * sz.fw_ksstamp;
-    (void)conv_img; (void)ref_img;
+    const int n = sz.mat_size, nR = sz.n_regions;
     k_wxy<<<(ctx->n_slots + 127) / 128, 128, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->n_slots, ctx->d_wxy); ZB_DBG("k_wxy");
     dim3 gb((n + 1 + 15) / 16, (n + 15) / 16, nR);
     k_build_matrix<<<gb, dim3(16, 16), 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_rhs, ctx->d_wxy, ctx->d_mat, ctx->d_sol); ZB_DBG("k_build_matrix");
-    {
-        k_lu_init<<<dim3((n + 3) / 4, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv); ZB_DBG("k_lu_init");
-        const size_t smp = ((size_t)n * (LU_NB + 1) + n) * sizeof(double);
-        if (smp > ZB_SMEM_OPTIN) { snprintf(ctx->err, sizeof ctx->err, "normal matrix of %d rows too large for the LU panel kernel", n); return ZB_ERR_UNSUPPORTED; }
-        cudaFuncSetAttribute(k_lu_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
-        for (int k0 = 0; k0 < n; k0 += LU_NB) {
-            const int nb = n - k0 < LU_NB ? n - k0 : LU_NB, rest = n - k0 - nb;
-            k_lu_panel<<<nR, LU_PT, ((size_t)(n - k0) * (LU_NB + 1) + (n - k0)) * sizeof(double), st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv, ctx->d_indx, k0); ZB_DBG("k_lu_panel");
-            ctx->launches++;
-            if (n - nb > 0) {
-                k_lu_swap_u<<<dim3((n - nb + 127) / 128, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, k0); ZB_DBG("k_lu_swap_u");
-                ctx->launches++;
-            }
-            if (rest > 0) {
-                k_lu_trail<<<dim3((rest + 31) / 32, (rest + 31) / 32, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, k0); ZB_DBG("k_lu_trail");
-                ctx->launches++;
-            }
-        }
-        const size_t sms = (size_t)5 * n * sizeof(double);
-        cudaFuncSetAttribute(k_lu_subst, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
-        k_lu_subst<<<nR, LU_ST, sms, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, ctx->d_sol); ZB_DBG("k_lu_subst");
+    k_lu_init<<<dim3((n + 3) / 4, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv); ZB_DBG("k_lu_init");
+    const size_t smp = ((size_t)n * (LU_NB + 1) + n) * sizeof(double);
+    if (smp > ZB_SMEM_OPTIN) { snprintf(ctx->err, sizeof ctx->err, "normal matrix of %d rows too large for the LU panel kernel", n); return ZB_ERR_UNSUPPORTED; }
+    cudaFuncSetAttribute(k_lu_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
+    for (int k0 = 0; k0 < n; k0 += LU_NB) {
+        const int nb = n - k0 < LU_NB ? n - k0 : LU_NB, rest = n - k0 - nb;
+        k_lu_panel<<<nR, LU_PT, ((size_t)(n - k0) * (LU_NB + 1) + (n - k0)) * sizeof(double), st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv, ctx->d_indx, k0); ZB_DBG("k_lu_panel");
         ctx->launches++;
+        if (n - nb > 0) {
+            k_lu_swap_u<<<dim3((n - nb + 127) / 128, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, k0); ZB_DBG("k_lu_swap_u");
+            ctx->launches++;
+        }
+        if (rest > 0) {
+            k_lu_trail<<<dim3((rest + 31) / 32, (rest + 31) / 32, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, k0); ZB_DBG("k_lu_trail");
+            ctx->launches++;
+        }
     }
+    const size_t sms = (size_t)5 * n * sizeof(double);
+    cudaFuncSetAttribute(k_lu_subst, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
+    k_lu_subst<<<nR, LU_ST, sms, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, ctx->d_sol); ZB_DBG("k_lu_subst");
+    ctx->launches += 4;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "fit solve", __FILE__, __LINE__);
+    return ZB_OK;
+}
+
+// getStampSig (alard.c:1062-1140) for the stamp slots [slot0, slot1)
+int zb_launch_stamp_sig(zb_ctx *ctx, const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
+                        int slot0, int slot1, cudaStream_t st)
+{
+    if (slot1 <= slot0) return ZB_OK;
+    const zb_sizes &sz = ctx->sz;
+    const int npix = sz.fw_ksstamp * sz.fw_ksstamp;
     size_t sm = (size_t)npix * (sizeof(double) + 1) + (size_t)sz.n_comp_ker * sizeof(double) + 16;
     cudaFuncSetAttribute(k_stamp_sig, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
-    k_stamp_sig<<<ctx->n_slots, 256, sm, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_vec, ctx->d_kref, ctx->d_sol,
-                                                sci, ref, sci_rms, ref_rms, ctx->d_min); ZB_DBG("k_stamp_sig");
+    k_stamp_sig<<<slot1 - slot0, 256, sm, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_vec, ctx->d_kref, ctx->d_sol,
+                                                 sci, ref, sci_rms, ref_rms, ctx->d_min, slot0); ZB_DBG("k_stamp_sig");
+    ctx->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "stamp sig", __FILE__, __LINE__);
+    return ZB_OK;
+}
+
+// check_again's decisions (alard.c:1143-1247); leaves the slots to refill in d_jobs / d_njobs
+int zb_launch_clip(zb_ctx *ctx, cudaStream_t st)
+{
+    const zb_sizes &sz = ctx->sz;
+    const int nR = sz.n_regions;
     cudaMemsetAsync(ctx->d_njobs, 0, sizeof(int), st);
     k_clip<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, (float *)ctx->d_stats, (char *)(ctx->d_stats) + (size_t)nR * sz.n_stamps * sizeof(float),
                                           ctx->d_jobs, ctx->d_njobs); ZB_DBG("k_clip");
-    ctx->launches += 5;
+    ctx->launches++;
     cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "fit iteration", __FILE__, __LINE__);
+    if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "clip", __FILE__, __LINE__);
     return ZB_OK;
+}
+
+int zb_launch_fit_iteration(zb_ctx *ctx, const float *conv_img, const float *ref_img,
+                            const float *sci, const float *ref, const float *sci_rms, const float *ref_rms, cudaStream_t st)
+{
+    (void)conv_img; (void)ref_img;
+    int rc = zb_launch_fit_solve(ctx, st);
+    if (rc != ZB_OK) return rc;
+    rc = zb_launch_stamp_sig(ctx, sci, ref, sci_rms, ref_rms, 0, ctx->n_slots, st);
+    if (rc != ZB_OK) return rc;
+    return zb_launch_clip(ctx, st);
 }

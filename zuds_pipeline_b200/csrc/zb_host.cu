@@ -268,7 +268,7 @@ static void set_scalars(zb_ctx *ctx, const zb_params *p) {
 
 // (Re)build the workspace for a parameter set.  Pairs of one survey share the geometry and differ
 // only in thresholds, so the usual call just refreshes the scalars.
-static int configure(zb_ctx *ctx, const zb_params *p) {
+int zb_configure(zb_ctx *ctx, const zb_params *p) {
     if (ctx->configured && memcmp(&ctx->p, p, sizeof *p) == 0) return ZB_OK;
     int rc = zb_params_check(p, ctx->err, (int)sizeof ctx->err);
     if (rc != ZB_OK) return rc;
@@ -342,7 +342,7 @@ static int configure(zb_ctx *ctx, const zb_params *p) {
     DMALLOC(ctx->d_indx, (size_t)sz.n_regions * sz.mat_size * sizeof(int));
     DMALLOC(ctx->d_fit, (size_t)sz.n_regions * sizeof(ZbFit));   HMALLOC(ctx->h_fit, (size_t)sz.n_regions * sizeof(ZbFit));
     DMALLOC(ctx->d_jobs, ns * sizeof(int));
-    DMALLOC(ctx->d_njobs, sizeof(int));   HMALLOC(ctx->h_njobs, 4 * sizeof(int));
+    DMALLOC(ctx->d_njobs, sizeof(int));   HMALLOC(ctx->h_njobs, (4 + ns) * sizeof(int));     // [0]: job count; [4..]: job list scratch (zb_tile.cu)
     const int B = sz.kc_step, nbx = (sz.max_rpix_x + B - 1) / B, nby = (sz.max_rpix_y + B - 1) / B;
     DMALLOC(ctx->d_kern, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * fw * fw * sizeof(double));
     DMALLOC(ctx->d_kaks, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * sizeof(double));
@@ -362,7 +362,7 @@ static int configure(zb_ctx *ctx, const zb_params *p) {
 
 // ------------------------------------------------------------- orchestration
 
-static void init_cells(zb_ctx *ctx, int r, float kft) {
+void zb_init_cells(zb_ctx *ctx, int r, float kft) {
     const zb_sizes &sz = ctx->sz;
     const ZbRegion &R = ctx->h_dev->reg[r];
     for (int gl = 0; gl < sz.nstamp_y; gl++)
@@ -413,6 +413,53 @@ static int resolve_region(zb_ctx *ctx, int r, const float *conv_img, cudaStream_
 #define CHECK_RC(x) do { int rc_ = (x); if (rc_ != ZB_OK) return rc_; } while (0)
 #define SYNC(what) do { cudaError_t e_ = cudaStreamSynchronize(st); if (e_ != cudaSuccess) return zb_cuda_fail(ctx, e_, what, __FILE__, __LINE__); } while (0)
 
+// Stage 8 of a subtraction: the small device-to-host read-backs and the per-region record (main.c:1719-1953 keywords)
+int zb_finish_readback(zb_ctx *ctx, zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps_out, int timing /* 0 none, 1 stages, 2 stages + k_convolve */, cudaStream_t st)
+{
+    const zb_sizes &sz = ctx->sz;
+    ZbDev *H = ctx->h_dev;
+    const int nR = sz.n_regions;
+    cudaMemcpyAsync(ctx->h_stamps, ctx->d_stamps, (size_t)ctx->n_slots * sizeof(ZbStamp), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, (size_t)nR * 64 * sizeof(double), cudaMemcpyDeviceToHost, st);
+    double *h_sol = (double *)((char *)ctx->h_stats + (size_t)nR * 64 * sizeof(double));
+    cudaMemcpyAsync(h_sol, ctx->d_sol, (size_t)nR * (sz.n_comp_total + 1) * sizeof(double), cudaMemcpyDeviceToHost, st);
+    double *h_ks = h_sol + (size_t)nR * (sz.n_comp_total + 1);
+    cudaMemcpyAsync(h_ks, ctx->d_kstat, (size_t)nR * 4 * sizeof(double), cudaMemcpyDeviceToHost, st);
+    STAGE(9);
+    SYNC("final read-back");
+    if (timing >= 1) for (int i = 0; i < 9; i++) cudaEventElapsedTime(&ctx->ms[i], ctx->ev[i], ctx->ev[i + 1]);
+    if (timing >= 2) cudaEventElapsedTime(&ctx->ms[9], ctx->ev[10], ctx->ev[11]);
+    for (int r = 0; r < nR; r++) {
+        zb_region_info *ri = &regions[r];
+        const ZbFit &F = ctx->h_fit[r];
+        const double *q = ctx->h_stats + (size_t)r * 64;
+        if (kernel_sol) {
+            double *dst = kernel_sol + (size_t)r * (sz.n_comp_total + 1);
+            if (H->reg[r].skip) memset(dst, 0, (size_t)(sz.n_comp_total + 1) * sizeof(double));
+            else { memcpy(dst, h_sol + (size_t)r * (sz.n_comp_total + 1), (size_t)(sz.n_comp_total + 1) * sizeof(double)); dst[0] = 0.0;
+                   for (int k = sz.mat_size + 1; k <= sz.n_comp_total; k++) dst[k] = 0.0; }
+        }
+        if (stamps_out) {
+            for (int k = 0; k < sz.n_stamps; k++) {
+                zb_stamp_info *so = &stamps_out[(size_t)r * sz.n_stamps + k];
+                memset(so, 0, sizeof *so);
+                if (k >= F.n_stamps) continue;
+                const ZbStamp &S = ctx->h_stamps[H->reg[r].stamp_base + k];
+                so->x0 = S.x0; so->y0 = S.y0; so->nss = S.nss; so->sscnt = S.sscnt;
+                for (int s = 0; s < S.nss; s++) { so->xss[s] = S.xss[s]; so->yss[s] = S.yss[s]; }
+                so->mode = S.mode; so->fwhm = S.fwhm; so->chi2 = S.chi2;
+            }
+        }
+        if (H->reg[r].skip) continue;
+        if (F.singular) ri->flags |= ZB_REGION_SINGULAR;
+        ri->n_skipped = F.n_skipped; ri->fit_iters = F.iters;
+        ri->ksum = h_ks[(size_t)r * 4]; ri->sssig = F.meansig; ri->ssscat = F.scatter;
+        ri->fsig = q[0]; ri->fscat = q[1]; ri->x2norm = q[2]; ri->nx2norm = (int)q[3];
+        ri->dmean = q[4]; ri->dsige = q[5]; ri->dsig = q[6]; ri->dmeano = q[7]; ri->dsigeo = q[8]; ri->dsigo = q[9]; ri->nscalo = q[10];
+    }
+    return ZB_OK;
+}
+
 extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
                            const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
                            const void *sci_mask, int sci_mask_dtype, const void *ref_mask, int ref_mask_dtype,
@@ -423,7 +470,7 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
     if (sci_mask && !(sci_mask_dtype == ZB_MASK_U8 || sci_mask_dtype == ZB_MASK_I16 || sci_mask_dtype == ZB_MASK_I32)) { snprintf(ctx->err, sizeof ctx->err, "bad sci_mask_dtype %d", sci_mask_dtype); return ZB_ERR_PARAM; }
     if (ref_mask && !(ref_mask_dtype == ZB_MASK_U8 || ref_mask_dtype == ZB_MASK_I16 || ref_mask_dtype == ZB_MASK_I32)) { snprintf(ctx->err, sizeof ctx->err, "bad ref_mask_dtype %d", ref_mask_dtype); return ZB_ERR_PARAM; }
     if (cudaSetDevice(ctx->device) != cudaSuccess) return zb_cuda_fail(ctx, cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
-    CHECK_RC(configure(ctx, p));
+    CHECK_RC(zb_configure(ctx, p));
     cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
     const zb_sizes &sz = ctx->sz;
     ZbDev *H = ctx->h_dev;
@@ -442,7 +489,7 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
 
     // ---- stage 1: stamp statistics + sub-stamp search, all grid cells of all regions at once
     STAGE(1);
-    for (int r = 0; r < nR; r++) init_cells(ctx, r, p->ker_fit_thresh);
+    for (int r = 0; r < nR; r++) zb_init_cells(ctx, r, p->ker_fit_thresh);
     cudaMemcpyAsync(ctx->d_cells, ctx->h_cells, (size_t)ctx->n_cells * sizeof(ZbCell), cudaMemcpyHostToDevice, st);
     CHECK_RC(zb_launch_stamp_search(ctx, conv_img, 0, ctx->n_cells, st));
     cudaMemcpyAsync(ctx->h_cells, ctx->d_cells, (size_t)ctx->n_cells * sizeof(ZbCell), cudaMemcpyDeviceToHost, st);
@@ -468,7 +515,7 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
         if ((kept / (float)sz.n_stamps) < p->min_frac_good_stamps && p->scale_fit_thresh < 1.f) {
             float kft = p->ker_fit_thresh;
             kft *= p->scale_fit_thresh;
-            init_cells(ctx, r, kft);
+            zb_init_cells(ctx, r, kft);
             const int c0 = r * sz.n_stamps;
             cudaMemcpyAsync(&ctx->d_cells[c0], &ctx->h_cells[c0], (size_t)sz.n_stamps * sizeof(ZbCell), cudaMemcpyHostToDevice, st);
             CHECK_RC(zb_launch_stamp_search(ctx, conv_img, c0, sz.n_stamps, st));
@@ -551,46 +598,8 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
 
     // ---- stage 8: small read-backs
     STAGE(8);
-    cudaMemcpyAsync(ctx->h_stamps, ctx->d_stamps, (size_t)ctx->n_slots * sizeof(ZbStamp), cudaMemcpyDeviceToHost, st);
-    cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, (size_t)nR * 64 * sizeof(double), cudaMemcpyDeviceToHost, st);
-    double *h_sol = (double *)((char *)ctx->h_stats + (size_t)nR * 64 * sizeof(double));
-    cudaMemcpyAsync(h_sol, ctx->d_sol, (size_t)nR * (sz.n_comp_total + 1) * sizeof(double), cudaMemcpyDeviceToHost, st);
-    double *h_ks = h_sol + (size_t)nR * (sz.n_comp_total + 1);
-    cudaMemcpyAsync(h_ks, ctx->d_kstat, (size_t)nR * 4 * sizeof(double), cudaMemcpyDeviceToHost, st);
-    STAGE(9);
-    SYNC("final read-back");
-    for (int i = 0; i < 9; i++) cudaEventElapsedTime(&ctx->ms[i], ctx->ev[i], ctx->ev[i + 1]);
-    if (njobs > 0) cudaEventElapsedTime(&ctx->ms[9], ctx->ev[10], ctx->ev[11]);
     ctx->ms[10] = cell_kclk[0]; ctx->ms[11] = cell_kclk[1];
-    for (int r = 0; r < nR; r++) {
-        zb_region_info *ri = &regions[r];
-        const ZbFit &F = ctx->h_fit[r];
-        const double *q = ctx->h_stats + (size_t)r * 64;
-        if (kernel_sol) {
-            double *dst = kernel_sol + (size_t)r * (sz.n_comp_total + 1);
-            if (H->reg[r].skip) memset(dst, 0, (size_t)(sz.n_comp_total + 1) * sizeof(double));
-            else { memcpy(dst, h_sol + (size_t)r * (sz.n_comp_total + 1), (size_t)(sz.n_comp_total + 1) * sizeof(double)); dst[0] = 0.0;
-                   for (int k = sz.mat_size + 1; k <= sz.n_comp_total; k++) dst[k] = 0.0; }
-        }
-        if (stamps_out) {
-            for (int k = 0; k < sz.n_stamps; k++) {
-                zb_stamp_info *so = &stamps_out[(size_t)r * sz.n_stamps + k];
-                memset(so, 0, sizeof *so);
-                if (k >= F.n_stamps) continue;
-                const ZbStamp &S = ctx->h_stamps[H->reg[r].stamp_base + k];
-                so->x0 = S.x0; so->y0 = S.y0; so->nss = S.nss; so->sscnt = S.sscnt;
-                for (int s = 0; s < S.nss; s++) { so->xss[s] = S.xss[s]; so->yss[s] = S.yss[s]; }
-                so->mode = S.mode; so->fwhm = S.fwhm; so->chi2 = S.chi2;
-            }
-        }
-        if (H->reg[r].skip) continue;
-        if (F.singular) ri->flags |= ZB_REGION_SINGULAR;
-        ri->n_skipped = F.n_skipped; ri->fit_iters = F.iters;
-        ri->ksum = h_ks[(size_t)r * 4]; ri->sssig = F.meansig; ri->ssscat = F.scatter;
-        ri->fsig = q[0]; ri->fscat = q[1]; ri->x2norm = q[2]; ri->nx2norm = (int)q[3];
-        ri->dmean = q[4]; ri->dsige = q[5]; ri->dsig = q[6]; ri->dmeano = q[7]; ri->dsigeo = q[8]; ri->dsigo = q[9]; ri->nscalo = q[10];
-    }
-    return ZB_OK;
+    return zb_finish_readback(ctx, regions, kernel_sol, stamps_out, njobs > 0 ? 2 : 1, st);
 }
 
 // ------------------------------------------------------------ host-buffer entry
@@ -648,6 +657,7 @@ extern "C" int zb_abi_sizeof(int which) {
     case 1: return (int)sizeof(zb_sizes);
     case 2: return (int)sizeof(zb_region_info);
     case 3: return (int)sizeof(zb_stamp_info);
+    case 4: return (int)sizeof(zb_tile_info);
     default: return -1;
     }
 }

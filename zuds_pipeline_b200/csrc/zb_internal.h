@@ -92,6 +92,23 @@ struct ZbQaPart { double s1, s2; int n, pad; };
 
 #define ZB_CUDA_OK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return zb_cuda_fail(ctx, e_, #call, __FILE__, __LINE__); } while (0)
 
+// Row-tile session state (zb_tile.cu): one oversized single-region frame split over ranks by rows.
+struct ZbTile {
+    int on, world, rank;
+    zb_tile_info info;
+    const float *sci, *ref, *sci_rms, *ref_rms;
+    const void *smask, *tmask; int sdt, tdt;
+    float *diff, *noise; int32_t *out_mask;
+    cudaStream_t st;
+    float kft; int retried;
+    int cell_lo, cell_hi;          // grid cells of this rank
+    int slot_lo, slot_hi;          // kept-stamp slots of this rank (contiguous: compaction keeps grid order)
+    int n_kept;
+    int pending_cell;              // cell the stale-slot walk wants searched again, with the values it inherits
+    double pend[7];
+    zb_region_info ri;             // the region record, completed by zb_tile_finish on rank 0
+};
+
 struct zb_ctx {
     int device;
     cudaStream_t stream;
@@ -128,6 +145,7 @@ struct zb_ctx {
     ZbQaPart *d_qpart;           // [region][5][ZB_QA_NBLK]  (4 stats + getNoiseStats3)
     // staging for zb_subtract_host
     void *d_stage[9]; size_t stage_bytes[9];
+    ZbTile tile;
     // timings
     cudaEvent_t ev[ZB_NSTAGES + 1];
     float ms[ZB_NSTAGES];
@@ -140,18 +158,26 @@ int zb_dbg_sync(zb_ctx *ctx, cudaStream_t st, const char *what);
 
 // kernel launchers (each returns a zb_status)
 int zb_launch_input_mask(zb_ctx *ctx, const float *sci, const float *ref, const void *smask, int sdt,
-                         const void *tmask, int tdt, cudaStream_t st);
+                         const void *tmask, int tdt, cudaStream_t st, int y_lo = 0, int y_hi = 0x7fffffff);
 int zb_launch_stamp_search(zb_ctx *ctx, const float *conv_img, int first_cell, int n_cells, cudaStream_t st);
 int zb_launch_fill(zb_ctx *ctx, const float *conv_img, const float *ref_img, const int *d_jobs, int n_jobs, cudaStream_t st);
 int zb_launch_fit_iteration(zb_ctx *ctx, const float *conv_img, const float *ref_img,
                             const float *sci, const float *ref, const float *sci_rms, const float *ref_rms, cudaStream_t st);
 int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
                        const void *smask, int sdt, const void *tmask, int tdt,
-                       float *diff, float *noise, int32_t *out_mask, cudaStream_t st);
+                       float *diff, float *noise, int32_t *out_mask, cudaStream_t st,
+                       int blk_row0 = 0, int blk_row1 = 0x7fffffff, int row0 = 0, int row1 = 0x7fffffff);
+int zb_launch_fit_solve(zb_ctx *ctx, cudaStream_t st);
+int zb_launch_stamp_sig(zb_ctx *ctx, const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
+                        int slot0, int slot1, cudaStream_t st);
+int zb_launch_clip(zb_ctx *ctx, cudaStream_t st);
 int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStream_t st);
 int zb_launch_final_sig(zb_ctx *ctx, cudaStream_t st);
 
 // host helpers
+int zb_configure(zb_ctx *ctx, const zb_params *p);
+void zb_init_cells(zb_ctx *ctx, int r, float kft);
+int zb_finish_readback(zb_ctx *ctx, zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps_out, int timing, cudaStream_t st);
 void zb_host_ran1_stream(double *out, int n);
 void zb_host_basis(const zb_params *p, double *kvec, double *fx, double *fy, int *ren);
 

@@ -13,13 +13,13 @@
 __global__ void __launch_bounds__(256)
 k_input_mask(const ZbDev *__restrict__ D, const float *__restrict__ sci, const float *__restrict__ ref,
              const void *__restrict__ smask, int sdt, const void *__restrict__ tmask, int tdt,
-             int32_t *__restrict__ m_in)
+             int32_t *__restrict__ m_in, int y_lo, int y_hi)
 {
     const ZbRegion R = D->reg[blockIdx.z];
     const float fill = D->p.fill_val;
     const float tU = D->tU, tL = D->tL, iU = D->iU, iL = D->iL;
     int y = blockIdx.y;
-    if (y >= R.rpy) return;
+    if (y >= R.rpy || y < y_lo || y >= y_hi) return;          // [y_lo, y_hi): row-tile window (whole region: 0 .. INT_MAX)
     for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < R.rpx; x += gridDim.x * blockDim.x) {
         long long g = (long long)(R.by0 + y) * D->nx + (R.bx0 + x);
         float t = ref[g], i = sci[g];
@@ -39,12 +39,12 @@ k_input_mask(const ZbDev *__restrict__ D, const float *__restrict__ sci, const f
 // One CTA = TILE x TILE output pixels; the bad flags of the tile + halo are staged in shared
 // memory and OR-reduced separably (rows, then columns).
 __global__ void __launch_bounds__(TILE * 8)
-k_spread_mask(const ZbDev *__restrict__ D, int32_t *__restrict__ m_in, int w2, int sborder)
+k_spread_mask(const ZbDev *__restrict__ D, int32_t *__restrict__ m_in, int w2, int sborder, int y_lo, int y_hi)
 {
     extern __shared__ unsigned char sm[];
     const ZbRegion R = D->reg[blockIdx.z];
     const int x0 = blockIdx.x * TILE, y0 = blockIdx.y * TILE;
-    if (x0 >= R.rpx || y0 >= R.rpy) return;
+    if (x0 >= R.rpx || y0 >= R.rpy || y0 >= y_hi || y0 + TILE <= y_lo) return;
     const int tw = TILE + 2 * w2;
     unsigned char *bad = sm;                 // [tw][tw]
     unsigned char *rowor = sm + tw * tw;     // [tw][TILE]
@@ -54,7 +54,7 @@ k_spread_mask(const ZbDev *__restrict__ D, int32_t *__restrict__ m_in, int w2, i
         int ty = k / tw, tx = k - ty * tw;
         int x = x0 + tx - w2, y = y0 + ty - w2;
         unsigned char b = 0;
-        if (x >= 0 && x < R.rpx && y >= 0 && y < R.rpy) b = (m[(long long)y * R.rpx + x] & ZB_FLAG_INPUT_ISBAD) ? 1 : 0;
+        if (x >= 0 && x < R.rpx && y >= max(0, y_lo) && y < min(R.rpy, y_hi)) b = (m[(long long)y * R.rpx + x] & ZB_FLAG_INPUT_ISBAD) ? 1 : 0;
         bad[k] = b;
     }
     __syncthreads();
@@ -68,7 +68,7 @@ k_spread_mask(const ZbDev *__restrict__ D, int32_t *__restrict__ m_in, int w2, i
     for (int k = tid; k < TILE * TILE; k += nt) {
         int ty = k / TILE, tx = k - ty * TILE;
         int x = x0 + tx, y = y0 + ty;
-        if (x >= R.rpx || y >= R.rpy) continue;
+        if (x >= R.rpx || y >= R.rpy || y < y_lo || y >= y_hi) continue;
         unsigned char b = 0;
         for (int d = 0; d <= 2 * w2; d++) b |= rowor[(ty + d) * TILE + tx];
         int v = m[(long long)y * R.rpx + x];
@@ -81,11 +81,11 @@ k_spread_mask(const ZbDev *__restrict__ D, int32_t *__restrict__ m_in, int w2, i
 }
 
 int zb_launch_input_mask(zb_ctx *ctx, const float *sci, const float *ref, const void *smask, int sdt,
-                         const void *tmask, int tdt, cudaStream_t st)
+                         const void *tmask, int tdt, cudaStream_t st, int y_lo, int y_hi)
 {
     const zb_sizes &sz = ctx->sz;
     dim3 g1((sz.max_rpix_x + 255) / 256, sz.max_rpix_y, sz.n_regions);
-    k_input_mask<<<g1, 256, 0, st>>>(ctx->d_dev, sci, ref, smask, sdt, tmask, tdt, ctx->d_min); ZB_DBG("k_input_mask");
+    k_input_mask<<<g1, 256, 0, st>>>(ctx->d_dev, sci, ref, smask, sdt, tmask, tdt, ctx->d_min, y_lo, y_hi); ZB_DBG("k_input_mask");
     ctx->launches++;
     int width = (int)(ctx->p.hw_kernel * ctx->p.kf_spread_mask1);
     int w2 = width > 0 ? width / 2 : 0;
@@ -95,7 +95,7 @@ int zb_launch_input_mask(zb_ctx *ctx, const float *sci, const float *ref, const 
     if (smem > 48 * 1024) cudaFuncSetAttribute(k_spread_mask, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
     dim3 g2((sz.max_rpix_x + TILE - 1) / TILE, (sz.max_rpix_y + TILE - 1) / TILE, sz.n_regions);
     // width <= 0: spreadMask returns at once (functions.c:1362-1364) but the frame is still drawn
-    k_spread_mask<<<g2, dim3(TILE, 8), smem, st>>>(ctx->d_dev, ctx->d_min, width > 0 ? w2 : 0, sz.s_border); ZB_DBG("k_spread_mask");
+    k_spread_mask<<<g2, dim3(TILE, 8), smem, st>>>(ctx->d_dev, ctx->d_min, width > 0 ? w2 : 0, sz.s_border, y_lo, y_hi); ZB_DBG("k_spread_mask");
     ctx->launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "input mask kernels", __FILE__, __LINE__);
