@@ -223,6 +223,7 @@ extern "C" void zb_destroy(zb_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     free_workspace(ctx);
     for (int i = 0; i < 9; i++) if (ctx->d_stage[i]) cudaFree(ctx->d_stage[i]);
+    if (ctx->d_search_scratch) cudaFree(ctx->d_search_scratch);
     for (int i = 0; i <= ZB_NSTAGES; i++) cudaEventDestroy(ctx->ev[i]);
     cudaStreamDestroy(ctx->stream);
     delete ctx;

@@ -126,6 +126,7 @@ struct zb_ctx {
     double  *d_ran;  int n_ran;  // ran1 stream, seed -666 (functions.c:811)
     double  *d_fx, *d_fy, *d_kvec; int *d_ren;   // basis (alard.c:134-197)
     ZbCell  *d_cells, *h_cells; int n_cells;
+    unsigned char *d_search_scratch; size_t search_scratch_bytes;   // stamps larger than shared memory (zb_stamps.cu)
     ZbStamp *d_stamps, *h_stamps; int n_slots;
     double  *d_vec;              // [slot][nvec][npix]
     double  *d_kref;             // [slot][npix]

@@ -218,9 +218,13 @@ __device__ static void qsort_idx(const double *v, int *idx, int n) {
 
 __global__ void __launch_bounds__(NT)
 k_stamp_search(const ZbDev *__restrict__ D, const float *__restrict__ img, int32_t *__restrict__ m_in,
-               ZbCell *__restrict__ cells, int first_cell, const double *__restrict__ ran, int n_ran)
+               ZbCell *__restrict__ cells, int first_cell, const double *__restrict__ ran, int n_ran,
+               unsigned char *__restrict__ gscratch, size_t gscratch_per_cell)
 {
-    extern __shared__ __align__(16) unsigned char dyn[];
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
+    // stamps too large for shared memory (coadd-scale frames with a coarse stamp grid) work out of a
+    // per-CTA slice of global scratch instead; same code, L1/L2-cached
+    unsigned char *dyn = gscratch ? gscratch + (size_t)blockIdx.x * gscratch_per_cell : dyn_smem;
     __shared__ Shared S;
     ZbCell &C = cells[first_cell + blockIdx.x];
     const ZbRegion R = D->reg[C.region];
@@ -419,12 +423,25 @@ int zb_launch_stamp_search(zb_ctx *ctx, const float *conv_img, int first_cell, i
     if (n_cells <= 0) return ZB_OK;
     size_t npx = (size_t)ctx->sz.fw_stamp * ctx->sz.fw_stamp;
     size_t smem = npx * (sizeof(float) + sizeof(int) + 1) + 32 + ((npx + 31) / 32) * sizeof(unsigned);
+    unsigned char *gs = NULL;
+    size_t per = 0;
     if (smem > ZB_SMEM_OPTIN) {
-        snprintf(ctx->err, sizeof ctx->err, "stamp of %d x %d pixels does not fit shared memory", ctx->sz.fw_stamp, ctx->sz.fw_stamp);
-        return ZB_ERR_UNSUPPORTED;
+        per = (smem + 255) & ~(size_t)255;
+        const size_t need = per * (size_t)ctx->n_cells;
+        if (ctx->search_scratch_bytes < need) {
+            cudaStreamSynchronize(st);
+            if (ctx->d_search_scratch) cudaFree(ctx->d_search_scratch);
+            ctx->d_search_scratch = NULL; ctx->search_scratch_bytes = 0;
+            if (cudaMalloc((void **)&ctx->d_search_scratch, need) != cudaSuccess) {
+                snprintf(ctx->err, sizeof ctx->err, "cudaMalloc of %zu bytes of stamp-search scratch failed (stamps of %d x %d pixels)", need, ctx->sz.fw_stamp, ctx->sz.fw_stamp);
+                return ZB_ERR_NOMEM;
+            }
+            ctx->search_scratch_bytes = need;
+        }
+        gs = ctx->d_search_scratch; smem = 0;
     }
     cudaFuncSetAttribute(k_stamp_search, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
-    k_stamp_search<<<n_cells, NT, smem, st>>>(ctx->d_dev, conv_img, ctx->d_min, ctx->d_cells, first_cell, ctx->d_ran, ctx->n_ran); ZB_DBG("k_stamp_search");
+    k_stamp_search<<<n_cells, NT, smem, st>>>(ctx->d_dev, conv_img, ctx->d_min, ctx->d_cells, first_cell, ctx->d_ran, ctx->n_ran, gs, per); ZB_DBG("k_stamp_search");
     ctx->launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "k_stamp_search", __FILE__, __LINE__);
