@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--profile", action="store_true", help="one extra step with a stream sync at every phase boundary")
     ap.add_argument("--shape", type=int, nargs=2, default=None)
     a = ap.parse_args()
     import torch
@@ -96,6 +97,21 @@ def main():
                 dist.all_reduce(ms, op=dist.ReduceOp.MAX)
             if it >= a.warmup:
                 times.append(float(ms.item()))
+        prof = None
+        if a.profile:
+            if world > 1:
+                for t, q in zip(mine, pristine):
+                    if t is not None:
+                        t.copy_(q)
+                st.synchronize()
+                dist.barrier()
+                ps = {"profile": True}
+                tiles.subtract_tiled(ctx, comm, p, *mine, stats=ps)
+                allp = [None] * world
+                dist.all_gather_object(allp, ps.get("phases_ms"))
+                prof = allp
+            else:
+                prof = [{k: round(v, 3) for k, v in ctx.timings().items()}]
         ok = None
         if a.check and rank == 0:
             full = [None if arr is None else torch.from_numpy(np.ascontiguousarray(arr.view(np.uint8) if arr.dtype == np.bool_ else arr)).to(dev) for arr in ins]
@@ -114,7 +130,7 @@ def main():
                            "tiles": [i.as_dict() for i in infos] if world > 1 else None,
                            "collectives": "P2P halo rows (inputs, then search-claimed mask rows), all-reduce(SUM) of search records / per-stamp Gram+rhs / per-stamp sigma, gather of output rows on rank 0"},
                 "n_stamps": int(res.regions[0].n_stamps), "fit_iters": int(res.regions[0].fit_iters),
-                "tile_stats_rank0": {k: v for k, v in stats.items() if k != "info"}, "bit_equal_to_single_gpu": ok,
+                "tile_stats_rank0": {k: v for k, v in stats.items() if k != "info"}, "bit_equal_to_single_gpu": ok, "phases_ms_per_rank": prof,
                 "synth_s": round(t_synth, 1)}
         print(json.dumps(line), flush=True)
     if world > 1:

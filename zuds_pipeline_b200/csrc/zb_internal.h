@@ -75,7 +75,8 @@ struct ZbFit {
 
 // Region QA statistics (main.c:1479-1554): four getStampStats3 runs per region, advanced in lock
 // step by whole-grid passes over the region (zb_stats.cu).
-#define ZB_QA_NBLK 64
+#define ZB_QA_NBLK 256          // stride of the per-CTA partial sums (max CTAs per region)
+#define ZB_QA_NBLK_MIN 64
 struct ZbQaStat {
     int phase;                   // 0 sigma-clip passes, 1 histogram passes, 2 done
     int status;                  // getStampStats3 return code

@@ -223,20 +223,20 @@ __device__ static bool qa_interval(double mean, double istd, float sig, float &l
 // The sequential decisions of sigma_clip (functions.c:1037-1107) and of the re-binning loop
 // (functions.c:879-1031) for one (region, stat); s == 4 finishes getNoiseStats3 on the first pass.
 // Runs in the last CTA of a pass to finish (see k_qa_pass).
-__device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *part /* [5][ZB_QA_NBLK] */, double *q, int r, int s, int first, const int *bins)
+__device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *part /* [5][ZB_QA_NBLK] */, int nblk, double *q, int r, int s, int first, const int *bins)
 {
     const ZbQaPart *P = part + s * ZB_QA_NBLK;          // this region's partial sums, staged in shared memory
     double s1 = 0, s2 = 0; long long n = 0;
     if (s == 4) {
         if (!first) return;
-        for (int b = 0; b < ZB_QA_NBLK; b++) { s1 += P[b].s1; n += P[b].n; }
+        for (int b = 0; b < nblk; b++) { s1 += P[b].s1; n += P[b].n; }
         q[(long long)r * 64 + 3] = (double)n;
         q[(long long)r * 64 + 2] = (n > 1) ? s1 / (float)n : ZB_MAXVAL;
         return;
     }
     ZbQaStat &Q = qa[r * 4 + s];
     if (Q.phase == 2) return;
-    for (int b = 0; b < ZB_QA_NBLK; b++) { s1 += P[b].s1; s2 += P[b].s2; n += P[b].n; }
+    for (int b = 0; b < nblk; b++) { s1 += P[b].s1; s2 += P[b].s2; n += P[b].n; }
     const int ncnt = (int)n;
     const float sig = D->p.stat_sig;
     if (Q.phase == 0) {
@@ -313,7 +313,8 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
                         const unsigned peers = __match_any_sync(__activemask(), index); \
                         if ((int)(__ffs(peers) - 1) == (threadIdx.x & 31)) atomicAdd(&S.bins[s][index], __popc(peers)); \
                         a1[s] += fabs((double)(xv)); an[s]++; } } } } } while (0)
-    const int stride = ZB_QA_NBLK * 256;
+    const int nblk = gridDim.x;                     // CTAs per region: ZB_QA_NBLK_MIN .. ZB_QA_NBLK (zb_launch_region_stats)
+    const int stride = nblk * 256;
     for (int kb = blockIdx.x * 256 + tid; kb < npix; kb += 4 * stride) {
         float dv[4], nv[4]; int mv[4];
 #pragma unroll
@@ -386,7 +387,7 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
     // the last CTA of this region to get here takes the decisions for the next pass
     __threadfence();
     __syncthreads();
-    if (tid == 0) s_last = (atomicAdd(&qa[r * 4].ticket, 1) == ZB_QA_NBLK - 1);
+    if (tid == 0) s_last = (atomicAdd(&qa[r * 4].ticket, 1) == nblk - 1);
     __syncthreads();
     if (!s_last) return;
     __threadfence();
@@ -397,7 +398,7 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
         s_part[k].s1 = __ldcg(&g->s1); s_part[k].s2 = __ldcg(&g->s2); s_part[k].n = __ldcg(&g->n);
     }
     __syncthreads();
-    if (tid < 5) qa_decide(D, qa, s_part, q, r, tid, first, tid < 4 ? S.bins[tid] : S.bins[0]);
+    if (tid < 5) qa_decide(D, qa, s_part, nblk, q, r, tid, first, tid < 4 ? S.bins[tid] : S.bins[0]);
     if (tid == 0) qa[r * 4].ticket = 0;
 }
 
@@ -440,9 +441,13 @@ int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStr
     const int nR = ctx->sz.n_regions;
     k_qa_sample<<<dim3(4, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, ctx->d_qa, ctx->d_ran, ctx->n_ran); ZB_DBG("k_qa_sample");
     ctx->launches++;
-    // at most maxiter (5) clip passes + 5 histogram passes; finished regions fall through at once
+    // at most maxiter (5) clip passes + 5 histogram passes; finished regions fall through at once.
+    // CTAs per region: enough to put ~4 CTAs on every SM whatever the number of regions (a single-region
+    // coadd-scale frame would otherwise stream 38 Mpx through 64 CTAs)
+    int nblk = nR >= 5 ? ZB_QA_NBLK_MIN : (4 * 148 + nR - 1) / nR;
+    nblk = nblk < ZB_QA_NBLK_MIN ? ZB_QA_NBLK_MIN : (nblk > ZB_QA_NBLK ? ZB_QA_NBLK : nblk);
     for (int pass = 0; pass < 10; pass++) {
-        k_qa_pass<<<dim3(ZB_QA_NBLK, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
+        k_qa_pass<<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
                                                         ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0); ZB_DBG("k_qa_pass");
         ctx->launches++;
     }

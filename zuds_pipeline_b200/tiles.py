@@ -233,6 +233,20 @@ def subtract_tiled(ctx, comm, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=
     if stream.cuda_stream == 0:
         raise ValueError("subtract_tiled must run under a non-default torch.cuda.stream (the C ABI treats stream 0 as 'use the context stream')")
     moved = [0, 0]
+    profile = bool(stats is not None and stats.get("profile"))
+    phases, t_last = {}, [0.0]
+    if profile:
+        import time
+        stream.synchronize()
+        t_last[0] = time.perf_counter()
+
+    def mark(name):
+        """profile mode only: wall-clock per phase with a stream sync at each boundary (perturbs the run)"""
+        if profile:
+            stream.synchronize()
+            t = time.perf_counter()
+            phases[name] = phases.get(name, 0.0) + (t - t_last[0]) * 1e3
+            t_last[0] = t
 
     def count(sr):
         moved[0] += sr[0]
@@ -246,6 +260,7 @@ def subtract_tiled(ctx, comm, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=
 
     if exchange_inputs and world > 1:
         count(exchange_rows([sci, ref, sci_rms, ref_rms, sci_mask, ref_mask], infos, rank, comm))
+    mark("halo_inputs")
     diff = torch.empty((ny, nx), dtype=torch.float32, device=dev)
     noise = torch.empty((ny, nx), dtype=torch.float32, device=dev)
     mask = torch.empty((ny, nx), dtype=torch.int32, device=dev)
@@ -253,6 +268,7 @@ def subtract_tiled(ctx, comm, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=
     _chk(ctx, lib.zb_tile_begin(h, C.byref(p), world, rank, ptr(sci), ptr(ref), ptr(sci_rms), ptr(ref_rms),
                                ptr(sci_mask), md(sci_mask), ptr(ref_mask), md(ref_mask),
                                ptr(diff), ptr(noise), ptr(mask), C.c_void_p(stream.cuda_stream)))
+    mark("mask+search")
     # ---- stamp search records: merge, replicated stale-slot walk / retry (main.c:909-998)
     words = np.zeros(me.n_cells * me.cell_words, np.int32)
     action, cell = C.c_int(0), C.c_int(-1)
@@ -274,6 +290,7 @@ def subtract_tiled(ctx, comm, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=
             _chk(ctx, lib.zb_tile_begin_retry(h))
         if rounds > 4 * me.n_cells + 8:
             raise _lib.ZbError(-5, "stamp resolve did not converge")
+    mark("merge_records+resolve")
     # ---- the search wrote claim bits into the mask rows of its stamps: refresh the halo rows
     scratch_i = torch.empty((ny, nx), dtype=torch.int32, device=dev)
     if world > 1:
@@ -282,8 +299,10 @@ def subtract_tiled(ctx, comm, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=
         for a, b in ((me.in_row0, me.row0), (me.row1, me.in_row1)):
             if b > a:
                 _chk(ctx, lib.zb_tile_rows(h, TILE_MASK_IN, 1, a, b, ptr(scratch_i[a:b])))
+    mark("halo_mask")
     # ---- fit loop (alard.c:316-381): per-stamp terms merged, global system replicated
     _chk(ctx, lib.zb_tile_fill(h))
+    mark("fill")
     gram = torch.empty(me.n_slots * me.gram_len, dtype=torch.float64, device=dev)
     rhs = torch.empty(me.n_slots * me.rhs_len, dtype=torch.float64, device=dev)
     sig = torch.empty(me.n_slots, dtype=torch.float64, device=dev)
@@ -295,17 +314,22 @@ def subtract_tiled(ctx, comm, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=
             comm.all_reduce_sum(gram)
             comm.all_reduce_sum(rhs)
             _chk(ctx, lib.zb_tile_normal_import(h, ptr(gram), ptr(rhs)))
+        mark("allreduce_normal")
         _chk(ctx, lib.zb_tile_solve(h))
+        mark("solve+sig")
         if world > 1:
             _chk(ctx, lib.zb_tile_sig_export(h, ptr(sig)))
             comm.all_reduce_sum(sig)
             _chk(ctx, lib.zb_tile_sig_import(h, ptr(sig)))
+        mark("allreduce_sig")
         _chk(ctx, lib.zb_tile_clip(h, C.byref(active)))
+        mark("clip+refill")
         iters += 1
         if iters > 4 * me.n_slots * 8:
             raise _lib.ZbError(-5, "fit loop did not converge")
     # ---- fused convolution / output pass on the rank's block rows
     _chk(ctx, lib.zb_tile_convolve(h))
+    mark("convolve")
     # ---- gather rows on rank 0: the three products and the three pre-masking arrays the QA statistics read
     if world > 1:
         scratch_f = [torch.empty((ny, nx), dtype=torch.float32, device=dev) for _ in range(2)]
@@ -330,13 +354,19 @@ def subtract_tiled(ctx, comm, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=
             lo = infos[0].out_row1
             for which, buf in work:
                 _chk(ctx, lib.zb_tile_rows(h, which, 1, lo, ny, ptr(buf[lo:ny])))
+    mark("gather")
     if stats is not None:
         stats.update(fit_iters=iters, resolve_rounds=rounds, sent_bytes=moved[0], recv_bytes=moved[1], info=me.as_dict())
     if rank != 0:
         stream.synchronize()
+        if profile:
+            stats["phases_ms"] = {k: round(v, 3) for k, v in phases.items()}
         return None
     r = ctx._outputs(p)
     _chk(ctx, lib.zb_tile_finish(h, r.regions, r.sol.ctypes.data_as(C.c_void_p), r.stamps))
+    mark("qa_stats")
+    if profile:
+        stats["phases_ms"] = {k: round(v, 3) for k, v in phases.items()}
     r.diff, r.noise, r.mask = diff, noise, mask
     return r
 
