@@ -293,6 +293,24 @@ def bench_b200(args):
     h1.record()
     barrier()
     host_s = h0.elapsed_time(h1) / 1e3
+    # ---- the host link, measured alone: what bounds e2e when the copies cannot hide behind compute
+    link = {}
+    try:
+        hb = torch.empty(256 << 20, dtype=torch.uint8).pin_memory()
+        db = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        for name, src, dst in (("h2d_gbs", hb, db), ("d2h_gbs", db, hb)):
+            best = 0.0
+            for _ in range(4):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                dst.copy_(src, non_blocking=True)
+                b.record()
+                b.synchronize()
+                best = max(best, hb.numel() / (a.elapsed_time(b) * 1e-3) / 1e9)
+            link[name] = round(best, 2)
+        del hb, db
+    except RuntimeError as e:          # pinned allocation refused: report, do not fail the bench
+        link = {"error": str(e)[:120]}
     # ---- the convolution kernel alone, one context, nothing else on the GPU (roofline)
     serial_ms = []
     for i in range(6):
@@ -320,7 +338,10 @@ def bench_b200(args):
                    "pairs_per_step_per_gpu": B, "contexts_per_gpu": W, "distinct_pairs_per_gpu": npairs_distinct,
                    "l2": "inputs of one pair are 161 MB (> 126 MB L2) and consecutive jobs alternate pairs",
                    "sharding": "by image pair, no collective"},
-        "e2e": {"value": pairs_total / host_s, "unit": UNIT, "h2d_bytes_per_step": in_bytes * B, "d2h_bytes_per_step": out_bytes * B},
+        "e2e": {"value": pairs_total / host_s, "unit": UNIT, "h2d_bytes_per_step": in_bytes * B, "d2h_bytes_per_step": out_bytes * B,
+                "host_link": link,
+                "link_bound_pairs_per_s": (round(min(link["h2d_gbs"] * 1e9 / in_bytes, link["d2h_gbs"] * 1e9 / out_bytes), 1)
+                                           if "h2d_gbs" in link else None)},
         "gpu_launches": launches,
         "clocks": clk,
         "roofline": {"kernel": "k_convolve", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
@@ -357,8 +378,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workers", type=int, default=4, help="concurrent contexts (streams) per GPU")
-    ap.add_argument("--batch", type=int, default=8, help="pair subtractions per step per GPU")
+    ap.add_argument("--workers", type=int, default=8, help="concurrent contexts (streams) per GPU")
+    ap.add_argument("--batch", type=int, default=32, help="pair subtractions per step per GPU")
     ap.add_argument("--cpu-procs", type=int, default=0, help="reference arm: concurrent hotpants processes (0 = all cores)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-clocks", action="store_true", help="(diagnostics) do not sample clocks during the timed region")

@@ -15,6 +15,7 @@
 // each thread keeps TX adjacent outputs in registers and slides a register window along the
 // kernel row so that one shared-memory load feeds up to TX DFMAs.
 #include "zb_internal.h"
+#include <stdlib.h>
 #include <type_traits>
 
 
@@ -558,13 +559,15 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
     // reserved per CTA), else one CTA with as many blocks as fit; among equals the squarer tile (less halo)
     int NBX = 1, NBY = 1, W = 0, TH = 0, threads = 0; size_t smem = 0;
     {
-        const size_t cap2 = (233472 - 2 * 1024) / 2;
+        static int env_nb = -1, env_ctas = 2;
+        if (env_nb < 0) { const char *e = getenv("ZB_CONV_NB"); env_nb = e ? atoi(e) : 0; e = getenv("ZB_CONV_CTAS"); env_ctas = e ? atoi(e) : 2; if (env_ctas < 1) env_ctas = 2; }
+        const size_t cap2 = (233472 - (size_t)env_ctas * 1024) / env_ctas;
         auto shape = [&](int bxn, int by, int *w, int *th) -> size_t {
             int ww = (bxn - 1) * B + GX * TXr + fwp - 1; while ((TYr * ww) % 8 != 1) ww++;   // conflict-free row-group stride
             *w = ww; *th = (by - 1) * B + GY * TYr + fw - 1;
             return (size_t)*th * ww * sizeof(double2) + (size_t)bxn * by * fw * fwp * sizeof(double) + 2 * (size_t)*th * ww;
         };
-        const int target = 128 / tpb > 0 ? 128 / tpb : 1;
+        const int target = env_nb > 0 ? env_nb : (128 / tpb > 0 ? 128 / tpb : 1);
         long best = -1;
         for (int pass = 0; pass < 2 && best < 0; pass++)
             for (int nb = target; nb >= 1 && best < 0; nb--)

@@ -11,6 +11,7 @@
 // loop termination, histogram re-binning).  HBM/L2-bound streaming: 12 bytes per pixel per pass.
 // Block partial sums are combined in block order, so results are deterministic.
 #include "zb_internal.h"
+#include <stdlib.h>
 #include "zb_hist.cuh"
 
 // ------------------------------------------------------------------ FSIG / FSCAT
@@ -273,7 +274,8 @@ __device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *p
     if (Q.tries >= 5) { Q.status = 1; Q.phase = 2; }
 }
 
-__global__ void __launch_bounds__(256)
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB)
 k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const float *__restrict__ rnoise,
           int32_t *__restrict__ omask, int32_t *__restrict__ out_mask, ZbQaStat *qa,
           ZbQaPart *part, double *__restrict__ q, int first)
@@ -444,11 +446,18 @@ int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStr
     // at most maxiter (5) clip passes + 5 histogram passes; finished regions fall through at once.
     // CTAs per region: enough to put ~4 CTAs on every SM whatever the number of regions (a single-region
     // coadd-scale frame would otherwise stream 38 Mpx through 64 CTAs)
+    static int minb = 0;
+    if (!minb) { const char *e = getenv("ZB_QA_MINB"); minb = e ? atoi(e) : 2; }
     int nblk = nR >= 5 ? ZB_QA_NBLK_MIN : (4 * 148 + nR - 1) / nR;
     nblk = nblk < ZB_QA_NBLK_MIN ? ZB_QA_NBLK_MIN : (nblk > ZB_QA_NBLK ? ZB_QA_NBLK : nblk);
     for (int pass = 0; pass < 10; pass++) {
-        k_qa_pass<<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
-                                                        ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0); ZB_DBG("k_qa_pass");
+        if (minb == 3) k_qa_pass<3><<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
+                                                                   ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0);
+        else if (minb == 4) k_qa_pass<4><<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
+                                                                   ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0);
+        else k_qa_pass<2><<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
+                                                         ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0);
+        ZB_DBG("k_qa_pass");
         ctx->launches++;
     }
     k_qa_finish<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_qa, ctx->d_stats); ZB_DBG("k_qa_finish");
