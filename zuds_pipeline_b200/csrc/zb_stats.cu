@@ -317,6 +317,15 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
                         a1[s] += fabs((double)(xv)); an[s]++; } } } } } while (0)
     const int nblk = gridDim.x;                     // CTAs per region: ZB_QA_NBLK_MIN .. ZB_QA_NBLK (zb_launch_region_stats)
     const int stride = nblk * 256;
+    // every statistic either finished (empty interval: nothing is kept, its sums are not used) or in a clip pass
+    bool fast = true;
+    float f_lo[4], f_hi[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        fast &= S.phase[q] == 2 || (S.phase[q] == 0 && !S.exact[q]);
+        f_lo[q] = S.phase[q] == 2 ? __int_as_float(0x7f800000) : S.flo[q];
+        f_hi[q] = S.phase[q] == 2 ? __int_as_float(0xff800000) : S.fhi[q];
+    }
     for (int kb = blockIdx.x * 256 + tid; kb < npix; kb += 4 * stride) {
         float dv[4], nv[4]; int mv[4];
 #pragma unroll
@@ -324,6 +333,40 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
             const int k = kb + u * stride;
             if (k < npix) { dv[u] = rdiff[R.off + k]; nv[u] = rnoise[R.off + k]; mv[u] = omask[R.off + k]; }
             else { dv[u] = 0.f; nv[u] = 0.f; mv[u] = 0xffff; }      // excluded from everything
+        }
+        // Common case — every statistic either finished or in a clip pass with a float interval, every
+        // value of the batch finite: branch-light code with the interval ends in registers.  It adds the
+        // same terms to the same per-thread sums in the same order as the generic code below (a rejected
+        // pixel adds 0.0), so the two paths are interchangeable bit for bit.
+        bool nonfinite = false;
+#pragma unroll
+        for (int u = 0; u < 4; u++) nonfinite |= (dv[u] * 0.0f != 0.0f) || (nv[u] * 0.0f != 0.0f);
+        if (fast && !nonfinite) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const float d = dv[u], nz = nv[u];
+                const int m0 = mv[u];
+                const bool good = (m0 & 0xffff) == 0;
+                const bool okp = !good && (m0 & 0xff) && !(m0 & ZB_FLAG_OUTPUT_ISBAD);
+                if (!(good || okp)) continue;
+                const double dd = (double)d, dn = (double)nz;
+                const double d2 = (double)(d * d), n2 = (double)(nz * nz);
+                const bool usable_d = !(fabs(dd) <= ZB_ZEROVAL), usable_n = !(fabs(dn) <= ZB_ZEROVAL);
+                if (good) {
+                    if (first && !(fabsf(d) < 1e-10f)) {        // getNoiseStats3, functions.c:719-761
+                        float ndat = (float)(1. / nz);
+                        nn++; nsum += (double)(d * d * ndat * ndat);
+                    }
+                    const bool kd = usable_d && !(d < f_lo[0] || d > f_hi[0]), kn = usable_n && !(nz < f_lo[1] || nz > f_hi[1]);
+                    a1[0] += kd ? dd : 0.0; a2[0] += kd ? d2 : 0.0; an[0] += kd;
+                    a1[1] += kn ? dn : 0.0; a2[1] += kn ? n2 : 0.0; an[1] += kn;
+                } else {
+                    const bool kd = usable_d && !(d < f_lo[2] || d > f_hi[2]), kn = usable_n && !(nz < f_lo[3] || nz > f_hi[3]);
+                    a1[2] += kd ? dd : 0.0; a2[2] += kd ? d2 : 0.0; an[2] += kd;
+                    a1[3] += kn ? dn : 0.0; a2[3] += kn ? n2 : 0.0; an[3] += kn;
+                }
+            }
+            continue;
         }
 #pragma unroll
         for (int u = 0; u < 4; u++) {
