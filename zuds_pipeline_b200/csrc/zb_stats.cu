@@ -490,7 +490,7 @@ int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStr
     // CTAs per region: enough to put ~4 CTAs on every SM whatever the number of regions (a single-region
     // coadd-scale frame would otherwise stream 38 Mpx through 64 CTAs)
     static int minb = 0;
-    if (!minb) { const char *e = getenv("ZB_QA_MINB"); minb = e ? atoi(e) : 2; }
+    if (!minb) { const char *e = getenv("ZB_QA_MINB"); minb = e ? atoi(e) : 3; }
     int nblk = nR >= 5 ? ZB_QA_NBLK_MIN : (4 * 148 + nR - 1) / nR;
     nblk = nblk < ZB_QA_NBLK_MIN ? ZB_QA_NBLK_MIN : (nblk > ZB_QA_NBLK ? ZB_QA_NBLK : nblk);
     for (int pass = 0; pass < 10; pass++) {
