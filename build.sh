@@ -15,7 +15,8 @@ nvcc $COMMON -fmad=false -c zb_fit.cu    -o ../../build/zb_fit.o &
 nvcc $COMMON             -c zb_conv.cu   -o ../../build/zb_conv.o &
 nvcc $COMMON -fmad=false -c zb_stats.cu  -o ../../build/zb_stats.o &
 nvcc $COMMON -fmad=false -c zb_tile.cu   -o ../../build/zb_tile.o &
+nvcc $COMMON -fmad=false -c zb_bkg.cu    -o ../../build/zb_bkg.o &
 wait
 nvcc $ARCH -shared -o ../libzb200.so ../../build/zb_host.o ../../build/zb_mask.o ../../build/zb_stamps.o \
-     ../../build/zb_fit.o ../../build/zb_conv.o ../../build/zb_stats.o ../../build/zb_tile.o -lcudart
+     ../../build/zb_fit.o ../../build/zb_conv.o ../../build/zb_stats.o ../../build/zb_tile.o ../../build/zb_bkg.o -lcudart
 echo "built zuds_pipeline_b200/libzb200.so"

@@ -187,6 +187,18 @@ long long zb_launch_count(const zb_ctx *ctx);
 int zb_abi_sizeof(int which);
 
 /* ------------------------------------------------------------------------------------------
+ * Wrapper pre-step on the GPU: zuds.utils.quick_background_estimate, zuds/utils.py:32-53.
+ *   bkg = median(data[mask == 0]);  bkgstd = 1.4826 * median(|data[mask == 0] - bkg|)
+ * float32 pixels promoted to float64, the two central values of an even count averaged (np.median);
+ * NaN when nothing is unmasked or an unmasked pixel is NaN.  Exact order statistics (radix selection),
+ * so the -il/-tl thresholds zuds derives from them are identical to the host computation.
+ * mask may be NULL (every pixel used); n = number of pixels. */
+int zb_background_estimate(zb_ctx *ctx, const float *data /* device */, const void *mask /* device */, int mask_dtype,
+                           long long n, double *bkg, double *bkgstd, void *stream);
+int zb_background_estimate_host(zb_ctx *ctx, const float *data /* host */, const void *mask /* host */, int mask_dtype,
+                                long long n, double *bkg, double *bkgstd);
+
+/* ------------------------------------------------------------------------------------------
  * Row-tile sessions: ONE oversized frame fitted by a single region (nreg_x == nreg_y == 1,
  * BASELINE.json configs[4]) split over `world` GPUs by image rows, one process (rank) per GPU.
  * The reference has no counterpart (one single-threaded process per frame, zuds/mpi.py:36-64);

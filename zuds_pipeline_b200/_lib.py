@@ -20,7 +20,9 @@ EXPORTS = ("zb_version", "zb_params_default", "zb_params_check", "zb_sizes_of", 
            "zb_tile_plan", "zb_tile_begin", "zb_tile_begin_retry", "zb_tile_cells_export", "zb_tile_cells_import",
            "zb_tile_resolve", "zb_tile_research", "zb_tile_rows", "zb_tile_fill", "zb_tile_normal_export",
            "zb_tile_normal_import", "zb_tile_solve", "zb_tile_sig_export", "zb_tile_sig_import", "zb_tile_clip",
-           "zb_tile_convolve", "zb_tile_finish")
+           "zb_tile_convolve", "zb_tile_finish",
+           # wrapper pre-step (zuds.utils.quick_background_estimate)
+           "zb_background_estimate", "zb_background_estimate_host")
 
 
 class ZbError(RuntimeError):
@@ -58,6 +60,9 @@ def load():
     lib.zb_stage_name.restype = C.c_char_p
     lib.zb_launch_count.argtypes = [vp]
     lib.zb_launch_count.restype = C.c_longlong
+    dp = C.POINTER(C.c_double)
+    lib.zb_background_estimate.argtypes = [vp, vp, vp, C.c_int, C.c_longlong, dp, dp, vp]
+    lib.zb_background_estimate_host.argtypes = [vp, vp, vp, C.c_int, C.c_longlong, dp, dp]
     _lib = lib
     return lib
 
@@ -119,6 +124,40 @@ class Context:
         r.sol = np.zeros((sz.n_regions, sz.n_comp_total + 1), np.float64)
         r.stamps = (P.ZbStampInfo * (sz.n_regions * sz.n_stamps))()
         return r
+
+    def background_estimate(self, data, mask=None):
+        """zuds.utils.quick_background_estimate (zuds/utils.py:32-53) on the GPU: (median, 1.4826 x MAD) of
+        the pixels whose mask value is zero, as Python floats.  ``data``/``mask``: numpy arrays (copied
+        to the device inside the call) or torch CUDA tensors (only data_ptr() crosses the C ABI)."""
+        bkg, std = C.c_double(), C.c_double()
+        if isinstance(data, np.ndarray):
+            d = np.ascontiguousarray(data, np.float32)
+            m, dt = None, 0
+            if mask is not None:
+                m = np.ascontiguousarray(mask)
+                if m.dtype == np.bool_:
+                    m = m.view(np.uint8)
+                if m.dtype.name not in MASK_DTYPES:
+                    m = m.astype(np.int32)
+                dt = MASK_DTYPES[m.dtype.name]
+                assert m.size == d.size
+            rc = self.lib.zb_background_estimate_host(self.h, d.ctypes.data_as(C.c_void_p),
+                                                      None if m is None else m.ctypes.data_as(C.c_void_p), dt,
+                                                      d.size, C.byref(bkg), C.byref(std))
+        else:
+            import torch
+            assert data.is_cuda and data.is_contiguous() and data.dtype == torch.float32 and data.device.index == self.device
+            dt = 0
+            if mask is not None:
+                assert mask.is_cuda and mask.is_contiguous() and mask.numel() == data.numel()
+                dt = MASK_DTYPES[str(mask.dtype).replace("torch.", "")]
+            s = torch.cuda.current_stream(data.device).cuda_stream
+            rc = self.lib.zb_background_estimate(self.h, C.c_void_p(data.data_ptr()),
+                                                 None if mask is None else C.c_void_p(mask.data_ptr()), dt,
+                                                 data.numel(), C.byref(bkg), C.byref(std), C.c_void_p(s))
+        if rc != 0:
+            self._err(rc)
+        return bkg.value, std.value
 
     def subtract_host(self, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=None, ref_mask=None,
                       want_mask=True, out=None):

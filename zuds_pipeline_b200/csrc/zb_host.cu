@@ -224,6 +224,8 @@ extern "C" void zb_destroy(zb_ctx *ctx) {
     free_workspace(ctx);
     for (int i = 0; i < 9; i++) if (ctx->d_stage[i]) cudaFree(ctx->d_stage[i]);
     if (ctx->d_search_scratch) cudaFree(ctx->d_search_scratch);
+    if (ctx->d_bkg) cudaFree(ctx->d_bkg);
+    if (ctx->h_bkg) cudaFreeHost(ctx->h_bkg);
     for (int i = 0; i <= ZB_NSTAGES; i++) cudaEventDestroy(ctx->ev[i]);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -605,7 +607,7 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
 
 // ------------------------------------------------------------ host-buffer entry
 
-static int stage_buf(zb_ctx *ctx, int i, size_t bytes) {
+int zb_stage_buf(zb_ctx *ctx, int i, size_t bytes) {
     if (ctx->stage_bytes[i] >= bytes && ctx->d_stage[i]) return ZB_OK;
     if (ctx->d_stage[i]) cudaFree(ctx->d_stage[i]);
     ctx->d_stage[i] = NULL; ctx->stage_bytes[i] = 0;
@@ -632,11 +634,11 @@ extern "C" int zb_subtract_host(zb_ctx *ctx, const zb_params *p,
     const size_t esz[6] = {4, 4, 4, 4, mask_elem(sci_mask_dtype), mask_elem(ref_mask_dtype)};
     for (int i = 0; i < 6; i++) {
         if (!src[i]) continue;
-        CHECK_RC(stage_buf(ctx, i, n * esz[i]));
+        CHECK_RC(zb_stage_buf(ctx, i, n * esz[i]));
         cudaMemcpyAsync(ctx->d_stage[i], src[i], n * esz[i], cudaMemcpyHostToDevice, st);
     }
-    CHECK_RC(stage_buf(ctx, 6, n * 4)); CHECK_RC(stage_buf(ctx, 7, n * 4));
-    if (out_mask) CHECK_RC(stage_buf(ctx, 8, n * 4));
+    CHECK_RC(zb_stage_buf(ctx, 6, n * 4)); CHECK_RC(zb_stage_buf(ctx, 7, n * 4));
+    if (out_mask) CHECK_RC(zb_stage_buf(ctx, 8, n * 4));
     int rc = zb_subtract(ctx, p, (const float *)ctx->d_stage[0], (const float *)ctx->d_stage[1],
                          sci_rms ? (const float *)ctx->d_stage[2] : NULL, ref_rms ? (const float *)ctx->d_stage[3] : NULL,
                          sci_mask ? ctx->d_stage[4] : NULL, sci_mask_dtype, ref_mask ? ctx->d_stage[5] : NULL, ref_mask_dtype,

@@ -145,6 +145,7 @@ struct zb_ctx {
     double  *d_stats;  double *h_stats;   // region QA scratch
     ZbQaStat *d_qa;              // [region][4]
     ZbQaPart *d_qpart;           // [region][5][ZB_QA_NBLK]  (4 stats + getNoiseStats3)
+    void *d_bkg; double *h_bkg;  // background-estimate selection state (zb_bkg.cu)
     // staging for zb_subtract_host
     void *d_stage[9]; size_t stage_bytes[9];
     ZbTile tile;
@@ -177,6 +178,7 @@ int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStr
 int zb_launch_final_sig(zb_ctx *ctx, cudaStream_t st);
 
 // host helpers
+int zb_stage_buf(zb_ctx *ctx, int i, size_t bytes);
 int zb_configure(zb_ctx *ctx, const zb_params *p);
 void zb_init_cells(zb_ctx *ctx, int r, float kft);
 int zb_finish_readback(zb_ctx *ctx, zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps_out, int timing, cudaStream_t st);

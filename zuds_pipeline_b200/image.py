@@ -20,11 +20,16 @@ from .synth import BAD_SUM, BIG_RMS
 __all__ = ["FITSImage", "MaskImageBase", "CalibratableImageBase", "quick_background_estimate"]
 
 
-def quick_background_estimate(image, nsamp=None, mask_image=None):
+def quick_background_estimate(image, nsamp=None, mask_image=None, ctx=None):
     """zuds/utils.py:32-53.  Median and 1.4826 x MAD of the pixels whose mask value is zero, evaluated
-    in float64 (matches the reference under its pinned numpy 1.x)."""
+    in float64 (matches the reference under its pinned numpy 1.x).
+
+    ``ctx`` (a ``_lib.Context``): run it on the GPU (``zb_background_estimate_host``: exact radix
+    selection, same two numbers bit for bit); without one this is the reference's own numpy code."""
     if mask_image is None:
         mask_image = image.mask_image
+    if ctx is not None and nsamp is None:
+        return ctx.background_estimate(np.asarray(image.data), np.asarray(mask_image.data))
     bkgpix = np.asarray(image.data)[np.asarray(mask_image.data) == 0].astype(np.float64)
     if nsamp is not None:
         bkgpix = np.random.choice(bkgpix, size=nsamp)
