@@ -378,8 +378,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workers", type=int, default=8, help="concurrent contexts (streams) per GPU")
-    ap.add_argument("--batch", type=int, default=32, help="pair subtractions per step per GPU")
+    ap.add_argument("--workers", type=int, default=24, help="concurrent contexts (streams) per GPU")
+    ap.add_argument("--batch", type=int, default=96, help="pair subtractions per step per GPU")
     ap.add_argument("--cpu-procs", type=int, default=0, help="reference arm: concurrent hotpants processes (0 = all cores)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-clocks", action="store_true", help="(diagnostics) do not sample clocks during the timed region")

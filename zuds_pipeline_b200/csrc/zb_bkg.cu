@@ -168,7 +168,7 @@ static int bkg_run(zb_ctx *ctx, const float *data, const void *mask, int mdt, lo
     ctx->launches += 9;
     cudaMemcpyAsync(&ctx->h_bkg[0], &S->bkg, sizeof(double), cudaMemcpyDeviceToHost, st);
     cudaMemcpyAsync(&ctx->h_bkg[1], &S->mad, sizeof(double), cudaMemcpyDeviceToHost, st);
-    cudaError_t e = cudaStreamSynchronize(st);
+    cudaError_t e = zb_stream_wait(ctx, st);
     if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "background estimate", __FILE__, __LINE__);
     *bkg = ctx->h_bkg[0];

@@ -19,6 +19,15 @@ int zb_cuda_fail(zb_ctx *ctx, cudaError_t e, const char *what, const char *file,
     return ZB_ERR_CUDA;
 }
 
+cudaError_t zb_stream_wait(zb_ctx *ctx, cudaStream_t st) {
+    static int spin = -1;
+    if (spin < 0) { const char *e = getenv("ZB_SYNC"); spin = (e && e[0] == 'b') ? 0 : 1; }
+    if (spin || !ctx->ev_sync) return cudaStreamSynchronize(st);
+    cudaError_t e = cudaEventRecord(ctx->ev_sync, st);
+    if (e != cudaSuccess) return e;
+    return cudaEventSynchronize(ctx->ev_sync);
+}
+
 int zb_dbg_sync(zb_ctx *ctx, cudaStream_t st, const char *what) {
     static int on = -1;
     if (on < 0) { const char *e = getenv("ZB_DEBUG_SYNC"); on = (e && e[0] && e[0] != '0') ? 1 : 0; }
@@ -200,6 +209,7 @@ extern "C" int zb_create(int device, zb_ctx **out) {
     ctx->device = device;
     if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return ZB_ERR_CUDA; }
     for (int i = 0; i <= ZB_NSTAGES; i++) cudaEventCreate(&ctx->ev[i]);
+    if (cudaEventCreateWithFlags(&ctx->ev_sync, cudaEventBlockingSync | cudaEventDisableTiming) != cudaSuccess) ctx->ev_sync = NULL;
     *out = ctx;
     return ZB_OK;
 }
@@ -227,6 +237,7 @@ extern "C" void zb_destroy(zb_ctx *ctx) {
     if (ctx->d_bkg) cudaFree(ctx->d_bkg);
     if (ctx->h_bkg) cudaFreeHost(ctx->h_bkg);
     for (int i = 0; i <= ZB_NSTAGES; i++) cudaEventDestroy(ctx->ev[i]);
+    if (ctx->ev_sync) cudaEventDestroy(ctx->ev_sync);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -403,7 +414,7 @@ static int resolve_region(zb_ctx *ctx, int r, const float *conv_img, cudaStream_
             int rc = zb_launch_stamp_search(ctx, conv_img, ci, 1, st);
             if (rc != ZB_OK) { *rc_out = rc; return 0; }
             cudaMemcpyAsync(C, &ctx->d_cells[ci], sizeof(ZbCell), cudaMemcpyDeviceToHost, st);
-            if (cudaStreamSynchronize(st) != cudaSuccess) { *rc_out = zb_cuda_fail(ctx, cudaGetLastError(), "stamp re-search", __FILE__, __LINE__); return 0; }
+            if (zb_stream_wait(ctx, st) != cudaSuccess) { *rc_out = zb_cuda_fail(ctx, cudaGetLastError(), "stamp re-search", __FILE__, __LINE__); return 0; }
         }
         if (C->nss > 0) { kept++; s_mode = s_fwhm = s_mean = s_sd = s_median = s_lfwhm = s_sum = 0; }
         else { s_mode = C->mode; s_fwhm = C->fwhm; s_mean = C->mean; s_sd = C->sd; s_median = C->median; s_lfwhm = C->lfwhm; s_sum = C->sum; }
@@ -414,7 +425,7 @@ static int resolve_region(zb_ctx *ctx, int r, const float *conv_img, cudaStream_
 
 #define STAGE(i) cudaEventRecord(ctx->ev[i], st)
 #define CHECK_RC(x) do { int rc_ = (x); if (rc_ != ZB_OK) return rc_; } while (0)
-#define SYNC(what) do { cudaError_t e_ = cudaStreamSynchronize(st); if (e_ != cudaSuccess) return zb_cuda_fail(ctx, e_, what, __FILE__, __LINE__); } while (0)
+#define SYNC(what) do { cudaError_t e_ = zb_stream_wait(ctx, st); if (e_ != cudaSuccess) return zb_cuda_fail(ctx, e_, what, __FILE__, __LINE__); } while (0)
 
 // Stage 8 of a subtraction: the small device-to-host read-backs and the per-region record (main.c:1719-1953 keywords)
 int zb_finish_readback(zb_ctx *ctx, zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps_out, int timing /* 0 none, 1 stages, 2 stages + k_convolve */, cudaStream_t st)
@@ -648,7 +659,7 @@ extern "C" int zb_subtract_host(zb_ctx *ctx, const zb_params *p,
     cudaMemcpyAsync(diff, ctx->d_stage[6], n * 4, cudaMemcpyDeviceToHost, st);
     cudaMemcpyAsync(noise, ctx->d_stage[7], n * 4, cudaMemcpyDeviceToHost, st);
     if (out_mask) cudaMemcpyAsync(out_mask, ctx->d_stage[8], n * 4, cudaMemcpyDeviceToHost, st);
-    cudaError_t e = cudaStreamSynchronize(st);
+    cudaError_t e = zb_stream_wait(ctx, st);
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "zb_subtract_host copies", __FILE__, __LINE__);
     return ZB_OK;
 }

@@ -16,7 +16,7 @@ static inline int imin_(int a, int b) { return a < b ? a : b; }
 static inline int imax_(int a, int b) { return a < b ? b : a; }
 
 #define CHECK_RC(x) do { int rc_ = (x); if (rc_ != ZB_OK) return rc_; } while (0)
-#define SYNC(what) do { cudaError_t e_ = cudaStreamSynchronize(st); if (e_ != cudaSuccess) return zb_cuda_fail(ctx, e_, what, __FILE__, __LINE__); } while (0)
+#define SYNC(what) do { cudaError_t e_ = zb_stream_wait(ctx, st); if (e_ != cudaSuccess) return zb_cuda_fail(ctx, e_, what, __FILE__, __LINE__); } while (0)
 #define NEED_TILE() do { if (!ctx || !ctx->tile.on) { if (ctx) snprintf(ctx->err, sizeof ctx->err, "no row-tile session (call zb_tile_begin first)"); return ZB_ERR_PARAM; } \
                          if (cudaSetDevice(ctx->device) != cudaSuccess) return zb_cuda_fail(ctx, cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__); } while (0)
 
