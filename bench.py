@@ -231,7 +231,11 @@ def bench_b200(args):
         dev_in.append([None if t is None else t.cuda(non_blocking=True) for t in pinned])
     torch.cuda.synchronize()
 
-    W, B = args.workers, args.batch
+    # contexts per GPU: each is a host thread that spins while it waits for its stream, so keep the ranks of
+    # one box within ~1.5 threads per host core; 24 is where the end-to-end rate stops growing on one GPU
+    cores = host_cores()
+    W = args.workers or max(4, min(24, int(1.5 * cores / world)))
+    B = args.batch or 4 * W
     from zuds_pipeline_b200.batch import GpuPool
     pool = GpuPool(local, W)
     dev_out = [(torch.empty((ny, nx), dtype=torch.float32, device="cuda"), torch.empty((ny, nx), dtype=torch.float32, device="cuda"),
@@ -335,7 +339,7 @@ def bench_b200(args):
         "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "c1: 3080x3072 quadrant pair, -c t -n i -r 10 -rss 24 -ko 2 -bgo 0, 3x3 regions x 10x10 stamps (BASELINE configs[1])",
-                   "pairs_per_step_per_gpu": B, "contexts_per_gpu": W, "distinct_pairs_per_gpu": npairs_distinct,
+                   "pairs_per_step_per_gpu": B, "contexts_per_gpu": W, "host_cores": cores, "distinct_pairs_per_gpu": npairs_distinct,
                    "l2": "inputs of one pair are 161 MB (> 126 MB L2) and consecutive jobs alternate pairs",
                    "sharding": "by image pair, no collective"},
         "e2e": {"value": pairs_total / host_s, "unit": UNIT, "h2d_bytes_per_step": in_bytes * B, "d2h_bytes_per_step": out_bytes * B,
@@ -378,8 +382,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workers", type=int, default=24, help="concurrent contexts (streams) per GPU")
-    ap.add_argument("--batch", type=int, default=96, help="pair subtractions per step per GPU")
+    ap.add_argument("--workers", type=int, default=0, help="concurrent contexts (streams) per GPU (0: from the host core count, at most 24)")
+    ap.add_argument("--batch", type=int, default=0, help="pair subtractions per step per GPU (0: 4 per context)")
     ap.add_argument("--cpu-procs", type=int, default=0, help="reference arm: concurrent hotpants processes (0 = all cores)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-clocks", action="store_true", help="(diagnostics) do not sample clocks during the timed region")
