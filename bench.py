@@ -231,10 +231,11 @@ def bench_b200(args):
         dev_in.append([None if t is None else t.cuda(non_blocking=True) for t in pinned])
     torch.cuda.synchronize()
 
-    # contexts per GPU: each is a host thread that spins while it waits for its stream, so keep the ranks of
-    # one box within ~1.5 threads per host core; 24 is where the end-to-end rate stops growing on one GPU
+    # contexts per GPU: each is a host thread that spins while it waits for its stream.  One GPU: 24 is where
+    # the end-to-end rate stops growing (16 cores).  Several ranks on one box: one thread per core share
+    # (measured on 8 B200 / 32 cores: 4 contexts 1330 pairs/s, 6: 1227, 12: 1167, 16: 1180)
     cores = host_cores()
-    W = args.workers or max(4, min(24, int(1.5 * cores / world)))
+    W = args.workers or (24 if 24 * world <= 1.5 * cores else max(4, cores // world))
     B = args.batch or 4 * W
     from zuds_pipeline_b200.batch import GpuPool
     pool = GpuPool(local, W)
