@@ -175,7 +175,7 @@ k_qa_sample(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const 
 struct QaShared {
     int phase[4], ncrit[4], exact[4];
     float flo[4], fhi[4];
-    double cm[4][8], ci[4][8], mean[4], isd[4], bin1[4], binsize[4];
+    double cm[4][8], ci[4][8], mean[4], isd[4], bin1[4], binsize[4], ibin[4];
     int bins[4][256];
     double ra[8], rb[8]; int rc[8];
 };
@@ -278,7 +278,7 @@ template <int MINB>
 __global__ void __launch_bounds__(256, MINB)
 k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const float *__restrict__ rnoise,
           int32_t *__restrict__ omask, int32_t *__restrict__ out_mask, ZbQaStat *qa,
-          ZbQaPart *part, double *__restrict__ q, int first)
+          ZbQaPart *part, double *__restrict__ q, int first, int use_div)
 {
     __shared__ QaShared S;
     __shared__ int s_last;
@@ -289,7 +289,7 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
         const ZbQaStat &Q = qa[r * 4 + tid];
         S.phase[tid] = Q.phase; S.ncrit[tid] = Q.ncrit; S.exact[tid] = Q.exact;
         for (int c = 0; c < 8; c++) { S.cm[tid][c] = Q.crit_mean[c]; S.ci[tid][c] = Q.crit_istd[c]; }
-        S.mean[tid] = Q.mean; S.isd[tid] = 1. / Q.sd; S.bin1[tid] = Q.bin1; S.binsize[tid] = Q.binsize;
+        S.mean[tid] = Q.mean; S.isd[tid] = 1. / Q.sd; S.bin1[tid] = Q.bin1; S.binsize[tid] = Q.binsize; S.ibin[tid] = use_div ? __longlong_as_double(0x7ff8000000000000ll) : 1. / Q.binsize;
         S.flo[tid] = Q.phase == 0 ? Q.clo : Q.llo; S.fhi[tid] = Q.phase == 0 ? Q.chi : Q.lhi;
     }
     for (int k = tid; k < 4 * 256; k += 256) (&S.bins[0][0])[k] = 0;
@@ -310,7 +310,14 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
                 if (keep_) { \
                     if (S.phase[s] == 0) { a1[s] += (xv); a2[s] += (double)((xv) * (xv)); an[s]++; } \
                     else { \
-                        int index = (int)(floor(((xv) - S.bin1[s]) / S.binsize[s]) + 1); \
+                        /* floor((x - bin1) / binsize) as the reference forms it; the division is replaced by a */ \
+                        /* multiplication whenever the quotient is provably not within rounding of an integer   */ \
+                        const double t_ = (xv) - S.bin1[s]; \
+                        const double q_ = t_ * S.ibin[s]; \
+                        double fl_ = floor(q_); \
+                        { const double fr_ = q_ - fl_, eps_ = fabs(q_) * 8.9e-16 + 1e-300; \
+                          if (!(fr_ >= eps_ && fr_ <= 1.0 - eps_)) fl_ = floor(t_ / S.binsize[s]); } \
+                        int index = (int)(fl_ + 1); \
                         index = (index < 0 ? 0 : index); index = (index > 255 ? 255 : index); \
                         const unsigned peers = __match_any_sync(__activemask(), index); \
                         if ((int)(__ffs(peers) - 1) == (threadIdx.x & 31)) atomicAdd(&S.bins[s][index], __popc(peers)); \
@@ -489,17 +496,18 @@ int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStr
     // at most maxiter (5) clip passes + 5 histogram passes; finished regions fall through at once.
     // CTAs per region: enough to put ~4 CTAs on every SM whatever the number of regions (a single-region
     // coadd-scale frame would otherwise stream 38 Mpx through 64 CTAs)
-    static int minb = 0;
-    if (!minb) { const char *e = getenv("ZB_QA_MINB"); minb = e ? atoi(e) : 3; }
+    static int minb = 0, use_div = 0;
+    { const char *e = getenv("ZB_QA_DIV"); use_div = (e && e[0] == '1') ? 1 : 0; }
+    if (!minb) { const char *e = getenv("ZB_QA_MINB"); minb = e ? atoi(e) : 4;      // 4 CTAs/SM: 9 regions x 64 CTAs = one resident wave (A/B on B200: 1.47 ms vs 1.65 at 3) }
     int nblk = nR >= 5 ? ZB_QA_NBLK_MIN : (4 * 148 + nR - 1) / nR;
     nblk = nblk < ZB_QA_NBLK_MIN ? ZB_QA_NBLK_MIN : (nblk > ZB_QA_NBLK ? ZB_QA_NBLK : nblk);
     for (int pass = 0; pass < 10; pass++) {
         if (minb == 3) k_qa_pass<3><<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
-                                                                   ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0);
+                                                                   ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0, use_div);
         else if (minb == 4) k_qa_pass<4><<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
-                                                                   ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0);
+                                                                   ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0, use_div);
         else k_qa_pass<2><<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
-                                                         ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0);
+                                                         ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0, use_div);
         ZB_DBG("k_qa_pass");
         ctx->launches++;
     }
