@@ -24,7 +24,8 @@
 #define MK_NB 16      // convolution blocks per CTA of k_make_kernels
 __global__ void __launch_bounds__(256)
 k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, const double *__restrict__ kvec,
-               double *__restrict__ kern, double *__restrict__ ksum_out, double *__restrict__ kaks, int nbx_max, int nby_max)
+               double *__restrict__ kern, double *__restrict__ kernr, int fwp,
+               double *__restrict__ ksum_out, double *__restrict__ kaks, int nbx_max, int nby_max)
 {
     __shared__ double coef[MK_NB][ZB_MAX_BASIS];
     const int r = blockIdx.y;
@@ -61,6 +62,7 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
     }
     __syncthreads();
     for (int t = tid; t < fw2; t += blockDim.x) {
+        const int roff = (fw - 1 - t / fw) * fwp + (fw - 1 - t % fw);      // position in the reversed, row-padded copy
         double acc[MK_NB];
 #pragma unroll
         for (int lb = 0; lb < MK_NB; lb++) acc[lb] = 0.0;
@@ -74,7 +76,16 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
             int b = b0 + lb;
             if (b > nb) continue;
             kern[((long long)r * per_region + b) * fw2 + t] = acc[lb];
+            // the same kernel reversed (image coordinates ascending) with rows padded to fwp: what k_convolve
+            // copies straight into shared memory
+            kernr[((long long)r * per_region + b) * fw * fwp + roff] = acc[lb];
         }
+    }
+    for (int lb = 0; lb < MK_NB; lb++) {                      // zero padding of the reversed rows
+        const int b = b0 + lb, npad = fwp - fw;
+        if (b > nb || npad <= 0) continue;
+        for (int t = tid; t < fw * npad; t += blockDim.x)
+            kernr[((long long)r * per_region + b) * fw * fwp + (t / npad) * fwp + fw + t % npad] = 0.0;
     }
     __syncthreads();
     // aks = sum |K| in spatial_convolve's tap order (image coordinates ascending = kernel index descending,
@@ -199,21 +210,21 @@ __device__ static inline void finish_pixel(const ZbDev *D, const ZbRegion &R, co
 // alard.c:1304-1308,1327: sum |K| over all taps (aks) and over the taps whose pixel is not INPUT_ISBAD
 // (uks), both in the reference's tap order; true when uks/aks < kerFracMask.  Rare path (a bad
 // pixel under the footprint), kept out of line so the output pass stays small.
-#define CONV_BADCAP 192     // INPUT_ISBAD pixels of a tile kept as a list; more than that: the exact loop
-__device__ __noinline__ static bool conv_kernel_fraction_low(const double *Kb, const unsigned char *f0, int fw, int fwp, int W, float kfm,
-                                                             double aks_blk, const int *bad, int nbad, int ox, int oy)
+__device__ __noinline__ static bool conv_kernel_fraction_low(const double *Kb, const unsigned char *f0, const unsigned char *h0,
+                                                             int fw, int fwp, int W, float kfm, double aks_blk)
 {
-    // Fast decision: uks = aks - (the few bad taps), accurate to ~1e-13 relative; the reference's
+    // Fast decision: uks = aks - (the bad taps), accurate to ~1e-13 relative; the reference's
     // sequentially rounded sums are only reproduced when the ratio is within 1e-9 of the threshold.
-    if (nbad <= CONV_BADCAP) {
-        double bs = 0.0;
-        for (int i = 0; i < nbad; i++) {
-            const unsigned dx = (unsigned)((bad[i] & 0xffff) - ox), dy = (unsigned)((bad[i] >> 16) - oy);
-            if (dx < (unsigned)fw && dy < (unsigned)fw) bs += fabs(Kb[dy * fwp + dx]);
-        }
-        const double ratio = (aks_blk - bs) / aks_blk;
-        if (fabs(ratio - (double)kfm) > 1e-9) return ratio < (double)kfm;
+    // h0[dy * W] bit 1: some INPUT_ISBAD pixel in the fw columns of footprint row dy.
+    double bs = 0.0;
+    for (int dy = 0; dy < fw; dy++) {
+        if (!(h0[dy * W] & 2)) continue;
+        const unsigned char *fr = f0 + dy * W;
+        const double *kr = Kb + dy * fwp;
+        for (int dx = 0; dx < fw; dx++) if (fr[dx] & 2) bs += fabs(kr[dx]);
     }
+    const double ratio = (aks_blk - bs) / aks_blk;
+    if (fabs(ratio - (double)kfm) > 1e-9) return ratio < (double)kfm;
     double aks = 0.0, uks = 0.0;
     for (int dy = 0; dy < fw; dy++)
         for (int dx = 0; dx < fw; dx++) {
@@ -236,7 +247,7 @@ __device__ static inline void cp_async_wait_all() { asm volatile("cp.async.wait_
 
 template <int TX, int TY, int CH, bool EXACT /* fw % CH == 0 */, bool KKONLY /* -convvar */>
 __global__ void __launch_bounds__(256)
-k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sols, const double *__restrict__ kern,
+k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sols, const double *__restrict__ kernr,
            const double *__restrict__ ksums, const double *__restrict__ kaks,
            int nbx_max, int nby_max, int NBX, int NBY, int GX, int GY, int W, int TH, int blk_row0, int blk_row1,
            float *__restrict__ rdiff, float *__restrict__ rnoise, int32_t *__restrict__ omask,
@@ -258,11 +269,11 @@ k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sol
     double *Kr = (double *)(tile + (size_t)TH * W);           // [NB][fw][fwp]  K reversed
     unsigned char *flag = (unsigned char *)(Kr + (size_t)NB * fw * fwp);   // [TH][W] bit0: any mask bit, bit1: 0x80
     unsigned char *hor = flag + (size_t)TH * W;               // [TH][W] OR of flag over the fw columns to the right
-    __shared__ int s_any, s_nbad, s_bad[CONV_BADCAP];
+    __shared__ int s_any;
     const int tid = threadIdx.x, nt = blockDim.x;
     const int per_region = nbx_max * nby_max + 1;
     const float fill = D->p.fill_val;
-    if (tid == 0) { s_any = 0; s_nbad = 0; }
+    if (tid == 0) s_any = 0;
     __syncthreads();
     // ---- stage the tile, origin (i00 - hw, j00 - hw) in region coords.  The raw floats travel by
     // cp.async into the low 8 bytes of their own double2 slot (all copies of the CTA in flight at
@@ -288,17 +299,15 @@ k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sol
             flag[k] = f;
         }
     }
-    {   // kernels of the CTA's blocks, reversed, also by cp.async: one (block, kernel row) per warp step
-        const int nrows = NB * fw;
-        for (int q = warp; q < nrows; q += nw) {
-            const int lb = q / fw, dy = q - lb * fw;
+    {   // kernels of the CTA's blocks: k_make_kernels left them reversed and row-padded, a flat cp.async copy
+        const int kn = fw * fwp;
+        for (int lb = 0; lb < NB; lb++) {
             const int lby = lb / NBX, lbx = lb - lby * NBX;
             const bool ex = bx0 + lbx < nbx && by0 + lby < nby;
-            const double *src = kern + ((long long)r * per_region + (long long)(by0 + lby) * nbx + (bx0 + lbx)) * fw2 + (fw - 1 - dy) * fw;
-            for (int dx = lane; dx < fwp; dx += 32) {
-                double *dst = Kr + (size_t)q * fwp + dx;
-                if (ex && dx < fw) cp_async8(dst, src + (fw - 1 - dx)); else *dst = 0.0;
-            }
+            const double *src = kernr + ((long long)r * per_region + (long long)(by0 + lby) * nbx + (bx0 + lbx)) * kn;
+            double *dst = Kr + (size_t)lb * kn;
+            if (ex) for (int e = tid; e < kn; e += nt) cp_async8(dst + e, src + e);
+            else for (int e = tid; e < kn; e += nt) dst[e] = 0.0;
         }
     }
     cp_async_wait_all();
@@ -320,7 +329,6 @@ k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sol
                 f |= (cm ? 1 : 0) | ((cm & ZB_FLAG_INPUT_ISBAD) ? 2 : 0);
             }
             tile[k] = v; flag[k] = f; anyf |= f;
-            if (f & 2) { const int q = atomicAdd(&s_nbad, 1); if (q < CONV_BADCAP) s_bad[q] = (ty << 16) | tx; }
         }
     }
     if (anyf) s_any = 1;
@@ -430,19 +438,31 @@ k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sol
     constexpr int EPB = 8;                                      // pixels per lane whose global loads are in flight together
     const int nchunk = (ox_lim + 31) >> 5;
     const int nitems = (oy_lim > warp ? (oy_lim - warp + nw - 1) / nw : 0) * nchunk;   // (row of this warp, column chunk)
+    // item -> (row of this warp, column chunk) without a division: nitems * nchunk is far below 2^16
+    const unsigned magic = (65536u + (unsigned)nchunk - 1u) / (unsigned)nchunk;
+    // the global loads of batch n+1 (other image, its rms, its user mask) are in flight while batch n is finished
+#define CONV_OUT_LOAD(IT0, OTH, ORV, UB) do { \
+        _Pragma("unroll") for (int e = 0; e < EPB; e++) { \
+            const int it = (IT0) + e, j = (int)(((unsigned)it * magic) >> 16), c = it - j * nchunk; \
+            const int lx = lane + 32 * c, ly = warp + nw * j; \
+            OTH[e] = 0.f; ORV[e] = 0.f; UB[e] = 0; \
+            if (it < nitems && lx < ox_lim) { \
+                const long long g = gout + (long long)ly * nxi + lx; \
+                OTH[e] = P.other[g]; \
+                if (have_orms) ORV[e] = P.other_rms[g]; \
+                UB[e] = user_bits(P.omask_src, P.odt, g); } } } while (0)
+    float oth[EPB], orv[EPB]; int ub[EPB];
+    CONV_OUT_LOAD(0, oth, orv, ub);
     for (int it0 = 0; it0 < nitems; it0 += EPB) {
         {
-            float oth[EPB], orv[EPB]; int ub[EPB], eox[EPB], eoy[EPB];
+            float noth[EPB], norv[EPB]; int nub[EPB];
+            if (it0 + EPB < nitems) CONV_OUT_LOAD(it0 + EPB, noth, norv, nub);
+            int eox[EPB], eoy[EPB];
 #pragma unroll
             for (int e = 0; e < EPB; e++) {
-                const int it = it0 + e, j = it / nchunk, c = it - j * nchunk;
+                const int it = it0 + e, j = (int)(((unsigned)it * magic) >> 16), c = it - j * nchunk;
                 eox[e] = lane + 32 * c; eoy[e] = warp + nw * j;
-                oth[e] = 0.f; orv[e] = 0.f; ub[e] = 0;
-                if (it >= nitems || eox[e] >= ox_lim) { eox[e] = -1; continue; }
-                const long long g = gout + (long long)eoy[e] * nxi + eox[e];
-                oth[e] = P.other[g];
-                if (have_orms) orv[e] = P.other_rms[g];
-                ub[e] = user_bits(P.omask_src, P.odt, g);
+                if (it >= nitems || eox[e] >= ox_lim) eox[e] = -1;
             }
 #pragma unroll
             for (int e = 0; e < EPB; e++) {
@@ -464,9 +484,8 @@ k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sol
                         bool low = false;                            // no bad tap: uks == aks exactly
                         if (mbit & 2) {
                             const int oby = oy / B, obx = ox / B;
-                            low = conv_kernel_fraction_low(Kr + (size_t)(oby * NBX + obx) * fw * fwp, flag + (size_t)oy * W + ox, fw, fwp, W, kfm,
-                                                           kaks[(long long)r * per_region + (long long)(by0 + oby) * nbx + (bx0 + obx)],
-                                                           s_bad, s_nbad, ox, oy);
+                            low = conv_kernel_fraction_low(Kr + (size_t)(oby * NBX + obx) * fw * fwp, flag + (size_t)oy * W + ox, h0, fw, fwp, W, kfm,
+                                                           kaks[(long long)r * per_region + (long long)(by0 + oby) * nbx + (bx0 + obx)]);
                         }
                         if (low) m |= (ZB_FLAG_OUTPUT_ISBAD | ZB_FLAG_BAD_CONV);
                         else m |= ZB_FLAG_OK_CONV;
@@ -496,8 +515,13 @@ k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sol
                     if (out_mask) out_mask[g] = m;
                 }
             }
+            if (it0 + EPB < nitems) {
+#pragma unroll
+                for (int e = 0; e < EPB; e++) { oth[e] = noth[e]; orv[e] = norv[e]; ub[e] = nub[e]; }
+            }
         }
     }
+#undef CONV_OUT_LOAD
 }
 
 // The hwKernel frame of every region (not touched by spatial_convolve).
@@ -544,9 +568,6 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
     P.c_invgain = ct ? tinv : iinv; P.c_quad = ct ? tq : iq;
     P.o_invgain = ct ? iinv : tinv; P.o_quad = ct ? iq : tq;
 
-    dim3 gk((nbx_max * nby_max + 1 + MK_NB - 1) / MK_NB + 1, nR);
-    k_make_kernels<<<gk, 256, 0, st>>>(ctx->d_dev, ctx->d_sol, ctx->d_kvec, ctx->d_kern, ctx->d_kstat, ctx->d_kaks, nbx_max, nby_max); ZB_DBG("k_make_kernels");
-
     // register tile per kernel-block size: (TX, TY, CH) with GX*TX >= B, GY*TY >= B
     int TXr, TYr, CHr;
     if (B <= 12)      { TXr = 4; TYr = 3; CHr = 4; }
@@ -555,6 +576,8 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
     const int GX = (B + TXr - 1) / TXr, GY = (B + TYr - 1) / TYr, tpb = GX * GY;
     if (tpb > 256) { snprintf(ctx->err, sizeof ctx->err, "kc_step %d too large for the convolution kernel", B); return ZB_ERR_UNSUPPORTED; }
     const int nch = (fw + CHr - 1) / CHr, fwp = nch * CHr;
+    dim3 gk((nbx_max * nby_max + 1 + MK_NB - 1) / MK_NB + 1, nR);
+    k_make_kernels<<<gk, 256, 0, st>>>(ctx->d_dev, ctx->d_sol, ctx->d_kvec, ctx->d_kern, ctx->d_kernr, fwp, ctx->d_kstat, ctx->d_kaks, nbx_max, nby_max); ZB_DBG("k_make_kernels");
     // blocks per CTA: ~128 threads and two CTAs per SM when shared memory allows (228 KB per SM, 1 KB
     // reserved per CTA), else one CTA with as many blocks as fit; among equals the squarer tile (less halo)
     int NBX = 1, NBY = 1, W = 0, TH = 0, threads = 0; size_t smem = 0;
@@ -587,7 +610,7 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
     cudaEventRecord(ctx->ev[10], st);          // k_convolve alone: the kernel bench.py's roofline is quoted on
 #define ZB_CONV_LAUNCH2(TX_, TY_, CH_, EX_, KK_) do { \
         cudaFuncSetAttribute(k_convolve<TX_, TY_, CH_, EX_, KK_>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN); \
-        k_convolve<TX_, TY_, CH_, EX_, KK_><<<gc, threads, smem, st>>>(ctx->d_dev, P, ctx->d_sol, ctx->d_kern, ctx->d_kstat, ctx->d_kaks, nbx_max, nby_max, \
+        k_convolve<TX_, TY_, CH_, EX_, KK_><<<gc, threads, smem, st>>>(ctx->d_dev, P, ctx->d_sol, ctx->d_kernr, ctx->d_kstat, ctx->d_kaks, nbx_max, nby_max, \
             NBX, NBY, GX, GY, W, TH, blk_row0, blk_row1, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask); } while (0)
 #define ZB_CONV_LAUNCH(TX_, TY_, CH_) do { \
         const bool ex_ = (fw % CH_) == 0, kk_ = p.convolve_variance != 0; \

@@ -140,6 +140,7 @@ struct zb_ctx {
     ZbFit   *d_fit, *h_fit;
     int     *d_jobs, *d_njobs, *h_njobs;
     double  *d_kern;             // [region][blocks+1][fw*fw]  K per convolution block (+ the region-centre kernel)
+    double  *d_kernr;            // the same kernels reversed, rows padded to the convolution's chunk width (what k_convolve stages)
     double  *d_kaks;             // [region][blocks+1]  sum |K| per block in the reference's tap order
     double  *d_kstat;            // per-region: ksum, aks
     double  *d_stats;  double *h_stats;   // region QA scratch

@@ -498,7 +498,8 @@ int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStr
     // coadd-scale frame would otherwise stream 38 Mpx through 64 CTAs)
     static int minb = 0, use_div = 0;
     { const char *e = getenv("ZB_QA_DIV"); use_div = (e && e[0] == '1') ? 1 : 0; }
-    if (!minb) { const char *e = getenv("ZB_QA_MINB"); minb = e ? atoi(e) : 4;      // 4 CTAs/SM: 9 regions x 64 CTAs = one resident wave (A/B on B200: 1.47 ms vs 1.65 at 3) }
+    // 4 CTAs/SM: 9 regions x 64 CTAs = one resident wave (A/B on B200: 1.47 ms vs 1.65 at 3)
+    if (!minb) { const char *e = getenv("ZB_QA_MINB"); minb = e ? atoi(e) : 4; }
     int nblk = nR >= 5 ? ZB_QA_NBLK_MIN : (4 * 148 + nR - 1) / nR;
     nblk = nblk < ZB_QA_NBLK_MIN ? ZB_QA_NBLK_MIN : (nblk > ZB_QA_NBLK ? ZB_QA_NBLK : nblk);
     for (int pass = 0; pass < 10; pass++) {
