@@ -450,7 +450,7 @@ k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sol
                 const long long g = gout + (long long)ly * nxi + lx; \
                 OTH[e] = P.other[g]; \
                 if (have_orms) ORV[e] = P.other_rms[g]; \
-                UB[e] = user_bits(P.omask_src, P.odt, g); } } } while (0)
+                UB[e] = zb_read_mask(P.omask_src, P.odt, g); } } } while (0)   /* raw value: nothing may depend on a load here */
     float oth[EPB], orv[EPB]; int ub[EPB];
     CONV_OUT_LOAD(0, oth, orv, ub);
     for (int it0 = 0; it0 < nitems; it0 += EPB) {
@@ -484,8 +484,9 @@ k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sol
                         bool low = false;                            // no bad tap: uks == aks exactly
                         if (mbit & 2) {
                             const int oby = oy / B, obx = ox / B;
+                            const double aks_blk = kaks[(long long)r * per_region + (long long)(by0 + oby) * nbx + (bx0 + obx)];
                             low = conv_kernel_fraction_low(Kr + (size_t)(oby * NBX + obx) * fw * fwp, flag + (size_t)oy * W + ox, h0, fw, fwp, W, kfm,
-                                                           kaks[(long long)r * per_region + (long long)(by0 + oby) * nbx + (bx0 + obx)]);
+                                                           aks_blk);
                         }
                         if (low) m |= (ZB_FLAG_OUTPUT_ISBAD | ZB_FLAG_BAD_CONV);
                         else m |= ZB_FLAG_OK_CONV;
@@ -495,8 +496,9 @@ k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sol
                 const float ov = oth[e];
                 const int ob = value_bits(ov, fill, P.oU, P.oL);
                 if (ob) m |= ob | ZB_FLAG_OUTPUT_ISBAD;
-                m |= ub[e];
-                if (ub[e] & ZB_FLAG_INPUT_ISBAD) m |= ZB_FLAG_OUTPUT_ISBAD;
+                const int ubit = ub[e] | (ZB_FLAG_INPUT_MASK * (ub[e] > 0));       // user_bits() of the prefetched raw mask value
+                m |= ubit;
+                if (ubit & ZB_FLAG_INPUT_ISBAD) m |= ZB_FLAG_OUTPUT_ISBAD;
                 float ovar;
                 if (have_orms) ovar = __fmul_rn(orv[e], orv[e]);
                 else ovar = (float)__dadd_rn(__dmul_rn(fabs((double)ov), (double)P.o_invgain), o_qq);
