@@ -17,6 +17,7 @@
 
 // ------------------------------------------------------------------ fillStamp
 
+#define FILL_ILP 4
 __global__ void __launch_bounds__(256)
 k_fill_conv(const ZbDev *__restrict__ D, const float *__restrict__ img, const ZbStamp *__restrict__ stamps,
             const int *__restrict__ jobs, const double *__restrict__ fxs, const double *__restrict__ fys,
@@ -30,34 +31,55 @@ k_fill_conv(const ZbDev *__restrict__ D, const float *__restrict__ img, const Zb
     const int hw = D->p.hw_kernel, hwss = D->p.hw_ksstamp, fw = D->sz.fw_kernel, fwss = D->sz.fw_ksstamp;
     const int sw = fwss + fw - 1;                     // sub_width
     const int xi = S.xss[S.sscnt], yi = S.yss[S.sscnt];
+    // The float -> double conversion pipe (16 lanes/clk/SM) is what bounds this kernel, so every value is
+    // widened ONCE when it is staged instead of once per tap: the patch as it is loaded, the y-pass result
+    // when it is stored.  What remains per tap is the rounding of the running y-sum to float and back.
     double *fx = (double *)dyn, *fy = fx + fw;
-    float *patch = (float *)(fy + fw);                // [sw][sw]
-    float *temp = patch + sw * sw;                    // [fwss][sw]
+    double *patch = fy + fw;                          // [sw][sw]   (double)pixel
+    double *temp = patch + sw * sw;                   // [fwss][sw] (double)(float) y-pass sums
     const int tid = threadIdx.x, nt = blockDim.x;
     for (int k = tid; k < fw; k += nt) { fx[k] = fxs[k + n * fw]; fy[k] = fys[k + n * fw]; }
     const int px0 = xi - hwss - hw, py0 = yi - hwss - hw;
-    for (int k = tid; k < sw * sw; k += nt) {
-        int py = k / sw, px = k - py * sw;
-        patch[k] = img[(long long)(R.by0 + py0 + py) * D->nx + (R.bx0 + px0 + px)];
+    for (int py = tid / sw, px = tid - (tid / sw) * sw, k = tid; k < sw * sw; k += nt) {
+        patch[k] = (double)img[(long long)(R.by0 + py0 + py) * D->nx + (R.bx0 + px0 + px)];
+        px += nt; while (px >= sw) { px -= sw; py++; }
     }
     __syncthreads();
     // y pass: float accumulator, rounded after every tap (the reference's scratch is float)
-    for (int k = tid; k < sw * fwss; k += nt) {
-        int r = k / sw, c = k - r * sw;               // r: row of the sub-stamp, c: column incl. halo
-        float t = 0.0f;
-        for (int yc = -hw; yc <= hw; yc++)
-            t = (float)((double)t + (double)patch[c + sw * (r + hw + yc)] * fy[hw - yc]);
-        temp[k] = t;
+    // FILL_ILP outputs per thread advance together: the per-tap chain (DMUL, DADD, round to float, widen) is
+    // ~100 cycles of dependent latency, and the staged doubles leave room for only a few CTAs per SM
+    for (int k0 = tid; k0 < sw * fwss; k0 += FILL_ILP * nt) {
+        double t[FILL_ILP]; int off[FILL_ILP];
+#pragma unroll
+        for (int u = 0; u < FILL_ILP; u++) {
+            const int k = k0 + u * nt, r = k / sw, c = k - r * sw;          // r: row of the sub-stamp, c: column incl. halo
+            t[u] = 0.0; off[u] = k < sw * fwss ? c + sw * r : 0;
+        }
+        for (int q = 0; q < fw; q++) {                                      // q = yc + hw
+            const double f = fy[fw - 1 - q];
+#pragma unroll
+            for (int u = 0; u < FILL_ILP; u++) t[u] = (double)(float)(t[u] + patch[off[u] + sw * q] * f);
+        }
+#pragma unroll
+        for (int u = 0; u < FILL_ILP; u++) if (k0 + u * nt < sw * fwss) temp[k0 + u * nt] = t[u];
     }
     __syncthreads();
     const int npix = fwss * fwss;
     double *out = vec + (long long)slot * (D->sz.n_comp_ker + D->sz.n_bg_vectors) * npix + (long long)n * npix;
-    for (int k = tid; k < npix; k += nt) {
-        int r = k / fwss, c = k - r * fwss;
-        double acc = 0.0;
-        for (int xc = -hw; xc <= hw; xc++)
-            acc += (double)temp[(c + xc + hw) + sw * r] * fx[hw - xc];
-        out[k] = acc;
+    for (int k0 = tid; k0 < npix; k0 += FILL_ILP * nt) {
+        double acc[FILL_ILP]; int off[FILL_ILP];
+#pragma unroll
+        for (int u = 0; u < FILL_ILP; u++) {
+            const int k = k0 + u * nt, r = k / fwss, c = k - r * fwss;
+            acc[u] = 0.0; off[u] = k < npix ? c + sw * r : 0;
+        }
+        for (int q = 0; q < fw; q++) {                                      // q = xc + hw
+            const double f = fx[fw - 1 - q];
+#pragma unroll
+            for (int u = 0; u < FILL_ILP; u++) acc[u] += temp[off[u] + q] * f;
+        }
+#pragma unroll
+        for (int u = 0; u < FILL_ILP; u++) if (k0 + u * nt < npix) out[k0 + u * nt] = acc[u];
     }
 }
 
@@ -245,7 +267,7 @@ int zb_launch_fill(zb_ctx *ctx, const float *conv_img, const float *ref_img, con
     const zb_sizes &sz = ctx->sz;
     const int fw = sz.fw_kernel, fwss = sz.fw_ksstamp, sw = fwss + fw - 1, npix = fwss * fwss;
     const int nvec = sz.n_comp_ker + sz.n_bg_vectors;
-    size_t sm1 = 2 * fw * sizeof(double) + ((size_t)sw * sw + (size_t)sw * fwss) * sizeof(float);
+    size_t sm1 = (2 * fw + (size_t)sw * sw + (size_t)sw * fwss) * sizeof(double);
     const int ldv = ((nvec + GRAM_T - 1) / GRAM_T) * GRAM_T;
     size_t sm3 = (size_t)GRAM_KC * ldv * sizeof(double);
     size_t sm4 = ((size_t)npix + (size_t)RHS_WARPS * 2 * RHS_COLS * fwss) * sizeof(double);
