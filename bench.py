@@ -41,8 +41,8 @@ UNIT = "quadrant-pairs/s"
 SHAPE = (3080, 3072)
 ALG_BYTES_PER_PIXEL = 29          # 4 float inputs + 1 mask byte in, 2 floats + int32 mask out
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_convolve launch at C1, from the ncu --set full
-# capture summarised in profiles/r01_ncu_k_convolve_s16.txt (251.70 MB + 190.47 MB); None for other shapes
-NCU_CONV_TRAFFIC_BYTES = 442164736
+# capture summarised in profiles/r01_ncu_k_convolve_s17.txt (251.88 MB + 188.61 MB)
+NCU_CONV_TRAFFIC_BYTES = 440489472
 
 
 def workload_case():
