@@ -166,8 +166,8 @@ static int bkg_run(zb_ctx *ctx, const float *data, const void *mask, int mdt, lo
     k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mdt, n, S, 1, 9, 11, 0, 0);
     k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mdt, n, S, 1, 0, 9, 0, 1);
     ctx->launches += 9;
-    cudaMemcpyAsync(&ctx->h_bkg[0], &S->bkg, sizeof(double), cudaMemcpyDeviceToHost, st);
-    cudaMemcpyAsync(&ctx->h_bkg[1], &S->mad, sizeof(double), cudaMemcpyDeviceToHost, st);
+    zb_copy_small(ctx, &ctx->h_bkg[0], &S->bkg, sizeof(double), st);
+    zb_copy_small(ctx, &ctx->h_bkg[1], &S->mad, sizeof(double), st);
     cudaError_t e = zb_stream_wait(ctx, st);
     if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "background estimate", __FILE__, __LINE__);

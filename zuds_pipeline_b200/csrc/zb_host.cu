@@ -28,6 +28,23 @@ cudaError_t zb_stream_wait(zb_ctx *ctx, cudaStream_t st) {
     return cudaEventSynchronize(ctx->ev_sync);
 }
 
+__global__ void k_copy_words(uint32_t *__restrict__ dst, const uint32_t *__restrict__ src, size_t nwords) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nwords; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
+cudaError_t zb_copy_small(zb_ctx *ctx, void *dst, const void *src, size_t bytes, cudaStream_t st) {
+    static int use_dma = -1;
+    if (use_dma < 0) { const char *e = getenv("ZB_SMALL_COPY"); use_dma = (e && e[0] == 'd') ? 1 : 0; }     // "dma": cudaMemcpyAsync
+    if (bytes == 0) return cudaSuccess;
+    if (use_dma || (bytes & 3) || ((uintptr_t)dst & 3) || ((uintptr_t)src & 3))
+        return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, st);
+    const size_t nwords = bytes >> 2;
+    const unsigned blocks = (unsigned)((nwords + 255) / 256 < 64 ? (nwords + 255) / 256 : 64);
+    k_copy_words<<<blocks, 256, 0, st>>>((uint32_t *)dst, (const uint32_t *)src, nwords);
+    if (ctx) ctx->launches++;
+    return cudaGetLastError();
+}
+
 int zb_dbg_sync(zb_ctx *ctx, cudaStream_t st, const char *what) {
     static int on = -1;
     if (on < 0) { const char *e = getenv("ZB_DEBUG_SYNC"); on = (e && e[0] && e[0] != '0') ? 1 : 0; }
@@ -367,7 +384,7 @@ int zb_configure(zb_ctx *ctx, const zb_params *p) {
     cudaMemsetAsync(ctx->d_stats, 0, stat_bytes, ctx->stream);
     DMALLOC(ctx->d_qa, (size_t)sz.n_regions * 4 * sizeof(ZbQaStat));
     DMALLOC(ctx->d_qpart, (size_t)sz.n_regions * 5 * ZB_QA_NBLK * sizeof(ZbQaPart));
-    cudaMemcpyAsync(ctx->d_dev, H, sizeof(ZbDev), cudaMemcpyHostToDevice, ctx->stream);
+    zb_copy_small(ctx, ctx->d_dev, H, sizeof(ZbDev), ctx->stream);
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
     if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) { free_workspace(ctx); return zb_cuda_fail(ctx, e, "configure", __FILE__, __LINE__); }
@@ -411,10 +428,10 @@ static int resolve_region(zb_ctx *ctx, int r, const float *conv_img, cudaStream_
             memset(C, 0, sizeof *C);
             C->region = r; C->gk = gk; C->gl = gl; C->sx0 = sx0; C->sy0 = sy0; C->spx = spx; C->spy = spy; C->kft = kft;
             C->in_mode = s_mode; C->in_fwhm = s_fwhm; C->mean = s_mean; C->sd = s_sd; C->median = s_median; C->lfwhm = s_lfwhm; C->sum = s_sum;
-            cudaMemcpyAsync(&ctx->d_cells[ci], C, sizeof(ZbCell), cudaMemcpyHostToDevice, st);
+            zb_copy_small(ctx, &ctx->d_cells[ci], C, sizeof(ZbCell), st);
             int rc = zb_launch_stamp_search(ctx, conv_img, ci, 1, st);
             if (rc != ZB_OK) { *rc_out = rc; return 0; }
-            cudaMemcpyAsync(C, &ctx->d_cells[ci], sizeof(ZbCell), cudaMemcpyDeviceToHost, st);
+            zb_copy_small(ctx, C, &ctx->d_cells[ci], sizeof(ZbCell), st);
             if (zb_stream_wait(ctx, st) != cudaSuccess) { *rc_out = zb_cuda_fail(ctx, cudaGetLastError(), "stamp re-search", __FILE__, __LINE__); return 0; }
         }
         if (C->nss > 0) { kept++; s_mode = s_fwhm = s_mean = s_sd = s_median = s_lfwhm = s_sum = 0; }
@@ -434,12 +451,12 @@ int zb_finish_readback(zb_ctx *ctx, zb_region_info *regions, double *kernel_sol,
     const zb_sizes &sz = ctx->sz;
     ZbDev *H = ctx->h_dev;
     const int nR = sz.n_regions;
-    cudaMemcpyAsync(ctx->h_stamps, ctx->d_stamps, (size_t)ctx->n_slots * sizeof(ZbStamp), cudaMemcpyDeviceToHost, st);
-    cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, (size_t)nR * 64 * sizeof(double), cudaMemcpyDeviceToHost, st);
+    zb_copy_small(ctx, ctx->h_stamps, ctx->d_stamps, (size_t)ctx->n_slots * sizeof(ZbStamp), st);
+    zb_copy_small(ctx, ctx->h_stats, ctx->d_stats, (size_t)nR * 64 * sizeof(double), st);
     double *h_sol = (double *)((char *)ctx->h_stats + (size_t)nR * 64 * sizeof(double));
-    cudaMemcpyAsync(h_sol, ctx->d_sol, (size_t)nR * (sz.n_comp_total + 1) * sizeof(double), cudaMemcpyDeviceToHost, st);
+    zb_copy_small(ctx, h_sol, ctx->d_sol, (size_t)nR * (sz.n_comp_total + 1) * sizeof(double), st);
     double *h_ks = h_sol + (size_t)nR * (sz.n_comp_total + 1);
-    cudaMemcpyAsync(h_ks, ctx->d_kstat, (size_t)nR * 4 * sizeof(double), cudaMemcpyDeviceToHost, st);
+    zb_copy_small(ctx, h_ks, ctx->d_kstat, (size_t)nR * 4 * sizeof(double), st);
     STAGE(9);
     SYNC("final read-back");
     if (timing >= 1) for (int i = 0; i < 9; i++) cudaEventElapsedTime(&ctx->ms[i], ctx->ev[i], ctx->ev[i + 1]);
@@ -499,15 +516,15 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
     // ---- stage 0: input masks
     STAGE(0);
     for (int r = 0; r < nR; r++) { H->reg[r].skip = 0; H->reg[r].own_x1 = H->reg[r].rx1; H->reg[r].own_y1 = H->reg[r].ry1; }
-    cudaMemcpyAsync(ctx->d_dev, H, sizeof(ZbDev), cudaMemcpyHostToDevice, st);     // scalars of THIS call
+    zb_copy_small(ctx, ctx->d_dev, H, sizeof(ZbDev), st);     // scalars of THIS call
     CHECK_RC(zb_launch_input_mask(ctx, sci, ref, sci_mask, sci_mask_dtype, ref_mask, ref_mask_dtype, st));
 
     // ---- stage 1: stamp statistics + sub-stamp search, all grid cells of all regions at once
     STAGE(1);
     for (int r = 0; r < nR; r++) zb_init_cells(ctx, r, p->ker_fit_thresh);
-    cudaMemcpyAsync(ctx->d_cells, ctx->h_cells, (size_t)ctx->n_cells * sizeof(ZbCell), cudaMemcpyHostToDevice, st);
+    zb_copy_small(ctx, ctx->d_cells, ctx->h_cells, (size_t)ctx->n_cells * sizeof(ZbCell), st);
     CHECK_RC(zb_launch_stamp_search(ctx, conv_img, 0, ctx->n_cells, st));
-    cudaMemcpyAsync(ctx->h_cells, ctx->d_cells, (size_t)ctx->n_cells * sizeof(ZbCell), cudaMemcpyDeviceToHost, st);
+    zb_copy_small(ctx, ctx->h_cells, ctx->d_cells, (size_t)ctx->n_cells * sizeof(ZbCell), st);
     SYNC("stamp search");
     {   // diagnostics: mean SM kilo-cycles per grid cell in the two halves of k_stamp_search
         double a = 0, b = 0;
@@ -532,9 +549,9 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
             kft *= p->scale_fit_thresh;
             zb_init_cells(ctx, r, kft);
             const int c0 = r * sz.n_stamps;
-            cudaMemcpyAsync(&ctx->d_cells[c0], &ctx->h_cells[c0], (size_t)sz.n_stamps * sizeof(ZbCell), cudaMemcpyHostToDevice, st);
+            zb_copy_small(ctx, &ctx->d_cells[c0], &ctx->h_cells[c0], (size_t)sz.n_stamps * sizeof(ZbCell), st);
             CHECK_RC(zb_launch_stamp_search(ctx, conv_img, c0, sz.n_stamps, st));
-            cudaMemcpyAsync(&ctx->h_cells[c0], &ctx->d_cells[c0], (size_t)sz.n_stamps * sizeof(ZbCell), cudaMemcpyDeviceToHost, st);
+            zb_copy_small(ctx, &ctx->h_cells[c0], &ctx->d_cells[c0], (size_t)sz.n_stamps * sizeof(ZbCell), st);
             SYNC("stamp search retry");
             kept = resolve_region(ctx, r, conv_img, st, &rc);
             CHECK_RC(rc);
@@ -574,9 +591,9 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
         cudaMemsetAsync(noise, 0, (size_t)p->nx * p->ny * sizeof(float), st);
         if (out_mask) cudaMemsetAsync(out_mask, 0, (size_t)p->nx * p->ny * sizeof(int32_t), st);
     }
-    cudaMemcpyAsync(ctx->d_dev, H, sizeof(ZbDev), cudaMemcpyHostToDevice, st);
-    cudaMemcpyAsync(ctx->d_stamps, ctx->h_stamps, (size_t)ctx->n_slots * sizeof(ZbStamp), cudaMemcpyHostToDevice, st);
-    cudaMemcpyAsync(ctx->d_fit, ctx->h_fit, (size_t)nR * sizeof(ZbFit), cudaMemcpyHostToDevice, st);
+    zb_copy_small(ctx, ctx->d_dev, H, sizeof(ZbDev), st);
+    zb_copy_small(ctx, ctx->d_stamps, ctx->h_stamps, (size_t)ctx->n_slots * sizeof(ZbStamp), st);
+    zb_copy_small(ctx, ctx->d_fit, ctx->h_fit, (size_t)nR * sizeof(ZbFit), st);
 
     // ---- stage 3: fill every kept stamp (alard.c:50-132)
     STAGE(3);
@@ -584,7 +601,7 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
     {
         int *jobs = (int *)ctx->h_stats;      // pinned scratch
         for (int r = 0; r < nR; r++) for (int k = 0; k < ctx->h_fit[r].n_stamps; k++) jobs[njobs++] = H->reg[r].stamp_base + k;
-        cudaMemcpyAsync(ctx->d_jobs, jobs, (size_t)njobs * sizeof(int), cudaMemcpyHostToDevice, st);
+        zb_copy_small(ctx, ctx->d_jobs, jobs, (size_t)njobs * sizeof(int), st);
         CHECK_RC(zb_launch_fill(ctx, conv_img, ref_img, ctx->d_jobs, njobs, st));
     }
 
@@ -594,8 +611,8 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
     int guard = 0;
     while (any_active) {
         CHECK_RC(zb_launch_fit_iteration(ctx, conv_img, ref_img, sci, ref, sci_rms, ref_rms, st));
-        cudaMemcpyAsync(ctx->h_fit, ctx->d_fit, (size_t)nR * sizeof(ZbFit), cudaMemcpyDeviceToHost, st);
-        cudaMemcpyAsync(ctx->h_njobs, ctx->d_njobs, sizeof(int), cudaMemcpyDeviceToHost, st);
+        zb_copy_small(ctx, ctx->h_fit, ctx->d_fit, (size_t)nR * sizeof(ZbFit), st);
+        zb_copy_small(ctx, ctx->h_njobs, ctx->d_njobs, sizeof(int), st);
         SYNC("fit iteration");
         any_active = false;
         for (int r = 0; r < nR; r++) any_active |= ctx->h_fit[r].active != 0;

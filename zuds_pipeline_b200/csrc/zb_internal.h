@@ -164,6 +164,13 @@ cudaError_t zb_stream_wait(zb_ctx *ctx, cudaStream_t st);
 int zb_dbg_sync(zb_ctx *ctx, cudaStream_t st, const char *what);
 #define ZB_DBG(what) do { int rc_d = zb_dbg_sync(ctx, st, what); if (rc_d != ZB_OK) return rc_d; } while (0)
 
+// Small control transfers (cell records, stamp table, fit state, job lists) between PINNED host memory and the
+// device, done by a copy KERNEL through the unified address space instead of cudaMemcpyAsync: the copy engines
+// are FIFOs shared by every context of the GPU, and a 200-byte read-back queued behind another pair's 38 MB image
+// copy waits milliseconds (measured: fit loop 4.8 -> 10.5 ms per pair with the D2H engine busy).  dst/src: one
+// device pointer and one cudaMallocHost pointer (or two device pointers), 4-byte aligned, bytes a multiple of 4.
+cudaError_t zb_copy_small(zb_ctx *ctx, void *dst, const void *src, size_t bytes, cudaStream_t st);
+
 // kernel launchers (each returns a zb_status)
 int zb_launch_input_mask(zb_ctx *ctx, const float *sci, const float *ref, const void *smask, int sdt,
                          const void *tmask, int tdt, cudaStream_t st, int y_lo = 0, int y_hi = 0x7fffffff);

@@ -72,10 +72,10 @@ static int search_own(zb_ctx *ctx) {
     cudaStream_t st = T.st;
     const float *conv_img = ctx->h_dev->conv_template ? T.ref : T.sci;
     zb_init_cells(ctx, 0, T.kft);
-    cudaMemcpyAsync(ctx->d_cells, ctx->h_cells, (size_t)ctx->n_cells * sizeof(ZbCell), cudaMemcpyHostToDevice, st);
+    zb_copy_small(ctx, ctx->d_cells, ctx->h_cells, (size_t)ctx->n_cells * sizeof(ZbCell), st);
     if (T.cell_hi > T.cell_lo) {
         CHECK_RC(zb_launch_stamp_search(ctx, conv_img, T.cell_lo, T.cell_hi - T.cell_lo, st));
-        cudaMemcpyAsync(&ctx->h_cells[T.cell_lo], &ctx->d_cells[T.cell_lo], (size_t)(T.cell_hi - T.cell_lo) * sizeof(ZbCell), cudaMemcpyDeviceToHost, st);
+        zb_copy_small(ctx, &ctx->h_cells[T.cell_lo], &ctx->d_cells[T.cell_lo], (size_t)(T.cell_hi - T.cell_lo) * sizeof(ZbCell), st);
     }
     return ZB_OK;
 }
@@ -105,7 +105,7 @@ extern "C" int zb_tile_begin(zb_ctx *ctx, const zb_params *p, int world, int ran
     ctx->err[0] = 0;
     memset(ctx->ms, 0, sizeof ctx->ms);
     H->reg[0].skip = 0; H->reg[0].own_x1 = H->reg[0].rx1; H->reg[0].own_y1 = H->reg[0].ry1;
-    cudaMemcpyAsync(ctx->d_dev, H, sizeof(ZbDev), cudaMemcpyHostToDevice, st);
+    zb_copy_small(ctx, ctx->d_dev, H, sizeof(ZbDev), st);
     CHECK_RC(zb_launch_input_mask(ctx, sci, ref, sci_mask, sci_mask_dtype, ref_mask, ref_mask_dtype, st, T.info.in_row0, T.info.in_row1));
     T.on = 1;
     return search_own(ctx);
@@ -204,9 +204,9 @@ extern "C" int zb_tile_resolve(zb_ctx *ctx, int *action, int *cell) {
         cudaMemsetAsync(T.noise + r0 * row_elems, 0, nrow * row_elems * sizeof(float), st);
         if (T.out_mask) cudaMemsetAsync(T.out_mask + r0 * row_elems, 0, nrow * row_elems * sizeof(int32_t), st);
     }
-    cudaMemcpyAsync(ctx->d_dev, H, sizeof(ZbDev), cudaMemcpyHostToDevice, st);
-    cudaMemcpyAsync(ctx->d_stamps, ctx->h_stamps, (size_t)ctx->n_slots * sizeof(ZbStamp), cudaMemcpyHostToDevice, st);
-    cudaMemcpyAsync(ctx->d_fit, ctx->h_fit, sizeof(ZbFit), cudaMemcpyHostToDevice, st);
+    zb_copy_small(ctx, ctx->d_dev, H, sizeof(ZbDev), st);
+    zb_copy_small(ctx, ctx->d_stamps, ctx->h_stamps, (size_t)ctx->n_slots * sizeof(ZbStamp), st);
+    zb_copy_small(ctx, ctx->d_fit, ctx->h_fit, sizeof(ZbFit), st);
     return ZB_OK;
 }
 
@@ -221,9 +221,9 @@ extern "C" int zb_tile_research(zb_ctx *ctx, int cell) {
     memset(C, 0, sizeof *C);
     C->region = 0; C->gk = gk; C->gl = gl; C->sx0 = sx0; C->sy0 = sy0; C->spx = spx; C->spy = spy; C->kft = kft;
     C->in_mode = T.pend[0]; C->in_fwhm = T.pend[1]; C->mean = T.pend[2]; C->sd = T.pend[3]; C->median = T.pend[4]; C->lfwhm = T.pend[5]; C->sum = T.pend[6];
-    cudaMemcpyAsync(&ctx->d_cells[cell], C, sizeof(ZbCell), cudaMemcpyHostToDevice, st);
+    zb_copy_small(ctx, &ctx->d_cells[cell], C, sizeof(ZbCell), st);
     CHECK_RC(zb_launch_stamp_search(ctx, ctx->h_dev->conv_template ? T.ref : T.sci, cell, 1, st));
-    cudaMemcpyAsync(C, &ctx->d_cells[cell], sizeof(ZbCell), cudaMemcpyDeviceToHost, st);
+    zb_copy_small(ctx, C, &ctx->d_cells[cell], sizeof(ZbCell), st);
     SYNC("stamp re-search");
     return ZB_OK;
 }
@@ -249,7 +249,7 @@ static int fill_slots(zb_ctx *ctx, const int *slots, int n) {
     const bool ct = ctx->h_dev->conv_template != 0;
     int *jobs = ctx->h_njobs + 4;                         // pinned, n_slots ints (see zb_configure)
     for (int i = 0; i < n; i++) jobs[i] = slots ? slots[i] : T.slot_lo + i;
-    cudaMemcpyAsync(ctx->d_jobs, jobs, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, T.st);
+    zb_copy_small(ctx, ctx->d_jobs, jobs, (size_t)n * sizeof(int), T.st);
     return zb_launch_fill(ctx, ct ? T.ref : T.sci, ct ? T.sci : T.ref, ctx->d_jobs, n, T.st);
 }
 
@@ -331,9 +331,9 @@ extern "C" int zb_tile_clip(zb_ctx *ctx, int *active) {
     cudaStream_t st = T.st;
     CHECK_RC(zb_launch_clip(ctx, st));
     int *h_jobs = ctx->h_njobs + 4;
-    cudaMemcpyAsync(ctx->h_fit, ctx->d_fit, sizeof(ZbFit), cudaMemcpyDeviceToHost, st);
-    cudaMemcpyAsync(ctx->h_njobs, ctx->d_njobs, sizeof(int), cudaMemcpyDeviceToHost, st);
-    cudaMemcpyAsync(h_jobs, ctx->d_jobs, (size_t)ctx->n_slots * sizeof(int), cudaMemcpyDeviceToHost, st);
+    zb_copy_small(ctx, ctx->h_fit, ctx->d_fit, sizeof(ZbFit), st);
+    zb_copy_small(ctx, ctx->h_njobs, ctx->d_njobs, sizeof(int), st);
+    zb_copy_small(ctx, h_jobs, ctx->d_jobs, (size_t)ctx->n_slots * sizeof(int), st);
     SYNC("clip");
     *active = ctx->h_fit[0].active != 0;
     // the slots check_again replaced (alard.c:1196-1234): each owner refills its own
