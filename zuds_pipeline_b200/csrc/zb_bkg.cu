@@ -151,7 +151,7 @@ static int bkg_run(zb_ctx *ctx, const float *data, const void *mask, int mdt, lo
         if (cudaMallocHost((void **)&ctx->h_bkg, 2 * sizeof(double)) != cudaSuccess) { snprintf(ctx->err, sizeof ctx->err, "cudaMallocHost failed"); return ZB_ERR_NOMEM; }
     }
     BkState *S = (BkState *)ctx->d_bkg;
-    cudaMemsetAsync(S, 0, sizeof(BkState), st);
+    zb_zero_small(ctx, S, sizeof(BkState), st);
     long long want = (n + BK_NT * 16 - 1) / (BK_NT * 16);
     const int grid = (int)(want < 1 ? 1 : (want > 148 * 8 ? 148 * 8 : want));
     // median of x: 32-bit keys in the high half of the 64-bit key

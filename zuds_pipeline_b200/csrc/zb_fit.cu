@@ -844,7 +844,7 @@ int zb_launch_clip(zb_ctx *ctx, cudaStream_t st)
 {
     const zb_sizes &sz = ctx->sz;
     const int nR = sz.n_regions;
-    cudaMemsetAsync(ctx->d_njobs, 0, sizeof(int), st);
+    zb_zero_small(ctx, ctx->d_njobs, sizeof(int), st);
     k_clip<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, (float *)ctx->d_stats, (char *)(ctx->d_stats) + (size_t)nR * sz.n_stamps * sizeof(float),
                                           ctx->d_jobs, ctx->d_njobs); ZB_DBG("k_clip");
     ctx->launches++;

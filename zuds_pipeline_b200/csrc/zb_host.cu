@@ -45,6 +45,20 @@ cudaError_t zb_copy_small(zb_ctx *ctx, void *dst, const void *src, size_t bytes,
     return cudaGetLastError();
 }
 
+__global__ void k_zero_words(uint32_t *__restrict__ dst, size_t nwords) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nwords; i += (size_t)gridDim.x * blockDim.x) dst[i] = 0u;
+}
+
+cudaError_t zb_zero_small(zb_ctx *ctx, void *dst, size_t bytes, cudaStream_t st) {
+    if (bytes == 0) return cudaSuccess;
+    if ((bytes & 3) || ((uintptr_t)dst & 3)) return cudaMemsetAsync(dst, 0, bytes, st);
+    const size_t nwords = bytes >> 2;
+    const unsigned blocks = (unsigned)((nwords + 255) / 256 < 64 ? (nwords + 255) / 256 : 64);
+    k_zero_words<<<blocks, 256, 0, st>>>((uint32_t *)dst, nwords);
+    if (ctx) ctx->launches++;
+    return cudaGetLastError();
+}
+
 int zb_dbg_sync(zb_ctx *ctx, cudaStream_t st, const char *what) {
     static int on = -1;
     if (on < 0) { const char *e = getenv("ZB_DEBUG_SYNC"); on = (e && e[0] && e[0] != '0') ? 1 : 0; }

@@ -170,6 +170,8 @@ int zb_dbg_sync(zb_ctx *ctx, cudaStream_t st, const char *what);
 // copy waits milliseconds (measured: fit loop 4.8 -> 10.5 ms per pair with the D2H engine busy).  dst/src: one
 // device pointer and one cudaMallocHost pointer (or two device pointers), 4-byte aligned, bytes a multiple of 4.
 cudaError_t zb_copy_small(zb_ctx *ctx, void *dst, const void *src, size_t bytes, cudaStream_t st);
+// the same for small device memsets to zero (a memset node may also be served by a copy engine)
+cudaError_t zb_zero_small(zb_ctx *ctx, void *dst, size_t bytes, cudaStream_t st);
 
 // kernel launchers (each returns a zb_status)
 int zb_launch_input_mask(zb_ctx *ctx, const float *sci, const float *ref, const void *smask, int sdt,

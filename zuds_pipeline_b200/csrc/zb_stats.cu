@@ -89,7 +89,7 @@ __global__ void k_final_clip(const ZbDev *__restrict__ D, const ZbStamp *__restr
 int zb_launch_final_sig(zb_ctx *ctx, cudaStream_t st) {
     const zb_sizes &sz = ctx->sz;
     const int nR = sz.n_regions, npix = sz.fw_ksstamp * sz.fw_ksstamp;
-    cudaMemsetAsync(ctx->d_stats, 0, (size_t)nR * 64 * sizeof(double), st);
+    zb_zero_small(ctx, ctx->d_stats, (size_t)nR * 64 * sizeof(double), st);
     size_t sm = (size_t)npix * (sizeof(double) + 1) + 16;
     cudaFuncSetAttribute(k_final_sig, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
     k_final_sig<<<ctx->n_slots, 256, sm, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask); ZB_DBG("k_final_sig");
