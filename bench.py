@@ -231,11 +231,12 @@ def bench_b200(args):
         dev_in.append([None if t is None else t.cuda(non_blocking=True) for t in pinned])
     torch.cuda.synchronize()
 
-    # contexts per GPU: each is a host thread that spins while it waits for its stream.  One GPU: 24 is where
-    # the end-to-end rate stops growing (16 cores).  Several ranks on one box: one thread per core share
-    # (measured on 8 B200 / 32 cores: 4 contexts 1330 pairs/s, 6: 1227, 12: 1167, 16: 1180)
+    # contexts per GPU: each is a host thread that polls its stream and yields the core between polls
+    # (zb_stream_wait, ZB_SYNC=yield), so the count does not depend on the cores: 24 is where the rate stops
+    # growing, with 16 cores or with 4 (taskset -c 0-3: 225.9 / 193.7 pairs/s; busy-waiting needed a core per
+    # thread and gave 196 / 151 with 4 contexts on 4 cores)
     cores = host_cores()
-    W = args.workers or (24 if 24 * world <= 1.5 * cores else max(4, cores // world))
+    W = args.workers or 24
     B = args.batch or 4 * W
     from zuds_pipeline_b200.batch import GpuPool
     pool = GpuPool(local, W)
