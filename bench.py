@@ -206,6 +206,18 @@ def bench_b200(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the subtraction path has no CPU fallback")
+    pinned_cores, box_cores = None, host_cores()
+    if world > 1 and not args.no_pin:
+        # one rank per GPU, each on its own share of the box's cores (what a production launcher does):
+        # the worker threads of a rank yield to each other, not to another rank's
+        try:
+            avail = sorted(os.sched_getaffinity(0))
+            share = len(avail) // world
+            if share >= 1:
+                pinned_cores = avail[local * share:(local + 1) * share]
+                os.sched_setaffinity(0, pinned_cores)
+        except (AttributeError, OSError):
+            pinned_cores = None
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -235,7 +247,7 @@ def bench_b200(args):
     # (zb_stream_wait, ZB_SYNC=yield), so the count does not depend on the cores: 24 is where the rate stops
     # growing, with 16 cores or with 4 (taskset -c 0-3: 225.9 / 193.7 pairs/s; busy-waiting needed a core per
     # thread and gave 196 / 151 with 4 contexts on 4 cores)
-    cores = host_cores()
+    cores = box_cores
     W = args.workers or 24
     B = args.batch or 4 * W
     from zuds_pipeline_b200.batch import GpuPool
@@ -341,7 +353,7 @@ def bench_b200(args):
         "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "c1: 3080x3072 quadrant pair, -c t -n i -r 10 -rss 24 -ko 2 -bgo 0, 3x3 regions x 10x10 stamps (BASELINE configs[1])",
-                   "pairs_per_step_per_gpu": B, "contexts_per_gpu": W, "host_cores": cores, "distinct_pairs_per_gpu": npairs_distinct,
+                   "pairs_per_step_per_gpu": B, "contexts_per_gpu": W, "host_cores": cores, "rank_cores": None if pinned_cores is None else len(pinned_cores), "distinct_pairs_per_gpu": npairs_distinct,
                    "l2": "inputs of one pair are 161 MB (> 126 MB L2) and consecutive jobs alternate pairs",
                    "sharding": "by image pair, no collective"},
         "e2e": {"value": pairs_total / host_s, "unit": UNIT, "h2d_bytes_per_step": in_bytes * B, "d2h_bytes_per_step": out_bytes * B,
@@ -388,6 +400,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="pair subtractions per step per GPU (0: 4 per context)")
     ap.add_argument("--cpu-procs", type=int, default=0, help="reference arm: concurrent hotpants processes (0 = all cores)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-pin", action="store_true", help="(N > 1) do not bind each rank to its share of the cores")
     ap.add_argument("--no-clocks", action="store_true", help="(diagnostics) do not sample clocks during the timed region")
     ap.add_argument("--verbose", action="store_true")
     args = ap.parse_args()
