@@ -32,6 +32,9 @@ import time
 
 import numpy as np
 
+# hardware work queues for the concurrent contexts (see zuds_pipeline_b200/_lib.py); must precede CUDA initialisation
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -244,11 +247,11 @@ def bench_b200(args):
     torch.cuda.synchronize()
 
     # contexts per GPU: each is a host thread that polls its stream and yields the core between polls
-    # (zb_stream_wait, ZB_SYNC=yield), so the count does not depend on the cores: 24 is where the rate stops
+    # (zb_stream_wait, ZB_SYNC=yield), so the count does not depend on the cores: 24-32 is where the rate stops
     # growing, with 16 cores or with 4 (taskset -c 0-3: 225.9 / 193.7 pairs/s; busy-waiting needed a core per
     # thread and gave 196 / 151 with 4 contexts on 4 cores)
     cores = box_cores
-    W = args.workers or 24
+    W = args.workers or 32
     B = args.batch or 4 * W
     from zuds_pipeline_b200.batch import GpuPool
     pool = GpuPool(local, W)
@@ -396,7 +399,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workers", type=int, default=0, help="concurrent contexts (streams) per GPU (0: from the host core count, at most 24)")
+    ap.add_argument("--workers", type=int, default=0, help="concurrent contexts (streams) per GPU (0: 32)")
     ap.add_argument("--batch", type=int, default=0, help="pair subtractions per step per GPU (0: 4 per context)")
     ap.add_argument("--cpu-procs", type=int, default=0, help="reference arm: concurrent hotpants processes (0 = all cores)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

@@ -185,3 +185,10 @@ def test_hotpants_cli_shim(oracle, tmp_path):
     bad = subprocess.run([sys.executable, os.path.join(ROOT, "bin", "hotpants"), "-inim", "nope.fits", "-tmplim", "x", "-outim", "y"],
                          capture_output=True, text=True)
     assert bad.returncode != 0
+
+
+def test_import_sets_hardware_queue_default():
+    """the binding asks for 32 CUDA work queues before the first CUDA call unless the caller chose a value"""
+    import os
+    from zuds_pipeline_b200 import _lib  # noqa: F401
+    assert os.environ.get("CUDA_DEVICE_MAX_CONNECTIONS") is not None

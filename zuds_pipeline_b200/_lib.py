@@ -9,6 +9,13 @@ import numpy as np
 
 from . import params as P
 
+# Concurrent contexts (one stream each) share the GPU's hardware work queues; with the default of 8 queues a
+# stream that waits for its input copy holds up other pairs' kernels queued behind it (measured on B200, 24
+# contexts: 227 -> 236 pairs/s device-resident, 198 -> 219 end to end with 32 queues).  Read by the CUDA
+# runtime when the process creates its context, so it is set here, before the first CUDA call, unless the
+# caller chose a value.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libzb200.so")
 ZB_NSTAGES = 12
