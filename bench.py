@@ -45,6 +45,7 @@ SHAPE = (3080, 3072)
 ALG_BYTES_PER_PIXEL = 29          # 4 float inputs + 1 mask byte in, 2 floats + int32 mask out
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_convolve launch at C1, from the ncu --set full
 # capture summarised in profiles/r01_ncu_k_convolve_s17.txt (251.88 MB + 188.61 MB)
+FP64_PEAK_TDFMA = 16.77
 NCU_CONV_TRAFFIC_BYTES = 440489472
 
 
@@ -370,6 +371,12 @@ def bench_b200(args):
                      "alg_bytes_per_launch": alg_bytes, "kernel_ms": stage_ms["k_convolve"],
                      "kernel_ms_in_timed_region": statistics.mean(conv_ms) if conv_ms else None,
                      "fp64_dfma_per_launch": 2 * (2 * params[0].hw_kernel + 1) ** 2 * nx * ny,
+                     # the pipe that actually bounds this kernel: FP64 FMA, peak measured on this pool's B200 with
+                     # tools/fp64_peak.cu (profiles/r01_fp64_peak_b200.txt: 57.7 DFMA/clk/SM = 16.77 T DFMA/s at 1965 MHz)
+                     "fp64": {"achieved": 2 * (2 * params[0].hw_kernel + 1) ** 2 * nx * ny / (stage_ms["k_convolve"] * 1e-3) / 1e12,
+                              "peak": FP64_PEAK_TDFMA, "unit": "T DFMA/s",
+                              "frac": 2 * (2 * params[0].hw_kernel + 1) ** 2 * nx * ny / (stage_ms["k_convolve"] * 1e-3) / 1e12 / FP64_PEAK_TDFMA,
+                              "peak_source": "measured (tools/fp64_peak.cu)"},
                      "note": "compute-bound at hw=10 (2x441 FP64 FMA per pixel, reference semantics); HBM fraction reported as the north star asks"},
         "stage_ms_serial": {k: round(v, 4) for k, v in stage_ms.items()},
         "wall_s": wall,
