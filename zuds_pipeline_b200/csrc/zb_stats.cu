@@ -274,7 +274,7 @@ __device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *p
     if (Q.tries >= 5) { Q.status = 1; Q.phase = 2; }
 }
 
-template <int MINB>
+template <int MINB, int ROT>
 __global__ void __launch_bounds__(256, MINB)
 k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const float *__restrict__ rnoise,
           int32_t *__restrict__ omask, int32_t *__restrict__ out_mask, ZbQaStat *qa,
@@ -375,12 +375,20 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
             }
             continue;
         }
-#pragma unroll
+        // generic form (a statistic in its histogram phase or clipping with the exact criteria, or a NaN/Inf in
+        // the batch): ONE copy of the code, the batch rotated through element 0 — unrolled four times this
+        // kernel was 13.7 k instructions and stalled on instruction fetch
+#pragma unroll (ROT ? 1 : 4)
         for (int u = 0; u < 4; u++) {
             const int k = kb + u * stride;
             if (k >= npix) break;
-            const float d = dv[u], nz = nv[u];
-            const int m0 = mv[u];
+            const float d = dv[ROT ? 0 : u], nz = nv[ROT ? 0 : u];
+            const int m0 = mv[ROT ? 0 : u];
+            if (ROT) {
+                dv[0] = dv[1]; dv[1] = dv[2]; dv[2] = dv[3];
+                nv[0] = nv[1]; nv[1] = nv[2]; nv[2] = nv[3];
+                mv[0] = mv[1]; mv[1] = mv[2]; mv[2] = mv[3];
+            }
             const bool nfd = (d * 0.0f != 0.0f), nfn = (nz * 0.0f != 0.0f);
             if (!(nfd || nfn)) {
                 // GOOD pixels (no mask bit at all) and OK pixels (a bit in 0xff, not OUTPUT_ISBAD) are disjoint
@@ -496,19 +504,21 @@ int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStr
     // at most maxiter (5) clip passes + 5 histogram passes; finished regions fall through at once.
     // CTAs per region: enough to put ~4 CTAs on every SM whatever the number of regions (a single-region
     // coadd-scale frame would otherwise stream 38 Mpx through 64 CTAs)
-    static int minb = 0, use_div = 0;
+    static int minb = 0, use_div = 0, rot = -1;
+    if (rot < 0) { const char *e = getenv("ZB_QA_ROT"); rot = e ? atoi(e) : 1; }
     { const char *e = getenv("ZB_QA_DIV"); use_div = (e && e[0] == '1') ? 1 : 0; }
     // 4 CTAs/SM: 9 regions x 64 CTAs = one resident wave (A/B on B200: 1.47 ms vs 1.65 at 3)
     if (!minb) { const char *e = getenv("ZB_QA_MINB"); minb = e ? atoi(e) : 4; }
     int nblk = nR >= 5 ? ZB_QA_NBLK_MIN : (4 * 148 + nR - 1) / nR;
     nblk = nblk < ZB_QA_NBLK_MIN ? ZB_QA_NBLK_MIN : (nblk > ZB_QA_NBLK ? ZB_QA_NBLK : nblk);
     for (int pass = 0; pass < 10; pass++) {
-        if (minb == 3) k_qa_pass<3><<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
-                                                                   ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0, use_div);
-        else if (minb == 4) k_qa_pass<4><<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
-                                                                   ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0, use_div);
-        else k_qa_pass<2><<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask,
-                                                         ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0, use_div);
+#define QA_LAUNCH(M, R) k_qa_pass<M, R><<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask, \
+                                                                  ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0, use_div)
+        if (!rot) QA_LAUNCH(4, 0);                  // ZB_QA_ROT=0: the generic form unrolled four times (A/B)
+        else if (minb == 3) QA_LAUNCH(3, 1);
+        else if (minb == 4) QA_LAUNCH(4, 1);
+        else QA_LAUNCH(2, 1);
+#undef QA_LAUNCH
         ZB_DBG("k_qa_pass");
         ctx->launches++;
     }
