@@ -377,6 +377,10 @@ def bench_b200(args):
                               "peak": FP64_PEAK_TDFMA, "unit": "T DFMA/s",
                               "frac": 2 * (2 * params[0].hw_kernel + 1) ** 2 * nx * ny / (stage_ms["k_convolve"] * 1e-3) / 1e12 / FP64_PEAK_TDFMA,
                               "peak_source": "measured (tools/fp64_peak.cu)"},
+                     # SURVEY.md 8(d)'s figure: ALG_FLOPS_CONV = 4 nx ny (2hw+1)^2 against the 74.4 TFLOP/s FP32 CUDA-core
+                     # peak; the products are float x double accumulated in double (alard.c:1289-1306), so the FP64 pipe above is the bound
+                     "alg_flops_conv": 4 * (2 * params[0].hw_kernel + 1) ** 2 * nx * ny,
+                     "frac_of_fp32_peak_74.4T": 4 * (2 * params[0].hw_kernel + 1) ** 2 * nx * ny / (stage_ms["k_convolve"] * 1e-3) / 74.4e12,
                      "note": "compute-bound at hw=10 (2x441 FP64 FMA per pixel, reference semantics); HBM fraction reported as the north star asks"},
         "stage_ms_serial": {k: round(v, 4) for k, v in stage_ms.items()},
         "wall_s": wall,
