@@ -76,7 +76,10 @@ def golden_of(case):
 
 
 def main():
-    for case in CS.SMALL + [CS.TINY_FULL]:
+    only = set(sys.argv[1:])
+    for case in CS.SMALL + CS.EXTRA + [CS.TINY_FULL]:
+        if only and case.name not in only:
+            continue
         g, pair, ref = golden_of(case)
         with open(os.path.join(HERE, "golden_%s.json" % case.name), "w") as f:
             json.dump(g, f, indent=1, sort_keys=True)

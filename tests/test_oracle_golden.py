@@ -87,7 +87,7 @@ def check_against_golden(case, res, gold, exact=True, pair=None):
                                          if mine.get(k) != gold["region_keys"].get(k)}
 
 
-@pytest.mark.parametrize("case", CS.SMALL + [CS.TINY_FULL], ids=lambda c: c.name)
+@pytest.mark.parametrize("case", CS.SMALL + CS.EXTRA + [CS.TINY_FULL], ids=lambda c: c.name)
 def test_oracle_matches_reference_golden(case, oracle):
     pair = CS.make_pair(case)
     gold = load_golden(case.name)
