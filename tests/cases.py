@@ -44,6 +44,11 @@ SMALL = [
     # different basis: 2 Gaussians, 3x3 regions, non-default clipping
     Case("two_gauss_3x3", (600, 640), 2.0, 3, {"ko": 1, "ng": "2 4 0.8 2 2.0", "ks": 1.5},
          dict(nstars=900, bad_frac=1e-4)),
+    # cubic kernel variation, quadratic background, 2x1 regions on a non-square frame
+    Case("ko3_bgo2_2x1", (420, 560), 2.0, 1, {"ko": 3, "bgo": 2}, dict(nstars=520, bad_frac=2e-4), replace={"-nrx": 2}),
+    # no photometric scaling of the difference (-n u), science image convolved, no mask file
+    Case("norm_u_nomask", (384, 400), 2.4, 1, {"ko": 1}, dict(nstars=260, bad_frac=2e-4), use_mask=False,
+         replace={"-c": "i", "-n": "u"}),
 ]
 
 # Options of the path that zuds does not pass by default.  Pinned against the reference on CPU (oracle vs golden);
@@ -52,11 +57,6 @@ EXTRA = [
     # -okn: noise of OK pixels rescaled by the region's diffrat (main.c:1557-1576); -convvar: variance convolved
     # with the kernel instead of its square (alard.c:1300-1306)
     Case("okn_convvar", (400, 416), 2.2, 1, {"ko": 1}, dict(nstars=260, bad_frac=3e-4), flags=("-okn", "-convvar")),
-    # cubic kernel variation, quadratic background, 2x1 regions on a non-square frame
-    Case("ko3_bgo2_2x1", (420, 560), 2.0, 1, {"ko": 3, "bgo": 2}, dict(nstars=520, bad_frac=2e-4), replace={"-nrx": 2}),
-    # no photometric scaling of the difference (-n u), science image convolved, no mask file
-    Case("norm_u_nomask", (384, 400), 2.4, 1, {"ko": 1}, dict(nstars=260, bad_frac=2e-4), use_mask=False,
-         replace={"-c": "i", "-n": "u"}),
 ]
 
 TINY_FULL = Case("tiny_full", (200, 208), 1.3, 1, {"ko": 1}, dict(nstars=120, bad_frac=2e-4))
