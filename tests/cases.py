@@ -57,6 +57,12 @@ EXTRA = [
     # -okn: noise of OK pixels rescaled by the region's diffrat (main.c:1557-1576); -convvar: variance convolved
     # with the kernel instead of its square (alard.c:1300-1306)
     Case("okn_convvar", (400, 416), 2.2, 1, {"ko": 1}, dict(nstars=260, bad_frac=3e-4), flags=("-okn", "-convvar")),
+    # the numeric knobs away from their defaults: 2 sub-stamps per stamp, stricter bad-tap fraction, wider input-mask
+    # dilation, no output masking (-mous < 0, main.c:1584), 2.5-sigma statistics, other fill values
+    Case("knobs", (440, 420), 2.0, 1, {"ko": 1, "nss": 2, "kfm": 0.9, "mins": 2.0, "mous": -1.0, "ssig": 2.5,
+                                       "fi": -7.0, "fin": 99.0}, dict(nstars=420, bad_frac=3e-4)),
+    # kernel re-evaluated every 7 pixels instead of every 2 hw + 1 (-kcs, alard.c:1272-1278)
+    Case("kcs7", (384, 400), 2.0, 1, {"ko": 2, "kcs": 7}, dict(nstars=300, bad_frac=2e-4)),
 ]
 
 TINY_FULL = Case("tiny_full", (200, 208), 1.3, 1, {"ko": 1}, dict(nstars=120, bad_frac=2e-4))

@@ -5,8 +5,9 @@ History: three cases were added when round 1 had seconds of GPU time left.  In t
 and `norm_u_nomask` passed and moved into tests/cases.py:SMALL; `okn_convvar` did not: with -convvar the reference itself
 writes NaN noise where the convolved variance goes negative next to BIG_RMS pixels (2122 pixels in this case), and
 test_gpu_parity.compare() was not NaN-aware then.  compare() now requires NaNs on the same pixels; this case has not run
-on a GPU since, so it stays a non-strict xfail (the file sorts last so that a fault here cannot disturb other tests).
-Whoever sees it pass on a B200 moves it into SMALL; if it fails, the message names the parity difference to fix.
+on a GPU since.  `knobs` and `kcs7` were added after the round's GPU time was spent and have never run on one.  All three
+stay non-strict xfails (the file sorts last so that a fault here cannot disturb other tests).
+Whoever sees one pass on a B200 moves it into SMALL; if it fails, the message names the parity difference to fix.
 """
 import pytest
 
@@ -18,7 +19,7 @@ from test_oracle_golden import check_against_golden, input_hash, load_golden
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.xfail(strict=False, reason="not run on a GPU since compare() became NaN-aware (see the module docstring)")
+@pytest.mark.xfail(strict=False, reason="not yet confirmed on a GPU (see the module docstring)")
 @pytest.mark.parametrize("case", CS.EXTRA, ids=lambda c: c.name)
 def test_extra_cases_host_call(case, oracle, gpu_ctx):
     pair = CS.make_pair(case)
