@@ -400,8 +400,8 @@ def bench_b200(args):
 
 
 class _NullStream:
-    """Passes NULL as the stream: the ctx then runs on its own non-blocking stream."""
-    cuda_stream = 0
+    """ZB_STREAM_OWN (include/zb200.h): the ctx runs on its own non-blocking stream (= _lib.OwnStream)."""
+    cuda_stream = -1
 
 
 def main():

@@ -154,10 +154,14 @@ const char *zb_last_error(const zb_ctx *ctx);
  *   regions             host, [n_regions]                    out
  *   kernel_sol          host, [n_regions*(n_comp_total+1)] or NULL   (-hki table column per region)
  *   stamps              host, [n_regions*n_stamps] or NULL
- *   stream              cudaStream_t (as void*), NULL = ctx's own stream
+ *   stream              cudaStream_t (as void*).  NULL has CUDA's own meaning, the legacy default stream, so
+ *                       work a caller queued on its default stream (torch's, say) is ordered before this call;
+ *                       ZB_STREAM_OWN selects the context's private non-blocking stream (what batch drivers
+ *                       that run many contexts side by side want).
  * Returns when the results are complete (host outputs are filled, device outputs
  * are ordered on `stream`).
  */
+#define ZB_STREAM_OWN ((void *)(intptr_t)-1)
 int zb_subtract(zb_ctx *ctx, const zb_params *p,
                 const float *sci, const float *ref,
                 const float *sci_rms, const float *ref_rms,

@@ -88,5 +88,5 @@ def test_prepare_hotpants_command_is_unchanged_by_the_gpu_prestep(tmp_path):
             cmds.append(hotpants.prepare_hotpants(sci, ref, str(tmp_path / "sub.fits"), submask.boolean, tmp_path / "w", nreg_side=1,
                                                   subtract_new_back=False, hotpants_kws={"ko": 2}))
         finally:
-            hotpants.prestep = "auto"
+            hotpants.prestep = "gpu"
     assert cmds[0] == cmds[1]

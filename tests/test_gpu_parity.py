@@ -6,7 +6,7 @@ import pytest
 
 import cases as CS
 import hp_helpers as H
-from test_oracle_golden import check_against_golden, input_hash, load_golden, region_keywords
+from test_oracle_golden import check_against_golden, input_hash, keywords_mismatch, load_golden, region_keywords
 
 pytestmark = pytest.mark.gpu
 
@@ -36,13 +36,14 @@ def compare(o, g):
     assert dd.max() <= TOL_SIGMA, "diff off by %.3g sigma" % dd.max()
     assert dn.max() <= TOL_SIGMA, "noise off by %.3g sigma" % dn.max()
     assert np.array_equal(o.noise[sent], g.noise[sent], equal_nan=True)
-    assert region_keywords(o) == region_keywords(g)
+    bad = keywords_mismatch(region_keywords(g), region_keywords(o), exact=False)
+    assert not bad, bad
     for r in range(o.sizes.n_regions):
         a, b = o.regions[r].nscalo, g.regions[r].nscalo
-        assert ("%.4f" % a) == ("%.4f" % b)
+        assert abs(a - b) <= 2e-4 + 1e-4 * abs(a) or (a != a and b != b)
 
 
-@pytest.mark.parametrize("case", CS.SMALL + [CS.TINY_FULL], ids=lambda c: c.name)
+@pytest.mark.parametrize("case", CS.SMALL + CS.EXTRA + [CS.TINY_FULL], ids=lambda c: c.name)
 def test_small_cases_host_call(case, oracle, gpu_ctx):
     pair = CS.make_pair(case)
     p = CS.params_of(case, pair)
@@ -52,8 +53,9 @@ def test_small_cases_host_call(case, oracle, gpu_ctx):
     assert gpu_ctx.launch_count() > 0
     compare(o, g)
     gold = load_golden(case.name)
-    if input_hash(case, pair) == gold["input_sha256"]:
-        check_against_golden(case, g, gold, exact=False)
+    if input_hash(case, pair) != gold["input_sha256"]:
+        pytest.fail("synthetic generator drifted on this host: golden vectors of %s not comparable" % case.name)
+    check_against_golden(case, g, gold, exact=False)
 
 
 @pytest.mark.parametrize("case", CS.SMALL[:3], ids=lambda c: c.name)
@@ -66,6 +68,27 @@ def test_small_cases_device_call(case, oracle, gpu_ctx):
     o = H.run_oracle(oracle, p, *ins)
     dev = [None if a is None else torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in ins]
     g = gpu_ctx.subtract(p, *dev)
+    torch.cuda.synchronize()
+    g.diff, g.noise, g.mask = g.diff.cpu().numpy(), g.noise.cpu().numpy(), g.mask.cpu().numpy()
+    compare(o, g)
+
+
+def test_device_call_orders_after_async_uploads(oracle, gpu_ctx):
+    """Inputs still in flight on the caller's (default) stream when zb_subtract is called: stream handle 0 must mean
+    the legacy default stream, not the context's private stream (round-1 advisor finding)."""
+    import torch
+    case = CS.SMALL[0]
+    pair = CS.make_pair(case)
+    p = CS.params_of(case, pair)
+    ins = CS.inputs_of(case, pair)
+    o = H.run_oracle(oracle, p, *ins)
+    pinned = [None if a is None else torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in ins]
+    torch.cuda.synchronize()
+    junk = torch.empty(64 << 20, dtype=torch.float32, device="cuda")
+    for _ in range(8):
+        junk.normal_()                              # keep the default stream busy so the uploads really are pending
+    dev = [None if t is None else t.cuda(non_blocking=True) for t in pinned]
+    g = gpu_ctx.subtract(p, *dev)                    # no synchronize in between
     torch.cuda.synchronize()
     g.diff, g.noise, g.mask = g.diff.cpu().numpy(), g.noise.cpu().numpy(), g.mask.cpu().numpy()
     compare(o, g)

@@ -192,3 +192,47 @@ def test_import_sets_hardware_queue_default():
     import os
     from zuds_pipeline_b200 import _lib  # noqa: F401
     assert os.environ.get("CUDA_DEVICE_MAX_CONNECTIONS") is not None
+
+
+def test_fits_scaling_cards_do_not_travel(tmp_path):
+    """Round-1 advisor finding: BSCALE/BZERO were applied on read but left in the header, so a saved copy was
+    scaled twice; unsigned 16-bit masks could not be written at all."""
+    from zuds_pipeline_b200 import fitsio
+    raw = (np.arange(12, dtype=np.int16).reshape(3, 4))
+    h = fitsio.Header()
+    h["BSCALE"] = 2.0
+    h["BZERO"] = 100.0
+    # write the raw integers with scaling cards by hand (write_image itself refuses to emit non-neutral cards)
+    path = str(tmp_path / "scaled.fits")
+    fitsio.write_image(path, raw)
+    buf = bytearray(open(path, "rb").read())
+    cards = ("BSCALE  = %20s" % "2.0").ljust(80) + ("BZERO   = %20s" % "100.0").ljust(80)
+    end = buf.index(b"END     ")
+    buf[end:end + 240] = (cards + "END".ljust(80)).encode()
+    open(path, "wb").write(buf)
+    data, hdr = fitsio.read_image(path)
+    assert np.array_equal(data, raw * 2.0 + 100.0)
+    assert "BSCALE" not in hdr and "BZERO" not in hdr
+    fitsio.write_image(str(tmp_path / "copy.fits"), data, hdr)
+    again, _ = fitsio.read_image(str(tmp_path / "copy.fits"))
+    assert np.array_equal(again, data)
+    # unsigned 16-bit: int16 + BZERO 32768 on disk, uint16 back, also through a second save
+    m = np.array([[0, 1, 32768, 65535]], np.uint16)
+    fitsio.write_image(str(tmp_path / "m.fits"), m)
+    back, mh = fitsio.read_image(str(tmp_path / "m.fits"))
+    assert back.dtype == np.uint16 and np.array_equal(back, m) and "BZERO" not in mh
+    fitsio.write_image(str(tmp_path / "m2.fits"), back, mh)
+    assert np.array_equal(fitsio.read_image(str(tmp_path / "m2.fits"))[0], m)
+
+
+def test_background_estimate_follows_float32_numpy():
+    """zuds/utils.py:32-53 on float32 pixels: np.median stays float32 (the two central values of an even count are
+    averaged in float32) and so do the deviations; only the 1.4826 factor is double."""
+    from zuds_pipeline_b200 import params as P
+    rng = np.random.default_rng(5)
+    x = (150 + 3 * rng.normal(size=10000)).astype(np.float32)
+    m = np.zeros(x.shape, np.uint8)
+    bkg, std = P.quick_background_estimate(x, m)
+    b32 = np.median(x)
+    assert b32.dtype == np.float32 and bkg == float(b32)
+    assert std == 1.4826 * float(np.median(np.abs(x - b32)))

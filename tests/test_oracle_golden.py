@@ -48,6 +48,32 @@ def region_keywords(res):
     return out
 
 
+# Keywords that are statistics of the difference / noise pixels.  The CUDA path's pixels agree with the reference
+# within the north star's 1e-4 sigma, not bit for bit (FP32 products in k_convolve), so these are compared as
+# numbers: equal at their printed %.4f precision up to KEY_ATOL + KEY_RTOL |value| (one unit of the last printed
+# digit is 1e-4).  Everything else (region box, direction, KSUM, the stamp-fit figures, pixel counts) stays exact.
+PIXEL_STAT_KEYS = ("FSIG", "FSCAT", "X2NRM", "DMEAN", "DSIGE", "DSIG", "DMEANO", "DSIGEO", "DSIGO")
+KEY_ATOL, KEY_RTOL = 2e-4, 1e-4
+
+
+def keywords_mismatch(mine, theirs, exact=True):
+    """{key: (mine, theirs)} for the keywords that differ (beyond tolerance when exact is False)."""
+    bad = {}
+    for k in set(mine) | set(theirs):
+        a, b = mine.get(k), theirs.get(k)
+        if a == b:
+            continue
+        if not exact and a is not None and b is not None and k.rstrip("0123456789") in PIXEL_STAT_KEYS:
+            try:
+                fa, fb = float(a), float(b)
+            except ValueError:
+                fa = fb = None
+            if fa is not None and (abs(fa - fb) <= KEY_ATOL + KEY_RTOL * abs(fb) or (fa != fa and fb != fb)):
+                continue
+        bad[k] = (a, b)
+    return bad
+
+
 def check_against_golden(case, res, gold, exact=True, pair=None):
     """Compare a Result (oracle or GPU) with the reference's golden record."""
     assert gold["xy_all"] == [list(c) for c in H.oracle_xy(res)[0]]
@@ -81,10 +107,8 @@ def check_against_golden(case, res, gold, exact=True, pair=None):
         # tolerance of the north star: |delta| <= 1e-4 x local sigma
         assert (np.abs(res.diff[cy - 4:cy + 4, cx - 4:cx + 4] - gd) <= 1e-4 * np.maximum(gn, 1e-3)).all()
         assert (np.abs(res.noise[cy - 4:cy + 4, cx - 4:cx + 4] - gn) <= 1e-4 * np.maximum(gn, 1e-3)).all()
-    mine = region_keywords(res)
-    assert mine == gold["region_keys"], {k: (mine.get(k), gold["region_keys"].get(k))
-                                         for k in set(mine) | set(gold["region_keys"])
-                                         if mine.get(k) != gold["region_keys"].get(k)}
+    bad = keywords_mismatch(region_keywords(res), gold["region_keys"], exact=exact)
+    assert not bad, bad
 
 
 @pytest.mark.parametrize("case", CS.SMALL + CS.EXTRA + [CS.TINY_FULL], ids=lambda c: c.name)

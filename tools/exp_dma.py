@@ -17,7 +17,7 @@ from zuds_pipeline_b200.batch import GpuPool  # noqa: E402
 
 
 class NullStream:
-    cuda_stream = 0
+    cuda_stream = -1
 
 
 def main():

@@ -90,6 +90,12 @@ class Result:
     """Outputs of one subtraction (arrays are torch tensors for device calls, numpy for host calls)."""
 
 
+class OwnStream:
+    """``stream=OwnStream()``: run on the context's private non-blocking stream (ZB_STREAM_OWN, include/zb200.h).
+    The default, ``stream=None``, is torch's current stream; its handle 0 is CUDA's legacy default stream."""
+    cuda_stream = -1
+
+
 class Context:
     """One zb_ctx: owns the device workspace of one GPU; use from one thread at a time."""
 

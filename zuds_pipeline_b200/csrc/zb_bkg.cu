@@ -1,10 +1,11 @@
 // zb_bkg.cu — zuds.utils.quick_background_estimate on the GPU (zuds/utils.py:32-53):
 //     bkgpix = data[mask == 0];  bkg = median(bkgpix);  bkgstd = 1.4826 * median(|bkgpix - bkg|)
-// evaluated as the host mirror does (image.py: float32 pixels promoted to float64; np.median averages
-// the two central values of an even count).  Both medians are EXACT order statistics found by radix
-// selection on order-preserving integer keys, 11 bits per pass:
+// evaluated as numpy evaluates it on the float32 pixels zuds holds: the median of float32 values is a float32
+// (the two central values of an even count are added and halved in float32), the deviations |x - bkg| are
+// float32 subtractions, and only the factor 1.4826 promotes to double.  Both medians are EXACT order
+// statistics found by radix selection on order-preserving integer keys, 11 bits per pass:
 //     x      -> 32-bit key of the float    (3 passes: 11 + 11 + 10 bits)
-//     |x-b|  -> 64-bit key of the double   (6 passes), recomputed from x on the fly, never stored
+//     |x-b|  -> 32-bit key of the float    (3 passes), recomputed from x on the fly, never stored
 // A pass streams the pixels once (HBM-bound: 4 B + mask bytes per pixel), builds the digit histogram
 // of the keys that still match the prefix of either wanted rank in shared memory, and the last CTA
 // to finish narrows the two prefixes.  Integer work throughout, so the result is bit-exact.
@@ -32,13 +33,6 @@ __device__ static inline unsigned int key32(float f) {
 __device__ static inline float unkey32(unsigned int k) {
     return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
 }
-__device__ static inline unsigned long long key64(double d) {
-    unsigned long long u = (unsigned long long)__double_as_longlong(d);
-    return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);
-}
-__device__ static inline double unkey64(unsigned long long k) {
-    return __longlong_as_double((long long)((k & 0x8000000000000000ull) ? (k & 0x7fffffffffffffffull) : ~k));
-}
 
 // sky pixels share their leading key bits, so whole warps hit one bin: aggregate before the shared atomic
 __device__ static inline void bk_hist_add(unsigned int *h, unsigned int dg) {
@@ -46,8 +40,7 @@ __device__ static inline void bk_hist_add(unsigned int *h, unsigned int dg) {
     if ((int)(__ffs(peers) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&h[dg], (unsigned int)__popc(peers));
 }
 
-// One radix pass.  mode 0: keys of x (32 bits, held in the high half of a 64-bit key); mode 1: keys of
-// |x - bkg| (64 bits).  `shift` = position of this pass's digit, `bits` its width; keys whose bits above
+// One radix pass.  mode 0: keys of x, mode 1: keys of |x - bkg| (32 bits, held in the high half of a 64-bit key).  `shift` = position of this pass's digit, `bits` its width; keys whose bits above
 // the digit equal prefix[r] are counted for rank r.  first: nothing fixed yet, every key matches, and the
 // unmasked / NaN counts are taken too.
 __global__ void __launch_bounds__(BK_NT)
@@ -74,7 +67,7 @@ k_bkg_pass(const float *__restrict__ data, const void *__restrict__ mask, int md
         cnt++;
         unsigned long long key;
         if (mode == 0) key = (unsigned long long)key32(x) << 32;
-        else key = key64(fabs(__dsub_rn((double)x, bkg)));
+        else key = (unsigned long long)key32(fabsf(__fsub_rn(x, (float)bkg))) << 32;
         const unsigned long long top = hi >= 64 ? 0ull : (key >> hi);
         const unsigned int dg = (unsigned int)(key >> shift) & dmask;
         if (first || top == p0) bk_hist_add(h[0], dg);
@@ -128,7 +121,7 @@ k_bkg_pass(const float *__restrict__ data, const void *__restrict__ mask, int md
             const unsigned long long pre = (first ? 0ull : st->prefix[r]);
             const unsigned long long np = (pre << bits) | (unsigned long long)dg;
             st->prefix[r] = np; st->k[r] = k - c;
-            if (last) st->val[r] = mode == 0 ? (double)unkey32((unsigned int)(np << shift >> 32)) : unkey64(np << shift);
+            if (last) st->val[r] = (double)unkey32((unsigned int)(np << shift >> 32));
         }
     }
     __syncthreads();
@@ -139,7 +132,7 @@ k_bkg_pass(const float *__restrict__ data, const void *__restrict__ mask, int md
         const long long m = st->n;
         double v;
         if (m <= 0 || st->n_nan > 0) v = __longlong_as_double(0x7ff8000000000000ll);     // numpy: median of nothing / of NaNs is NaN
-        else v = __dmul_rn(__dadd_rn(st->val[0], st->val[1]), 0.5);
+        else v = (double)__fmul_rn(__fadd_rn((float)st->val[0], (float)st->val[1]), 0.5f);      // np.mean of two float32
         if (mode == 0) st->bkg = v; else st->mad = v;
     }
 }
@@ -158,14 +151,11 @@ static int bkg_run(zb_ctx *ctx, const float *data, const void *mask, int mdt, lo
     k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mdt, n, S, 0, 53, 11, 1, 0);
     k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mdt, n, S, 0, 42, 11, 0, 0);
     k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mdt, n, S, 0, 32, 10, 0, 1);
-    // median of |x - bkg|: 64-bit keys, 11 x 5 + 9 bits
+    // median of |x - bkg| (float32 deviations): the same three passes
     k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mdt, n, S, 1, 53, 11, 1, 0);
     k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mdt, n, S, 1, 42, 11, 0, 0);
-    k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mdt, n, S, 1, 31, 11, 0, 0);
-    k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mdt, n, S, 1, 20, 11, 0, 0);
-    k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mdt, n, S, 1, 9, 11, 0, 0);
-    k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mdt, n, S, 1, 0, 9, 0, 1);
-    ctx->launches += 9;
+    k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mdt, n, S, 1, 32, 10, 0, 1);
+    ctx->launches += 6;
     zb_copy_small(ctx, &ctx->h_bkg[0], &S->bkg, sizeof(double), st);
     zb_copy_small(ctx, &ctx->h_bkg[1], &S->mad, sizeof(double), st);
     cudaError_t e = zb_stream_wait(ctx, st);
@@ -184,7 +174,7 @@ extern "C" int zb_background_estimate(zb_ctx *ctx, const float *data, const void
     if (!ctx || !data || !bkg || !bkgstd || n < 0) { if (ctx) snprintf(ctx->err, sizeof ctx->err, "null argument"); return ZB_ERR_PARAM; }
     if (mask && !(mask_dtype == ZB_MASK_U8 || mask_dtype == ZB_MASK_I16 || mask_dtype == ZB_MASK_I32)) { snprintf(ctx->err, sizeof ctx->err, "bad mask dtype %d", mask_dtype); return ZB_ERR_PARAM; }
     if (cudaSetDevice(ctx->device) != cudaSuccess) return zb_cuda_fail(ctx, cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
-    return bkg_run(ctx, data, mask, mask_dtype, n, bkg, bkgstd, stream ? (cudaStream_t)stream : ctx->stream);
+    return bkg_run(ctx, data, mask, mask_dtype, n, bkg, bkgstd, zb_pick_stream(ctx, stream));
 }
 
 // host arrays in (what zuds holds: FITS data and mask), staged through the context's buffers

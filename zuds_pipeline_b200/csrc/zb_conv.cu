@@ -8,13 +8,18 @@
 //                    :1399-1415 / :1439-1454 subtract + scale, :1584-1605 output masking
 //   k_region_frame   the hwKernel frame spatial_convolve never touches (main.c:1089,1320-1331; alard.c:1264)
 //
-// Bound: the reference semantics (one dense (2hw+1)^2 kernel per block, double accumulation of
-// float x double products) make this pass FP64-pipe bound, not HBM bound: 2*(2hw+1)^2 DFMA per
-// pixel against 29 bytes of traffic.  Layout: a CTA owns NB horizontally adjacent blocks; the
-// image/variance tile (+halo) is converted to double ONCE while it is staged in shared memory,
-// each thread keeps TX adjacent outputs in registers and slides a register window along the
-// kernel row so that one shared-memory load feeds up to TX DFMAs.
+// Bound: one dense (2hw+1)^2 kernel per block, image AND variance convolved: 2*(2hw+1)^2 multiply-adds
+// per pixel against 29 bytes of traffic, so the pass is arithmetic-bound for hw >= 5.  The arithmetic is
+// packed FP32 (fma.rn.f32x2: image and variance of one tap in one instruction) on the sky-subtracted
+// image, each kernel row's 2hw+1 products summed in FP32 and folded into an FP64 total; the measured
+// decision between this, the FP64 form of round 1 and a tensor-core form is in profiles/r02_conv_arith.md.
+// Structure (persistent, warp-specialised, one CTA per SM):
+//   warp 0        producer: TMA (cp.async.bulk.tensor.2d) of the next tile's float image / rms boxes and
+//                 bulk copies of its blocks' kernels, signalled through mbarriers
+//   warps 1-3     epilogue of tile n-1 (background, noise, masks, subtraction, outputs) while
+//   warps 4-11    convert tile n+... to (image - sky, variance) pairs once, then run the FMA/LDS loop
 #include "zb_internal.h"
+#include <cuda.h>
 #include <stdlib.h>
 #include <type_traits>
 
@@ -25,7 +30,9 @@
 __global__ void __launch_bounds__(256)
 k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, const double *__restrict__ kvec,
                double *__restrict__ kern, double *__restrict__ kernr, int fwp,
-               double *__restrict__ ksum_out, double *__restrict__ kaks, int nbx_max, int nby_max)
+               double *__restrict__ ksum_out, double *__restrict__ kaks, int nbx_max, int nby_max,
+               float2 *__restrict__ kern32, int kstride, double *__restrict__ ksumb, float *__restrict__ csky,
+               const ZbStamp *__restrict__ stamps)
 {
     __shared__ double coef[MK_NB][ZB_MAX_BASIS];
     const int r = blockIdx.y;
@@ -39,6 +46,14 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
     if (b0 > nb) return;
     const double *sol = sols + (long long)r * (D->sz.n_comp_total + 1);
     const int tid = threadIdx.x;
+    const bool kkonly = D->p.convolve_variance != 0;          // -convvar: the variance sees K, not K^2 (alard.c:1300-1306)
+    if (blockIdx.x == 0 && tid == 0) {
+        // sky level the convolution subtracts before its FP32 products and adds back as sky * sum(K): the
+        // histogram mode of the region's first kept stamp (getStampStats3 of the image being convolved).  Any
+        // constant is exact in exact arithmetic; a value near the sky keeps the FP32 products small.
+        const double m = stamps[R.stamp_base].mode;
+        csky[r] = (m * 0.0 == 0.0 && fabs(m) < 1e30) ? (float)m : 0.f;
+    }
     // coefficients of every basis at the block centre, terms in the reference order
     for (int it = tid; it < MK_NB * nK; it += blockDim.x) {
         int lb = it / nK, i1 = it - lb * nK, b = b0 + lb;
@@ -79,22 +94,33 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
             // the same kernel reversed (image coordinates ascending) with rows padded to fwp: what k_convolve
             // copies straight into shared memory
             kernr[((long long)r * per_region + b) * fw * fwp + roff] = acc[lb];
+            // (K, K^2) float pairs, same reversed / row-padded layout: one fma.rn.f32x2 operand per tap
+            const float kf = (float)acc[lb];
+            kern32[((long long)r * per_region + b) * kstride + roff] = make_float2(kf, kkonly ? kf : (float)(acc[lb] * acc[lb]));
         }
     }
     for (int lb = 0; lb < MK_NB; lb++) {                      // zero padding of the reversed rows
         const int b = b0 + lb, npad = fwp - fw;
         if (b > nb || npad <= 0) continue;
-        for (int t = tid; t < fw * npad; t += blockDim.x)
+        for (int t = tid; t < fw * npad; t += blockDim.x) {
             kernr[((long long)r * per_region + b) * fw * fwp + (t / npad) * fwp + fw + t % npad] = 0.0;
+            kern32[((long long)r * per_region + b) * kstride + (t / npad) * fwp + fw + t % npad] = make_float2(0.f, 0.f);
+        }
+    }
+    for (int lb = 0; lb < MK_NB; lb++) {                      // tail of the 16-byte padded block record
+        const int b = b0 + lb;
+        if (b > nb) continue;
+        for (int t = fw * fwp + tid; t < kstride; t += blockDim.x) kern32[((long long)r * per_region + b) * kstride + t] = make_float2(0.f, 0.f);
     }
     __syncthreads();
     // aks = sum |K| in spatial_convolve's tap order (image coordinates ascending = kernel index descending,
     // alard.c:1289-1304): one dependent chain per block, needed only where a bad pixel lies under a footprint
     if (tid < MK_NB && b0 + tid < nb) {
         const double *o = kern + ((long long)r * per_region + b0 + tid) * fw2;
-        double s = 0.0;
-        for (int i = fw2 - 1; i >= 0; i--) s = __dadd_rn(s, fabs(o[i]));
+        double s = 0.0, ks = 0.0;
+        for (int i = fw2 - 1; i >= 0; i--) { s = __dadd_rn(s, fabs(o[i])); ks = __dadd_rn(ks, o[i]); }
         kaks[(long long)r * per_region + b0 + tid] = s;
+        ksumb[(long long)r * per_region + b0 + tid] = ks;     // sum K of the block: the sky term of k_convolve
     }
     if (b0 <= nb && nb < b0 + MK_NB) {                             // this CTA made the centre kernel
         if (tid == MK_NB) {
@@ -129,7 +155,7 @@ __device__ static inline int user_bits(const void *m, int dt, long long g) {
     return v | (ZB_FLAG_INPUT_MASK * (v > 0));
 }
 
-__device__ static inline double background_at(const ZbDev *D, const ZbRegion &R, const double *sol, int xi, int yi) {
+__device__ __noinline__ static double background_at(const ZbDev *D, const ZbRegion &R, const double *sol, int xi, int yi) {
     const int ncompBG = (D->sz.n_comp_ker - 1) * D->sz.n_comp + 1, bgo = D->p.bg_order;
     double xf = (xi - 0.5 * R.rpx) / (0.5 * R.rpx), yf = (yi - 0.5 * R.rpy) / (0.5 * R.rpy);
     double bg = 0.0, ax = 1.0; int k = 1;
@@ -196,334 +222,495 @@ __device__ static inline void finish_pixel(const ZbDev *D, const ZbRegion &R, co
 
 // --------------------------------------------------------------------------- convolution
 //
-// Register-tiled direct convolution.  A CTA owns NBX x NBY convolution blocks (each B x B output
-// pixels with its own kernel, alard.c:1272-1280).  The (image, variance) tile + halo is staged once in
-// shared memory as double2 (float -> double converted at staging); the kernels K of the CTA's blocks
-// are staged reversed, so all loops ascend in image coordinates.  A thread owns TX x TY outputs of one
-// block and walks the tile rows s = 0 .. TY+fw-2: each tile row it loads (TX+CH-1 values per chunk of
-// CH kernel columns) feeds the TY output rows whose footprint contains it, with kernel row
-// dy = s - oy.  Per output the taps are visited dy-outer / dx-inner, the reference's order
-// (alard.c:1289-1306).  Shared-memory traffic per DFMA falls by ~TY against a one-row register tile,
-// which is what moves the pass from shared-memory-bound to FP64-pipe-bound.
-//   per (s, chunk):  TX+CH-1 LDS.128 (window) + TY*CH LDS.64 (kernel, warp-broadcast)
-//                    -> TY*CH*TX*2 DFMA (+ TY*CH DMUL for K^2)
-// alard.c:1304-1308,1327: sum |K| over all taps (aks) and over the taps whose pixel is not INPUT_ISBAD
-// (uks), both in the reference's tap order; true when uks/aks < kerFracMask.  Rare path (a bad
-// pixel under the footprint), kept out of line so the output pass stays small.
-__device__ __noinline__ static bool conv_kernel_fraction_low(const double *Kb, const unsigned char *f0, const unsigned char *h0,
-                                                             int fw, int fwp, int W, float kfm, double aks_blk)
+// Persistent, warp-specialised direct convolution (alard.c:1249-1344).  The unit of work is a tile of
+// NBX x NBY convolution blocks (each B x B output pixels with its own kernel, alard.c:1272-1280); a CTA
+// takes tiles t = blockIdx.x, blockIdx.x + gridDim.x, ... (static schedule, deterministic).  12 warps:
+//
+//   warp 0 (producer)   one thread: TMA tensor loads (cp.async.bulk.tensor.2d) of the tile's float boxes of the
+//                       convolved image and its rms map (+halo) into `raw`, bulk copies (cp.async.bulk) of the
+//                       blocks' (K, K^2) float pairs into `kbuf`, completion on mbarriers.  The boxes of tile
+//                       n+1 land while tile n is being multiplied.
+//   warps 4-11 (FMA)    convert `raw` once into `comp` = (image - sky, variance) float pairs + flag bit rows,
+//                       then the register-tiled FMA/LDS loop: a thread owns TX x TY outputs of one block and
+//                       (K-split KS) a band of kernel rows; it walks the tile rows, each row's window of
+//                       TX+CH-1 pairs feeding the TY output rows whose footprint contains it.  One
+//                       fma.rn.f32x2 per tap and output (image and variance together); every kernel row's
+//                       2hw+1 products are summed in FP32 and folded into an FP64 (image) / FP32 (variance)
+//                       total.  Sums go to `res`.
+//   warps 1-3 (epilogue) everything after the sum for tile n-1 while tile n is multiplied: sky term, background,
+//                       noise, mask propagation incl. the uks/aks test, subtraction, scaling, output masking,
+//                       global stores (main.c:1126-1173, 1399-1454, 1584-1605).
+//
+// Flags: bit rows.  R_any / R_bad hold one bit per tile pixel (any mask bit / INPUT_ISBAD), V_* their OR over
+// the 2hw+1 rows of a footprint; "is there a flagged pixel under this output's footprint" is a shift and a
+// mask, and the bad taps of a footprint row are the set bits of a word.
+//
+// Arithmetic note (profiles/r02_conv_arith.md): the reference accumulates float x double products in
+// double.  Here the image enters as I - sky (exact in FP32 near the sky, error proportional to the flux
+// elsewhere), K and K^2 as floats, and the sky term is added back in FP64 as sky * sum(K).  Worst pixel
+// measured over the parity seeds: see that file; the north-star bound is 1e-4 of the local noise.
+
+typedef unsigned long long u64;
+
+#define CONV_THREADS 384            // warp group 0: producer + 3 epilogue warps; warp groups 1, 2: FMA warps
+#define CONV_FMA_THREADS 256
+#define CONV_EPI_WARPS 3
+#define CONV_MAX_KS 4
+#define CONV_MAX_NB 64
+#define CONV_REGS_LIGHT 96          // setmaxnreg of warp group 0
+#define CONV_REGS_FMA 200           // setmaxnreg of the FMA warp groups: 128*96 + 256*200 = 63488 <= 65536
+
+struct ConvGeom {
+    int NBX, NBY, KS, GX, GY;       // blocks per tile, kernel-row split, thread grid per block
+    int Wt, TH;                     // tile columns / rows actually used (outputs + halo + chunk padding)
+    int WR;                         // raw row pitch in floats = TMA box width (multiple of 4)
+    int Wc;                         // comp row pitch in float2
+    int NW;                         // 32-bit words per flag row (incl. 2 zero words of padding)
+    int fwp, kstride;               // kernel row pitch / block stride in float2
+    int nbx_max, nby_max, blk_row0, blk_row1;
+    int use_tma, have_rms;
+    unsigned o_raw_img, o_raw_rms, o_comp, o_k, o_res, o_rmask, o_vmask, o_misc;   // shared-memory offsets
+    int n_tiles;
+    int first[ZB_MAX_REGIONS + 1];  // tiles of region r: [first[r], first[r+1])
+};
+
+// ---- PTX wrappers -----------------------------------------------------------------------------
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *b, int count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint64_t *b) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *b, unsigned bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory"); }
+__device__ __forceinline__ void mbar_wait(uint64_t *b, unsigned parity) {
+    asm volatile("{\n\t.reg .pred P1;\n\tLAB_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t@P1 bra DONE;\n\tbra LAB_WAIT;\n\tDONE:\n\t}"
+                 ::"r"(smem_u32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *tm, int x, int y, uint64_t *bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(smem_u32(dst)), "l"(tm), "r"(x), "r"(y), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void *dst, const void *src, unsigned bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+__device__ __forceinline__ u64 pack2(float a, float b) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void unpack2(u64 v, float &a, float &b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) { u64 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ u64 fmul2(u64 a, u64 b) { u64 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+
+// n (<= 64) bits of a flag row starting at bit x; rows carry two zero words of padding
+__device__ __forceinline__ u64 bits_at(const unsigned *row, int x, int n) {
+    const int w = x >> 5, sh = x & 31;
+    u64 v = ((u64)row[w] | ((u64)row[w + 1] << 32)) >> sh;
+    if (sh) v |= (u64)row[w + 2] << (64 - sh);
+    return n >= 64 ? v : (v & ((1ull << n) - 1ull));
+}
+
+// alard.c:1304-1308,1327: sum |K| over all taps (aks) and over the taps whose pixel is not INPUT_ISBAD (uks),
+// both in the reference's tap order; true when uks/aks < kerFracMask.  Kb: the block's kernel in double,
+// reversed (image coordinates ascending), rows padded to fwp; rbad: R_bad row of the footprint's first row.
+__device__ __noinline__ static bool conv_kernel_fraction_low(const double *__restrict__ Kb, const unsigned *rbad, int NW, int ox,
+                                                             int fw, int fwp, float kfm, double aks_blk)
 {
-    // Fast decision: uks = aks - (the bad taps), accurate to ~1e-13 relative; the reference's
-    // sequentially rounded sums are only reproduced when the ratio is within 1e-9 of the threshold.
-    // h0[dy * W] bit 1: some INPUT_ISBAD pixel in the fw columns of footprint row dy.
+    // Fast decision: uks = aks - (the bad taps), accurate to ~1e-13 relative; the reference's sequentially
+    // rounded sums are only reproduced when the ratio is within 1e-9 of the threshold.
     double bs = 0.0;
     for (int dy = 0; dy < fw; dy++) {
-        if (!(h0[dy * W] & 2)) continue;
-        const unsigned char *fr = f0 + dy * W;
+        u64 rb = bits_at(rbad + (size_t)dy * NW, ox, fw);
         const double *kr = Kb + dy * fwp;
-        for (int dx = 0; dx < fw; dx++) if (fr[dx] & 2) bs += fabs(kr[dx]);
+        while (rb) { const int dx = __ffsll((long long)rb) - 1; rb &= rb - 1; bs += fabs(__ldg(kr + dx)); }
     }
     const double ratio = (aks_blk - bs) / aks_blk;
     if (fabs(ratio - (double)kfm) > 1e-9) return ratio < (double)kfm;
     double aks = 0.0, uks = 0.0;
-    for (int dy = 0; dy < fw; dy++)
+    for (int dy = 0; dy < fw; dy++) {
+        const u64 rb = bits_at(rbad + (size_t)dy * NW, ox, fw);
         for (int dx = 0; dx < fw; dx++) {
-            const double ak = fabs(Kb[dy * fwp + dx]);
+            const double ak = fabs(__ldg(Kb + dy * fwp + dx));
             aks = __dadd_rn(aks, ak);
-            if (!(f0[dy * W + dx] & 2)) uks = __dadd_rn(uks, ak);
+            if (!((rb >> dx) & 1ull)) uks = __dadd_rn(uks, ak);
         }
+    }
     return (uks / aks) < kfm;
 }
 
-__device__ static inline void cp_async4(void *smem_dst, const void *gsrc) {
-    unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(gsrc) : "memory");
+// tile t -> region, first block of the tile; false when the tile has no output pixel
+struct TileRef { int r, bx0, by0, nbx, nby; };
+__device__ __forceinline__ bool conv_tile(const ZbDev *D, const ConvGeom &G, int t, TileRef &T, ZbRegion &R) {
+    int r = 0;
+    while (t >= G.first[r + 1]) r++;
+    R = D->reg[r];
+    const int B = D->sz.kc_step, hw = D->p.hw_kernel;
+    T.r = r;
+    T.nbx = (R.rpx + B - 1) / B;
+    T.nby = min((R.rpy + B - 1) / B, G.blk_row1);
+    const int ntx = (T.nbx + G.NBX - 1) / G.NBX;
+    const int lt = t - G.first[r], ty = lt / ntx, tx = lt - ty * ntx;
+    T.bx0 = tx * G.NBX; T.by0 = G.blk_row0 + ty * G.NBY;
+    return !(R.skip || T.by0 >= T.nby || T.bx0 >= T.nbx || T.by0 * B + hw >= R.rpy - hw || T.bx0 * B + hw >= R.rpx - hw);
 }
-__device__ static inline void cp_async8(void *smem_dst, const void *gsrc) {
-    unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(gsrc) : "memory");
-}
-__device__ static inline void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
-template <int TX, int TY, int CH, bool EXACT /* fw % CH == 0 */, bool KKONLY /* -convvar */>
-__global__ void __launch_bounds__(256)
-k_convolve(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__ sols, const double *__restrict__ kernr,
-           const double *__restrict__ ksums, const double *__restrict__ kaks,
-           int nbx_max, int nby_max, int NBX, int NBY, int GX, int GY, int W, int TH, int blk_row0, int blk_row1,
+// One chunk of CH kernel columns for the TY output rows of a thread.  FIRST: the row sums start here.
+template <int TX, int TY, int CH, bool EXACT, bool FIRST>
+__device__ __forceinline__ void conv_chunk(const u64 *__restrict__ trow, const u64 *__restrict__ Kb, int ch, int s, int fw, int fwp,
+                                           int dy0, int dy1, bool steady, u64 (&ra)[TY][TX])
+{
+    u64 w[TX + CH - 1];
+#pragma unroll
+    for (int q = 0; q < TX + CH - 1; q++) w[q] = trow[ch + q];
+#pragma unroll
+    for (int oy = 0; oy < TY; oy++) {
+        const int dy = s - oy;
+        if (!steady && (dy < dy0 || dy >= dy1)) continue;       // warp-uniform
+        const u64 *krow = Kb + dy * fwp + ch;
+        if (EXACT || ch + CH <= fw) {
+            u64 k[CH];
+#pragma unroll
+            for (int dx = 0; dx < CH; dx++) k[dx] = krow[dx];
+#pragma unroll
+            for (int dx = 0; dx < CH; dx++)
+#pragma unroll
+                for (int t = 0; t < TX; t++)
+                    ra[oy][t] = (FIRST && dx == 0) ? fmul2(w[t], k[0]) : ffma2(w[t + dx], k[dx], ra[oy][t]);
+        } else {
+#pragma unroll
+            for (int dx = 0; dx < CH; dx++) {
+                if (ch + dx >= fw) break;                        // padded taps are never multiplied (0 x NaN)
+                const u64 k = krow[dx];
+#pragma unroll
+                for (int t = 0; t < TX; t++)
+                    ra[oy][t] = (FIRST && dx == 0) ? fmul2(w[t], k) : ffma2(w[t + dx], k, ra[oy][t]);
+            }
+        }
+    }
+}
+
+template <int TX, int TY, int CH, bool EXACT>
+__global__ void __launch_bounds__(CONV_THREADS, 1)
+k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ CUtensorMap tm_rms,
+           const ZbDev *__restrict__ D, const PixCtx P, const __grid_constant__ ConvGeom G,
+           const double *__restrict__ sols, const float2 *__restrict__ kern32, const double *__restrict__ kernr,
+           const double *__restrict__ ksumb, const double *__restrict__ ksums, const double *__restrict__ kaks,
+           const float *__restrict__ csky,
            float *__restrict__ rdiff, float *__restrict__ rnoise, int32_t *__restrict__ omask,
            float *__restrict__ diff, float *__restrict__ noise, int32_t *__restrict__ out_mask)
 {
-    extern __shared__ __align__(16) unsigned char dyn[];
-    const int r = blockIdx.z;
-    const ZbRegion R = D->reg[r];
-    if (R.skip) return;
-    const int hw = D->p.hw_kernel, fw = D->sz.fw_kernel, fw2 = fw * fw, B = D->sz.kc_step;
-    const int nbx = (R.rpx + B - 1) / B, nby = min((R.rpy + B - 1) / B, blk_row1);   // block rows [blk_row0, blk_row1): row-tile window
-    const int bx0 = blockIdx.x * NBX, by0 = blk_row0 + blockIdx.y * NBY;
-    if (by0 >= nby || bx0 >= nbx) return;
-    const int i00 = bx0 * B + hw, j00 = by0 * B + hw;         // first output pixel of the CTA (region coords)
-    if (j00 >= R.rpy - hw || i00 >= R.rpx - hw) return;
-    const int nch = (fw + CH - 1) / CH, fwp = nch * CH;
-    const int NB = NBX * NBY;
-    double2 *tile = (double2 *)dyn;                           // [TH][W]  (image, variance)
-    double *Kr = (double *)(tile + (size_t)TH * W);           // [NB][fw][fwp]  K reversed
-    unsigned char *flag = (unsigned char *)(Kr + (size_t)NB * fw * fwp);   // [TH][W] bit0: any mask bit, bit1: 0x80
-    unsigned char *hor = flag + (size_t)TH * W;               // [TH][W] OR of flag over the fw columns to the right
-    __shared__ int s_any;
-    const int tid = threadIdx.x, nt = blockDim.x;
-    const int per_region = nbx_max * nby_max + 1;
-    const float fill = D->p.fill_val;
-    if (tid == 0) s_any = 0;
-    __syncthreads();
-    // ---- stage the tile, origin (i00 - hw, j00 - hw) in region coords.  The raw floats travel by
-    // cp.async into the low 8 bytes of their own double2 slot (all copies of the CTA in flight at
-    // once), then each thread widens the slots it copied in place.
-    const bool have_rms = P.conv_rms != nullptr;
-    const int ntile = TH * W;
-    const int lane = tid & 31, warp = tid >> 5, nw = nt >> 5;
-    const int nxi = D->nx;
-    const int xlim = R.rpx - (i00 - hw), ylim = R.rpy - (j00 - hw);      // tile columns / rows inside the region
-    const long long gbase = (long long)(R.by0 + j00 - hw) * nxi + (R.bx0 + i00 - hw);
-    for (int ty = warp; ty < TH; ty += nw) {
-        const long long grow = gbase + (long long)ty * nxi;
-        const bool yin = ty < ylim;
-        for (int tx = lane; tx < W; tx += 32) {
-            const int k = ty * W + tx;
-            unsigned char f = 0;
-            if (yin && tx < xlim) {
-                float *slot = (float *)&tile[k];
-                cp_async4(slot, P.conv + grow + tx);
-                if (have_rms) cp_async4(slot + 1, P.conv_rms + grow + tx);
-                if (P.cmask_src) { const int ub = user_bits(P.cmask_src, P.cdt, grow + tx); f = (ub ? 1 : 0) | ((ub & ZB_FLAG_INPUT_ISBAD) ? 2 : 0); }
-            }
-            flag[k] = f;
-        }
-    }
-    {   // kernels of the CTA's blocks: k_make_kernels left them reversed and row-padded, a flat cp.async copy
-        const int kn = fw * fwp;
-        for (int lb = 0; lb < NB; lb++) {
-            const int lby = lb / NBX, lbx = lb - lby * NBX;
-            const bool ex = bx0 + lbx < nbx && by0 + lby < nby;
-            const double *src = kernr + ((long long)r * per_region + (long long)(by0 + lby) * nbx + (bx0 + lbx)) * kn;
-            double *dst = Kr + (size_t)lb * kn;
-            if (ex) for (int e = tid; e < kn; e += nt) cp_async8(dst + e, src + e);
-            else for (int e = tid; e < kn; e += nt) dst[e] = 0.0;
-        }
-    }
-    cp_async_wait_all();
-    int anyf = 0;
-    const double c_qq = __fmul_rn(P.c_quad, P.c_quad);
-    for (int ty = warp; ty < TH; ty += nw) {
-        const bool yin = ty < ylim;
-        for (int tx = lane; tx < W; tx += 32) {
-            const int k = ty * W + tx;
-            double2 v = make_double2(0.0, 0.0); unsigned char f = flag[k];
-            if (yin && tx < xlim) {
-                const float2 raw = *(const float2 *)&tile[k];
-                const float pv = raw.x;
-                float var;
-                if (have_rms) var = __fmul_rn(raw.y, raw.y);
-                else var = (float)__dadd_rn(__dmul_rn(fabs((double)pv), (double)P.c_invgain), c_qq);
-                v.x = (double)pv; v.y = (double)var;
-                const int cm = value_bits(pv, fill, P.cU, P.cL);
-                f |= (cm ? 1 : 0) | ((cm & ZB_FLAG_INPUT_ISBAD) ? 2 : 0);
-            }
-            tile[k] = v; flag[k] = f; anyf |= f;
-        }
-    }
-    if (anyf) s_any = 1;
-    __syncthreads();
-    const int any = s_any;
-    if (any) {                                                // row-wise OR: the box dilation is separable
-        for (int k = tid; k < ntile; k += nt) {
-            const int ty = k / W, tx = k - ty * W;
-            const int n = min(fw, W - tx);
-            int h = 0;
-            for (int dx = 0; dx < n; dx++) h |= flag[k + dx];
-            hor[k] = (unsigned char)h;
-        }
-    }
+    extern __shared__ __align__(128) unsigned char dyn[];
+    float *raw_img = (float *)(dyn + G.o_raw_img);             // [TH][WR]
+    float *raw_rms = (float *)(dyn + G.o_raw_rms);             // [TH][WR]
+    u64 *comp = (u64 *)(dyn + G.o_comp);                       // [TH][Wc]  (image - sky, variance)
+    u64 *kbuf = (u64 *)(dyn + G.o_k);                          // [NB][kstride]  (K, K^2) reversed, rows padded to fwp
+    float2 *res = (float2 *)(dyn + G.o_res);                   // [KS][OH][OW]  partial (conv, var) sums
+    unsigned *rmask = (unsigned *)(dyn + G.o_rmask);           // [2 parity][2 any/bad][TH][NW]
+    unsigned *vmask = (unsigned *)(dyn + G.o_vmask);           // [2 parity][2 any/bad][OH][NW]
+    uint64_t *bars = (uint64_t *)(dyn + G.o_misc);             // raw_full, raw_empty, k_full, k_empty, res_full, res_empty
+    int *s_any = (int *)(bars + 6);                            // [2 parity]
+    double *s_qsky = (double *)(bars + 8);                     // [2 parity][CONV_MAX_NB] sky * sum(K) of the tile's blocks (epilogue)
+    uint64_t *raw_full = bars, *raw_empty = bars + 1, *k_full = bars + 2, *k_empty = bars + 3, *res_full = bars + 4, *res_empty = bars + 5;
 
-    // thread -> (block of the CTA, column group, row group); row groups fastest
-    const int tpb = GX * GY;
-    const int lb = tid / tpb, lt = tid - lb * tpb;
-    const int gx = lt / GY, gy = lt - gx * GY;
-    const int lby = lb / NBX, lbx = lb - lby * NBX;
-    const bool active = lb < NB && bx0 + lbx < nbx && by0 + lby < nby;
-    const int x0 = lbx * B + gx * TX, y0 = lby * B + gy * TY;   // first output of the thread, relative to (i00, j00)
-    double aq[TY][TX], av[TY][TX];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int hw = D->p.hw_kernel, fw = D->sz.fw_kernel, B = D->sz.kc_step;
+    const int NBX = G.NBX, NBY = G.NBY, NB = NBX * NBY, KS = G.KS;
+    const int OW = NBX * B, OH = NBY * B;
+    const int TH = G.TH, Wt = G.Wt, WR = G.WR, Wc = G.Wc, NW = G.NW, fwp = G.fwp;
+    const int per_region = G.nbx_max * G.nby_max + 1;
+    const int nxi = D->nx, nyi = D->ny;
+    const float fill = D->p.fill_val;
+    constexpr int NFW = CONV_FMA_THREADS / 32;
+
+    if (tid == 0) {
+        mbar_init(raw_full, 1); mbar_init(raw_empty, NFW); mbar_init(k_full, 1); mbar_init(k_empty, NFW);
+        mbar_init(res_full, NFW); mbar_init(res_empty, CONV_EPI_WARPS);
+        s_any[0] = s_any[1] = 0;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // zero the flag rows once: the padding words stay zero for the whole launch
+    for (int k = tid; k < 2 * 2 * (TH + OH) * NW; k += CONV_THREADS) (k < 4 * TH * NW ? rmask[k] : vmask[k - 4 * TH * NW]) = 0u;
+    __syncthreads();
+
+    if (warp < 4) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(CONV_REGS_LIGHT));
+        if (warp == 0) {
+            // ================================================================== producer
+            int it = 0;
+            for (int t = blockIdx.x; t < G.n_tiles; t += gridDim.x) {
+                TileRef T; ZbRegion R;
+                if (!conv_tile(D, G, t, T, R)) continue;
+                const unsigned par = it & 1; it++;
+                const int gx0 = R.bx0 + T.bx0 * B, gy0 = R.by0 + T.by0 * B;     // tile origin, image coordinates
+                if (lane == 0) mbar_wait(raw_empty, par ^ 1);
+                __syncwarp();
+                if (G.use_tma) {
+                    if (lane == 0) {
+                        const unsigned bytes = (unsigned)(WR * TH * 4) * (G.have_rms ? 2u : 1u);
+                        mbar_expect_tx(raw_full, bytes);
+                        tma_load_2d(raw_img, &tm_img, gx0, gy0, raw_full);
+                        if (G.have_rms) tma_load_2d(raw_rms, &tm_rms, gx0, gy0, raw_full);
+                    }
+                } else {
+                    // row pitch or base address not TMA-encodable (nx % 4 != 0): the warp copies the box itself
+                    for (int ty = 0; ty < TH; ty++) {
+                        const int gy = gy0 + ty;
+                        for (int tx = lane; tx < Wt; tx += 32) {
+                            const int gx = gx0 + tx;
+                            const bool in = gx < nxi && gy < nyi;
+                            raw_img[ty * WR + tx] = in ? P.conv[(long long)gy * nxi + gx] : 0.f;
+                            if (G.have_rms) raw_rms[ty * WR + tx] = in ? P.conv_rms[(long long)gy * nxi + gx] : 0.f;
+                        }
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(raw_full);
+                }
+                if (lane == 0) {
+                    mbar_wait(k_empty, par ^ 1);
+                    int nex = 0;
+                    for (int lb = 0; lb < NB; lb++) { const int lby = lb / NBX, lbx = lb - lby * NBX; nex += (T.bx0 + lbx < T.nbx && T.by0 + lby < T.nby); }
+                    mbar_expect_tx(k_full, (unsigned)(nex * G.kstride * 8));
+                    for (int lb = 0; lb < NB; lb++) {
+                        const int lby = lb / NBX, lbx = lb - lby * NBX;
+                        if (!(T.bx0 + lbx < T.nbx && T.by0 + lby < T.nby)) continue;
+                        const float2 *src = kern32 + ((long long)T.r * per_region + (long long)(T.by0 + lby) * T.nbx + (T.bx0 + lbx)) * G.kstride;
+                        bulk_load(kbuf + (size_t)lb * G.kstride, src, (unsigned)(G.kstride * 8), k_full);
+                    }
+                }
+                __syncwarp();
+            }
+        } else {
+            // ================================================================== epilogue (warps 1-3)
+            const int ew = warp - 1, et = tid - 32;
+            int it = 0;
+            for (int t = blockIdx.x; t < G.n_tiles; t += gridDim.x) {
+                TileRef T; ZbRegion R;
+                if (!conv_tile(D, G, t, T, R)) continue;
+                const unsigned par = it & 1; it++;
+                const int r = T.r;
+                const int i00 = T.bx0 * B + hw, j00 = T.by0 * B + hw;              // first output pixel, region coordinates
+                const double *sol = sols + (long long)r * (D->sz.n_comp_total + 1);
+                const double ksum = ksums[(size_t)r * 4], inv1 = 1. / ksum;
+                const double csk = (double)csky[r];
+                const bool conv_t = D->conv_template != 0;
+                const bool do_scale = conv_t ? (D->p.phot_normalize == 't') : (D->p.phot_normalize == 'i');
+                const bool bg_const = D->p.bg_order == 0;
+                const double bg0 = background_at(D, R, sol, 0, 0);                 // the whole background when bgo == 0
+                const bool have_orms = P.other_rms != nullptr;
+                const double o_qq = __fmul_rn(P.o_quad, P.o_quad);
+                const float kfm = D->p.ker_frac_mask, fill_noise = D->p.fill_val_noise;
+                const bool mask_out = D->p.kf_spread_mask2 >= 0;
+                const int ox_lim = min(OW, R.rpx - hw - i00), oy_lim = min(min(OH, (T.nby - T.by0) * B), R.rpy - hw - j00);
+                const int own_x0 = R.rx0 - R.bx0 - i00, own_x1 = R.own_x1 - R.bx0 - i00;   // ownership window, tile coords
+                const int own_y0 = R.ry0 - R.by0 - j00, own_y1 = R.own_y1 - R.by0 - j00;
+                const long long gout = (long long)(R.by0 + j00) * nxi + (R.bx0 + i00);
+                const long long lout = R.off + (long long)j00 * R.rpx + i00;
+                const long long blk0 = (long long)r * per_region + (long long)T.by0 * T.nbx + T.bx0;
+                const float invB = 1.0f / (float)B;
+                // sky term of the tile's blocks (global reads issued before the wait)
+                double my_qsky = 0.0;
+                if (et < NB) {
+                    const int lby = et / NBX, lbx = et - lby * NBX;
+                    if (T.bx0 + lbx < T.nbx && T.by0 + lby < T.nby) my_qsky = csk * ksumb[blk0 + (long long)lby * T.nbx + lbx];
+                }
+                mbar_wait(res_full, par);
+                double *qsky = s_qsky + par * CONV_MAX_NB;
+                if (et < NB) qsky[et] = my_qsky;
+                named_bar_sync(2, CONV_EPI_WARPS * 32);
+                const int any = s_any[par];
+                const unsigned *Rany = rmask + (size_t)(par * 2 + 0) * TH * NW, *Rbad = rmask + (size_t)(par * 2 + 1) * TH * NW;
+                const unsigned *Vany = vmask + (size_t)(par * 2 + 0) * OH * NW, *Vbad = vmask + (size_t)(par * 2 + 1) * OH * NW;
+                constexpr int EPB = 4;                                             // pixels per lane with their global loads in flight together
+                const int nchunk = (ox_lim + 31) >> 5;
+                const int nrow = oy_lim > ew ? (oy_lim - ew + CONV_EPI_WARPS - 1) / CONV_EPI_WARPS : 0;
+                const int nitems = nrow * nchunk;
+                const unsigned magic = (65536u + (unsigned)nchunk - 1u) / (unsigned)nchunk;      // item -> (row, chunk): nitems * nchunk << 2^16
+                for (int it0 = 0; it0 < nitems; it0 += EPB) {
+                    float oth[EPB], orv[EPB]; int ub[EPB], eox[EPB], eoy[EPB];
 #pragma unroll
-    for (int oy = 0; oy < TY; oy++)
+                    for (int e = 0; e < EPB; e++) {
+                        const int itm = it0 + e, j = (int)(((unsigned)itm * magic) >> 16), c = itm - j * nchunk;
+                        eox[e] = lane + 32 * c; eoy[e] = ew + CONV_EPI_WARPS * j;
+                        oth[e] = 0.f; orv[e] = 0.f; ub[e] = 0;
+                        if (itm >= nitems || eox[e] >= ox_lim) { eox[e] = -1; continue; }
+                        const long long g = gout + (long long)eoy[e] * nxi + eox[e];
+                        oth[e] = P.other[g];
+                        if (have_orms) orv[e] = P.other_rms[g];
+                        ub[e] = zb_read_mask(P.omask_src, P.odt, g);               // raw value: nothing may depend on a load here
+                    }
+                    // ONE copy of the per-pixel code, the batch rotated through element 0: unrolled it is several
+                    // thousand instructions that would share the instruction cache with the FMA loop
+#pragma unroll 1
+                    for (int e = 0; e < EPB; e++) {
+                        const int ox = eox[0], oy = eoy[0];
+                        const float ov = oth[0], orv0 = orv[0]; const int ub0 = ub[0];
 #pragma unroll
-        for (int t = 0; t < TX; t++) { aq[oy][t] = 0.0; av[oy][t] = 0.0; }
-    const int ns = TY + fw - 1;
-    if (active) {
-        const double *Kb = Kr + (size_t)lb * fw * fwp;
-        for (int s = 0; s < ns; s++) {
-            const double2 *trow = tile + (size_t)(y0 + s) * W + x0;
-            const bool steady = s >= TY - 1 && s < fw;              // every output row of the thread sees this tile row
-            for (int ch = 0; ch < fwp; ch += CH) {
-                double2 w[TX + CH - 1];
+                        for (int q = 0; q + 1 < EPB; q++) { eox[q] = eox[q + 1]; eoy[q] = eoy[q + 1]; oth[q] = oth[q + 1]; orv[q] = orv[q + 1]; ub[q] = ub[q + 1]; }
+                        if (ox < 0) continue;
+                        const int obx = __float2int_rz(((float)ox + 0.5f) * invB), oby = __float2int_rz(((float)oy + 0.5f) * invB);
+                        const int lb = oby * NBX + obx;
+                        // mask of the convolved image at this pixel and under the footprint
+                        int m = 0;
+                        if (any) {
+                            const bool f_any = bits_at(Vany + (size_t)oy * NW, ox, fw) != 0ull;
+                            if ((Rany[(size_t)(oy + hw) * NW + ((ox + hw) >> 5)] >> ((ox + hw) & 31)) & 1u) {
+                                const long long g = gout + (long long)oy * nxi + ox;
+                                const int cm = user_bits(P.cmask_src, P.cdt, g) | value_bits(P.conv[g], fill, P.cU, P.cL);
+                                m |= cm;
+                                if (cm & ZB_FLAG_INPUT_ISBAD) m |= ZB_FLAG_OUTPUT_ISBAD;
+                            }
+                            if (f_any) {
+                                bool low = false;                                  // no bad tap: uks == aks exactly
+                                if (bits_at(Vbad + (size_t)oy * NW, ox, fw) != 0ull) {
+                                    const long long blk = blk0 + (long long)oby * T.nbx + obx;
+                                    low = conv_kernel_fraction_low(kernr + blk * fw * fwp, Rbad + (size_t)oy * NW, NW, ox, fw, fwp, kfm, kaks[blk]);
+                                }
+                                if (low) m |= (ZB_FLAG_OUTPUT_ISBAD | ZB_FLAG_BAD_CONV);
+                                else m |= ZB_FLAG_OK_CONV;
+                            }
+                        }
+                        double q = qsky[lb]; float var = 0.f;
+                        for (int g2 = 0; g2 < KS; g2++) {
+                            const float2 pr = res[((size_t)g2 * OH + oy) * OW + ox];
+                            q += (double)pr.x; var += pr.y;
+                        }
+                        const float conv_out = (float)q;
+                        const int ob = value_bits(ov, fill, P.oU, P.oL);
+                        if (ob) m |= ob | ZB_FLAG_OUTPUT_ISBAD;
+                        const int ubit = ub0 | (ZB_FLAG_INPUT_MASK * (ub0 > 0));           // user_bits() of the prefetched raw mask value
+                        m |= ubit;
+                        if (ubit & ZB_FLAG_INPUT_ISBAD) m |= ZB_FLAG_OUTPUT_ISBAD;
+                        float ovar;
+                        if (have_orms) ovar = __fmul_rn(orv0, orv0);
+                        else ovar = (float)__dadd_rn(__dmul_rn(fabs((double)ov), (double)P.o_invgain), o_qq);
+                        // (float)sqrt((double)x) == sqrtf(x) correctly rounded: 53 >= 2*24+2 makes the double rounding innocuous
+                        float nz = __fsqrt_rn(__fadd_rn(ovar, var));
+                        const double bg = bg_const ? bg0 : background_at(D, R, sol, i00 + ox, j00 + oy);
+                        float d = __fsub_rn((float)__dadd_rn((double)conv_out, bg), ov);
+                        if (do_scale) { d = (float)__dmul_rn((double)d, inv1); nz = (float)__dmul_rn((double)nz, inv1); }
+                        if (conv_t) d = -d;
+                        const long long l = lout + (long long)oy * R.rpx + ox;
+                        rdiff[l] = d; rnoise[l] = nz; omask[l] = m;
+                        if (ox >= own_x0 && ox <= own_x1 && oy >= own_y0 && oy <= own_y1) {
+                            if (mask_out && (m & ZB_FLAG_OUTPUT_ISBAD)) { d = fill; nz = fill_noise; }
+                            const long long g = gout + (long long)oy * nxi + ox;
+                            diff[g] = d; noise[g] = nz;
+                            if (out_mask) out_mask[g] = m;
+                        }
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(res_empty);
+            }
+        }
+    } else {
+        // ====================================================================== FMA warps (4-11)
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CONV_REGS_FMA));
+        const int ft = tid - 128, fwarp = ft >> 5;
+        const int Tg = CONV_FMA_THREADS / KS;                                      // threads of one kernel-row band
+        const int g = ft / Tg, u = ft - g * Tg;
+        const int tpb = G.GX * G.GY;
+        const int lb = u / tpb, lt = u - lb * tpb;
+        const int gxi = lt / G.GY, gyi = lt - gxi * G.GY;
+        const int lby = lb / NBX, lbx = lb - lby * NBX;
+        const int x0 = lbx * B + gxi * TX, y0 = lby * B + gyi * TY;               // first output of the thread, relative to the tile's first output
+        const int dy0 = (g * fw) / KS, dy1 = ((g + 1) * fw) / KS;                  // this band's kernel rows (ascending image rows)
+        const bool have_rms = G.have_rms != 0;
+        const double c_qq = __fmul_rn(P.c_quad, P.c_quad);
+        int it = 0;
+        for (int t = blockIdx.x; t < G.n_tiles; t += gridDim.x) {
+            TileRef T; ZbRegion R;
+            if (!conv_tile(D, G, t, T, R)) continue;
+            const unsigned par = it & 1; it++;
+            const float c = csky[T.r];
+            const int gx0 = R.bx0 + T.bx0 * B, gy0 = R.by0 + T.by0 * B;
+            unsigned *Rany = rmask + (size_t)(par * 2 + 0) * TH * NW, *Rbad = rmask + (size_t)(par * 2 + 1) * TH * NW;
+            unsigned *Vany = vmask + (size_t)(par * 2 + 0) * OH * NW, *Vbad = vmask + (size_t)(par * 2 + 1) * OH * NW;
+            mbar_wait(raw_full, par);
+            if (ft == 0) s_any[par] = 0;
+            named_bar_sync(1, CONV_FMA_THREADS);                                   // every FMA warp is done with the previous comp tile
+            // ---- convert: raw floats -> (image - sky, variance) pairs, flag bit rows
+            int anyf = 0;
+            for (int ty = fwarp; ty < TH; ty += NFW) {
+                const int gy = gy0 + ty;
+                for (int txb = 0; txb < Wt; txb += 32) {
+                    const int tx = txb + lane;
+                    int f = 0;
+                    if (tx < Wt) {
+                        const float pv = raw_img[ty * WR + tx];
+                        float var;
+                        if (have_rms) { const float rv = raw_rms[ty * WR + tx]; var = __fmul_rn(rv, rv); }
+                        else var = (float)__dadd_rn(__dmul_rn(fabs((double)pv), (double)P.c_invgain), c_qq);
+                        comp[(size_t)ty * Wc + tx] = pack2(__fsub_rn(pv, c), var);
+                        const int gx = gx0 + tx;
+                        if (gx < nxi && gy < nyi) {
+                            int cm = value_bits(pv, fill, P.cU, P.cL);
+                            if (P.cmask_src) cm |= user_bits(P.cmask_src, P.cdt, (long long)gy * nxi + gx);
+                            f = (cm ? 1 : 0) | ((cm & ZB_FLAG_INPUT_ISBAD) ? 2 : 0);
+                        }
+                    }
+                    const unsigned ba = __ballot_sync(0xffffffffu, f & 1), bb = __ballot_sync(0xffffffffu, f & 2);
+                    if (lane == 0) { Rany[(size_t)ty * NW + (txb >> 5)] = ba; Rbad[(size_t)ty * NW + (txb >> 5)] = bb; }
+                    anyf |= (ba != 0u);
+                }
+            }
+            if (lane == 0 && anyf) s_any[par] = 1;
+            __syncwarp();
+            if (lane == 0) mbar_arrive(raw_empty);                                 // the producer may fetch the next tile's boxes
+            named_bar_sync(1, CONV_FMA_THREADS);
+            if (s_any[par]) {                                                      // OR of the flag rows over each footprint's 2hw+1 rows
+                for (int k = ft; k < 2 * OH * NW; k += CONV_FMA_THREADS) {
+                    const int pl = k / (OH * NW), rem = k - pl * OH * NW, oy = rem / NW, w = rem - oy * NW;
+                    const unsigned *src = (pl ? Rbad : Rany) + (size_t)oy * NW + w;
+                    unsigned v = 0u;
+                    for (int dy = 0; dy < fw; dy++) v |= src[(size_t)dy * NW];
+                    (pl ? Vbad : Vany)[(size_t)oy * NW + w] = v;
+                }
+            }
+            // ---- multiply
+            const bool active = lb < NB && T.bx0 + lbx < T.nbx && T.by0 + lby < T.nby;
+            double aq[TY][TX]; float av[TY][TX];
 #pragma unroll
-                for (int q = 0; q < TX + CH - 1; q++) w[q] = trow[ch + q];
+            for (int oy = 0; oy < TY; oy++)
+#pragma unroll
+                for (int tt = 0; tt < TX; tt++) { aq[oy][tt] = 0.0; av[oy][tt] = 0.f; }
+            mbar_wait(k_full, par);
+            if (active) {
+                const u64 *Kb = kbuf + (size_t)lb * G.kstride;
+                const u64 *tbase = comp + (size_t)y0 * Wc + x0;
+                for (int s = dy0; s < dy1 + TY - 1; s++) {
+                    const u64 *trow = tbase + (size_t)s * Wc;
+                    const bool steady = (s - (TY - 1) >= dy0) && (s < dy1);        // every output row of the thread sees this tile row
+                    u64 ra[TY][TX];
+                    conv_chunk<TX, TY, CH, EXACT, true>(trow, Kb, 0, s, fw, fwp, dy0, dy1, steady, ra);
+                    for (int ch = CH; ch < fwp; ch += CH) conv_chunk<TX, TY, CH, EXACT, false>(trow, Kb, ch, s, fw, fwp, dy0, dy1, steady, ra);
+#pragma unroll
+                    for (int oy = 0; oy < TY; oy++) {
+                        const int dy = s - oy;
+                        if (!steady && (dy < dy0 || dy >= dy1)) continue;
+#pragma unroll
+                        for (int tt = 0; tt < TX; tt++) {
+                            float a, b; unpack2(ra[oy][tt], a, b);
+                            aq[oy][tt] += (double)a; av[oy][tt] += b;
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(k_empty);                                   // kernels (and, with the bar.sync above, comp) are free
+            // ---- hand the sums to the epilogue warps
+            mbar_wait(res_empty, par ^ 1);
+            if (active) {
+                float2 *rp = res + (size_t)g * OH * OW;
 #pragma unroll
                 for (int oy = 0; oy < TY; oy++) {
-                    const int dy = s - oy;
-                    if (!steady && (dy < 0 || dy >= fw)) continue;  // warp-uniform
-                    const double *krow = Kb + dy * fwp + ch;
-                    if (EXACT || ch + CH <= fw) {
-                        double k1[CH], k2[CH];
+                    if (gyi * TY + oy >= B) break;
 #pragma unroll
-                        for (int dx = 0; dx < CH; dx++) k1[dx] = krow[dx];
-#pragma unroll
-                        for (int dx = 0; dx < CH; dx++) k2[dx] = KKONLY ? k1[dx] : __dmul_rn(k1[dx], k1[dx]);
-#pragma unroll
-                        for (int dx = 0; dx < CH; dx++)
-#pragma unroll
-                            for (int t = 0; t < TX; t++) {
-                                aq[oy][t] = fma(w[t + dx].x, k1[dx], aq[oy][t]);
-                                av[oy][t] = fma(w[t + dx].y, k2[dx], av[oy][t]);
-                            }
-                    } else {
-#pragma unroll
-                        for (int dx = 0; dx < CH; dx++) {
-                            if (ch + dx >= fw) break;               // padded taps are never multiplied (0 x NaN)
-                            const double k1 = krow[dx];
-                            const double k2 = KKONLY ? k1 : __dmul_rn(k1, k1);
-#pragma unroll
-                            for (int t = 0; t < TX; t++) {
-                                aq[oy][t] = fma(w[t + dx].x, k1, aq[oy][t]);
-                                av[oy][t] = fma(w[t + dx].y, k2, av[oy][t]);
-                            }
-                        }
+                    for (int tt = 0; tt < TX; tt++) {
+                        if (gxi * TX + tt >= B) break;
+                        rp[(size_t)(y0 + oy) * OW + x0 + tt] = make_float2((float)aq[oy][tt], av[oy][tt]);
                     }
                 }
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(res_full);
         }
     }
-    // ---- hand the sums over through shared memory (the tile is dead) so that the output pass
-    // below runs row-major over the CTA's rectangle: coalesced global traffic, loads batched
-    const int OW = NBX * B, OH = NBY * B;
-    float2 *res = (float2 *)dyn;                                  // [OH][OW] (conv, var)
-    __syncthreads();
-    if (active) {
-#pragma unroll
-        for (int oy = 0; oy < TY; oy++) {
-            if (gy * TY + oy >= B) break;
-#pragma unroll
-            for (int t = 0; t < TX; t++) {
-                if (gx * TX + t >= B) break;
-                res[(size_t)(y0 + oy) * OW + x0 + t] = make_float2((float)aq[oy][t], (float)av[oy][t]);
-            }
-        }
-    }
-    __syncthreads();
-    // ---- output pass: background, noise, masks, subtraction, scaling, output masking (main.c:1126-1173,
-    // 1399-1454, 1584-1605).  A warp owns output rows, lanes own columns; EPR rows are in flight per step.
-    const double *sol = sols + (long long)r * (D->sz.n_comp_total + 1);
-    const double ksum = ksums[(size_t)r * 4], inv1 = 1. / ksum;
-    const bool conv_t = D->conv_template != 0;
-    const bool do_scale = conv_t ? (D->p.phot_normalize == 't') : (D->p.phot_normalize == 'i');
-    const bool bg_const = D->p.bg_order == 0;
-    const double bg0 = background_at(D, R, sol, 0, 0);             // the whole background when bgo == 0
-    const bool have_orms = P.other_rms != nullptr;
-    const double o_qq = __fmul_rn(P.o_quad, P.o_quad);
-    const float kfm = D->p.ker_frac_mask, fill_noise = D->p.fill_val_noise;
-    const bool mask_out = D->p.kf_spread_mask2 >= 0;
-    const int ox_lim = min(OW, R.rpx - hw - i00), oy_lim = min(min(OH, (nby - by0) * B), R.rpy - hw - j00);
-    const int own_x0 = R.rx0 - R.bx0 - i00, own_x1 = R.own_x1 - R.bx0 - i00;   // ownership window, CTA coords
-    const int own_y0 = R.ry0 - R.by0 - j00, own_y1 = R.own_y1 - R.by0 - j00;
-    const long long gout = (long long)(R.by0 + j00) * nxi + (R.bx0 + i00);
-    const long long lout = R.off + (long long)j00 * R.rpx + i00;
-    constexpr int EPB = 8;                                      // pixels per lane whose global loads are in flight together
-    const int nchunk = (ox_lim + 31) >> 5;
-    const int nitems = (oy_lim > warp ? (oy_lim - warp + nw - 1) / nw : 0) * nchunk;   // (row of this warp, column chunk)
-    // item -> (row of this warp, column chunk) without a division: nitems * nchunk is far below 2^16
-    const unsigned magic = (65536u + (unsigned)nchunk - 1u) / (unsigned)nchunk;
-    // the global loads of batch n+1 (other image, its rms, its user mask) are in flight while batch n is finished
-#define CONV_OUT_LOAD(IT0, OTH, ORV, UB) do { \
-        _Pragma("unroll") for (int e = 0; e < EPB; e++) { \
-            const int it = (IT0) + e, j = (int)(((unsigned)it * magic) >> 16), c = it - j * nchunk; \
-            const int lx = lane + 32 * c, ly = warp + nw * j; \
-            OTH[e] = 0.f; ORV[e] = 0.f; UB[e] = 0; \
-            if (it < nitems && lx < ox_lim) { \
-                const long long g = gout + (long long)ly * nxi + lx; \
-                OTH[e] = P.other[g]; \
-                if (have_orms) ORV[e] = P.other_rms[g]; \
-                UB[e] = zb_read_mask(P.omask_src, P.odt, g); } } } while (0)   /* raw value: nothing may depend on a load here */
-    float oth[EPB], orv[EPB]; int ub[EPB];
-    CONV_OUT_LOAD(0, oth, orv, ub);
-    for (int it0 = 0; it0 < nitems; it0 += EPB) {
-        {
-            float noth[EPB], norv[EPB]; int nub[EPB];
-            if (it0 + EPB < nitems) CONV_OUT_LOAD(it0 + EPB, noth, norv, nub);
-            int eox[EPB], eoy[EPB];
-#pragma unroll
-            for (int e = 0; e < EPB; e++) {
-                const int it = it0 + e, j = (int)(((unsigned)it * magic) >> 16), c = it - j * nchunk;
-                eox[e] = lane + 32 * c; eoy[e] = warp + nw * j;
-                if (it >= nitems || eox[e] >= ox_lim) eox[e] = -1;
-            }
-#pragma unroll
-            for (int e = 0; e < EPB; e++) {
-                const int ox = eox[e], oy = eoy[e];
-                if (ox < 0) continue;
-                // mask of the convolved image at this pixel and under the footprint
-                int m = 0;
-                if (any) {
-                    const unsigned char *h0 = hor + (size_t)oy * W + ox;
-                    int mbit = 0;
-                    for (int dy = 0; dy < fw; dy++) mbit |= h0[dy * W];
-                    if (flag[(size_t)(oy + hw) * W + ox + hw]) {
-                        const long long g = gout + (long long)oy * nxi + ox;
-                        const int cm = user_bits(P.cmask_src, P.cdt, g) | value_bits(P.conv[g], fill, P.cU, P.cL);
-                        m |= cm;
-                        if (cm & ZB_FLAG_INPUT_ISBAD) m |= ZB_FLAG_OUTPUT_ISBAD;
-                    }
-                    if (mbit) {
-                        bool low = false;                            // no bad tap: uks == aks exactly
-                        if (mbit & 2) {
-                            const int oby = oy / B, obx = ox / B;
-                            const double aks_blk = kaks[(long long)r * per_region + (long long)(by0 + oby) * nbx + (bx0 + obx)];
-                            low = conv_kernel_fraction_low(Kr + (size_t)(oby * NBX + obx) * fw * fwp, flag + (size_t)oy * W + ox, h0, fw, fwp, W, kfm,
-                                                           aks_blk);
-                        }
-                        if (low) m |= (ZB_FLAG_OUTPUT_ISBAD | ZB_FLAG_BAD_CONV);
-                        else m |= ZB_FLAG_OK_CONV;
-                    }
-                }
-                const float2 qv = res[(size_t)oy * OW + ox];
-                const float ov = oth[e];
-                const int ob = value_bits(ov, fill, P.oU, P.oL);
-                if (ob) m |= ob | ZB_FLAG_OUTPUT_ISBAD;
-                const int ubit = ub[e] | (ZB_FLAG_INPUT_MASK * (ub[e] > 0));       // user_bits() of the prefetched raw mask value
-                m |= ubit;
-                if (ubit & ZB_FLAG_INPUT_ISBAD) m |= ZB_FLAG_OUTPUT_ISBAD;
-                float ovar;
-                if (have_orms) ovar = __fmul_rn(orv[e], orv[e]);
-                else ovar = (float)__dadd_rn(__dmul_rn(fabs((double)ov), (double)P.o_invgain), o_qq);
-                // (float)sqrt((double)x) == sqrtf(x) correctly rounded: 53 >= 2*24+2 makes the double rounding innocuous
-                float nz = __fsqrt_rn(__fadd_rn(ovar, qv.y));
-                const double bg = bg_const ? bg0 : background_at(D, R, sol, i00 + ox, j00 + oy);
-                float d = __fsub_rn((float)__dadd_rn((double)qv.x, bg), ov);
-                if (do_scale) { d = (float)__dmul_rn((double)d, inv1); nz = (float)__dmul_rn((double)nz, inv1); }
-                if (conv_t) d = -d;
-                const long long l = lout + (long long)oy * R.rpx + ox;
-                rdiff[l] = d; rnoise[l] = nz; omask[l] = m;
-                if (ox >= own_x0 && ox <= own_x1 && oy >= own_y0 && oy <= own_y1) {
-                    if (mask_out && (m & ZB_FLAG_OUTPUT_ISBAD)) { d = fill; nz = fill_noise; }
-                    const long long g = gout + (long long)oy * nxi + ox;
-                    diff[g] = d; noise[g] = nz;
-                    if (out_mask) out_mask[g] = m;
-                }
-            }
-            if (it0 + EPB < nitems) {
-#pragma unroll
-                for (int e = 0; e < EPB; e++) { oth[e] = noth[e]; orv[e] = norv[e]; ub[e] = nub[e]; }
-            }
-        }
-    }
-#undef CONV_OUT_LOAD
 }
 
 // The hwKernel frame of every region (not touched by spatial_convolve).
@@ -548,6 +735,80 @@ k_region_frame(const ZbDev *__restrict__ D, PixCtx P, const double *__restrict__
     }
 }
 
+// ---- host side: tile geometry, tensor maps, launch -------------------------------------------------
+
+typedef CUresult (*zb_encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                       const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                       CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static zb_encode_tiled_fn zb_encode_tiled() {
+    static zb_encode_tiled_fn fn = nullptr;
+    static int tried = 0;
+    if (!tried) {
+        void *f = nullptr; cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) fn = (zb_encode_tiled_fn)f;
+        tried = 1;
+    }
+    return fn;
+}
+
+// float image nx x ny, box WR x TH, out-of-bounds elements read as zero
+static bool conv_tensor_map(CUtensorMap *tm, const float *img, int nx, int ny, int WR, int TH) {
+    zb_encode_tiled_fn enc = zb_encode_tiled();
+    if (!enc || !img || (nx & 3) || ((uintptr_t)img & 15) || WR > 256 || TH > 256) return false;
+    const cuuint64_t gdim[2] = {(cuuint64_t)nx, (cuuint64_t)ny}, gstr[1] = {(cuuint64_t)nx * 4};
+    const cuuint32_t box[2] = {(cuuint32_t)WR, (cuuint32_t)TH}, estr[2] = {1, 1};
+    return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)img, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+static inline int min_i(int a, int b) { return a < b ? a : b; }
+static inline unsigned up128(size_t v) { return (unsigned)((v + 127) & ~(size_t)127); }
+
+// Shared-memory plan of one tile shape; returns the total bytes.
+static size_t conv_plan(ConvGeom &G, int B, int fw, int TX, int TY, int CH, bool have_rms) {
+    const int nch = (fw + CH - 1) / CH;
+    G.fwp = nch * CH;
+    G.kstride = (fw * G.fwp + 1) & ~1;
+    G.Wt = (G.NBX - 1) * B + G.GX * TX + G.fwp - 1;
+    G.TH = (G.NBY - 1) * B + G.GY * TY + fw - 1;
+    G.WR = (G.Wt + 3) & ~3;
+    G.NW = (G.Wt + 31) / 32 + 2;
+    // comp row pitch: fewest shared-memory conflicts of the window loads (8-byte elements, 16 lanes per
+    // wavefront) for the thread layout of the first two warps of a band
+    {
+        const int tpb = G.GX * G.GY;
+        int best = -1, bestw = G.Wt;
+        for (int wc = G.Wt; wc < G.Wt + 16; wc++) {
+            int worst = 0;
+            for (int h = 0; h < 4; h++) {
+                int cnt[16] = {0};
+                for (int l = 0; l < 16; l++) {
+                    const int u = h * 16 + l, lb = u / tpb, lt = u - lb * tpb;
+                    const int gx = lt / G.GY, gy = lt - gx * G.GY, lby = lb / G.NBX, lbx = lb - lby * G.NBX;
+                    if (lb >= G.NBX * G.NBY) continue;
+                    const long a = (long)(lby * B + gy * TY) * wc + lbx * B + gx * TX;
+                    cnt[a & 15]++;
+                }
+                for (int k = 0; k < 16; k++) worst = cnt[k] > worst ? cnt[k] : worst;
+            }
+            if (best < 0 || worst < best) { best = worst; bestw = wc; }
+        }
+        G.Wc = bestw;
+    }
+    const int NB = G.NBX * G.NBY, OW = G.NBX * B, OH = G.NBY * B;
+    size_t o = 0;
+    G.o_raw_img = up128(o); o = G.o_raw_img + (size_t)G.WR * G.TH * 4;
+    G.o_raw_rms = up128(o); o = G.o_raw_rms + (have_rms ? (size_t)G.WR * G.TH * 4 : 0);
+    G.o_comp = up128(o);    o = G.o_comp + (size_t)G.Wc * G.TH * 8;
+    G.o_k = up128(o);       o = G.o_k + (size_t)NB * G.kstride * 8;
+    G.o_res = up128(o);     o = G.o_res + (size_t)G.KS * OH * OW * 8;
+    G.o_rmask = up128(o);   o = G.o_rmask + (size_t)4 * G.TH * G.NW * 4;
+    G.o_vmask = up128(o);   o = G.o_vmask + (size_t)4 * OH * G.NW * 4;
+    G.o_misc = up128(o);    o = G.o_misc + 64 + (size_t)2 * CONV_MAX_NB * 8;
+    return o;
+}
+
 int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
                        const void *smask, int sdt, const void *tmask, int tdt,
                        float *diff, float *noise, int32_t *out_mask, cudaStream_t st,
@@ -569,61 +830,84 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
     const float tinv = (float)(1. / p.t_gain), tq = p.t_rdnoise / p.t_gain, iinv = (float)(1. / p.i_gain), iq = p.i_rdnoise / p.i_gain;
     P.c_invgain = ct ? tinv : iinv; P.c_quad = ct ? tq : iq;
     P.o_invgain = ct ? iinv : tinv; P.o_quad = ct ? iq : tq;
+    if (fw > 64) { snprintf(ctx->err, sizeof ctx->err, "kernel width %d > 64 is not built", fw); return ZB_ERR_UNSUPPORTED; }
 
     // register tile per kernel-block size: (TX, TY, CH) with GX*TX >= B, GY*TY >= B
     int TXr, TYr, CHr;
     if (B <= 12)      { TXr = 4; TYr = 3; CHr = 4; }
     else if (B <= 24) { TXr = 7; TYr = 3; CHr = 7; }
     else              { TXr = 8; TYr = 3; CHr = 8; }
-    const int GX = (B + TXr - 1) / TXr, GY = (B + TYr - 1) / TYr, tpb = GX * GY;
-    if (tpb > 256) { snprintf(ctx->err, sizeof ctx->err, "kc_step %d too large for the convolution kernel", B); return ZB_ERR_UNSUPPORTED; }
-    const int nch = (fw + CHr - 1) / CHr, fwp = nch * CHr;
-    dim3 gk((nbx_max * nby_max + 1 + MK_NB - 1) / MK_NB + 1, nR);
-    k_make_kernels<<<gk, 256, 0, st>>>(ctx->d_dev, ctx->d_sol, ctx->d_kvec, ctx->d_kern, ctx->d_kernr, fwp, ctx->d_kstat, ctx->d_kaks, nbx_max, nby_max); ZB_DBG("k_make_kernels");
-    // blocks per CTA: ~128 threads and two CTAs per SM when shared memory allows (228 KB per SM, 1 KB
-    // reserved per CTA), else one CTA with as many blocks as fit; among equals the squarer tile (less halo)
-    int NBX = 1, NBY = 1, W = 0, TH = 0, threads = 0; size_t smem = 0;
+    const bool have_rms = P.conv_rms != nullptr;
+    ConvGeom G; memset(&G, 0, sizeof G);
+    G.GX = (B + TXr - 1) / TXr; G.GY = (B + TYr - 1) / TYr;
+    const int tpb = G.GX * G.GY;
+    if (tpb > CONV_FMA_THREADS) { snprintf(ctx->err, sizeof ctx->err, "kc_step %d too large for the convolution kernel", B); return ZB_ERR_UNSUPPORTED; }
+    // Tile shape: NBX x NBY blocks and KS bands of kernel rows.  256 FMA threads, one band per 256/KS of them.
+    // Score = busy lanes x a mild preference for little halo; limited by shared memory and the TMA box (256).
     {
-        static int env_nb = -1, env_ctas = 2;
-        if (env_nb < 0) { const char *e = getenv("ZB_CONV_NB"); env_nb = e ? atoi(e) : 0; e = getenv("ZB_CONV_CTAS"); env_ctas = e ? atoi(e) : 2; if (env_ctas < 1) env_ctas = 2; }
-        const size_t cap2 = (233472 - (size_t)env_ctas * 1024) / env_ctas;
-        auto shape = [&](int bxn, int by, int *w, int *th) -> size_t {
-            int ww = (bxn - 1) * B + GX * TXr + fwp - 1; while ((TYr * ww) % 8 != 1) ww++;   // conflict-free row-group stride
-            *w = ww; *th = (by - 1) * B + GY * TYr + fw - 1;
-            return (size_t)*th * ww * sizeof(double2) + (size_t)bxn * by * fw * fwp * sizeof(double) + 2 * (size_t)*th * ww;
-        };
-        const int target = env_nb > 0 ? env_nb : (128 / tpb > 0 ? 128 / tpb : 1);
-        long best = -1;
-        for (int pass = 0; pass < 2 && best < 0; pass++)
-            for (int nb = target; nb >= 1 && best < 0; nb--)
-                for (int by = 1; by * by <= nb; by++) {
-                    if (nb % by) continue;
-                    int w, th; const size_t sm = shape(nb / by, by, &w, &th);
-                    if (sm > (pass == 0 ? cap2 : (size_t)ZB_SMEM_OPTIN)) continue;
-                    best = nb; NBX = nb / by; NBY = by; W = w; TH = th; smem = sm;          // larger `by` overwrites: squarer
+        static int env_nbx = -1, env_nby = 0, env_ks = 0;
+        if (env_nbx < 0) { const char *e = getenv("ZB_CONV_TILE"); env_nbx = 0; if (e) sscanf(e, "%dx%dx%d", &env_nbx, &env_nby, &env_ks); }
+        double best = -1; ConvGeom Gb = G;
+        for (int ks = 1; ks <= CONV_MAX_KS; ks *= 2)
+            for (int by = 1; by <= 8; by++)
+                for (int bx = 1; bx <= 8; bx++) {
+                    if (env_nbx > 0 && !(bx == env_nbx && by == env_nby && ks == env_ks)) continue;
+                    const int nb = bx * by;
+                    if (nb * tpb > CONV_FMA_THREADS / ks || nb > CONV_MAX_NB || ks > fw) continue;
+                    ConvGeom T = G; T.NBX = bx; T.NBY = by; T.KS = ks;
+                    const size_t sm = conv_plan(T, B, fw, TXr, TYr, CHr, have_rms);
+                    if (sm > (size_t)ZB_SMEM_OPTIN || T.WR > 256 || T.TH > 256) continue;
+                    const double util = (double)(nb * tpb * ks) / CONV_FMA_THREADS;
+                    const double halo = (double)(nb * B * B) / ((double)T.Wt * T.TH);
+                    const int lo = fw / ks, hi = (fw + ks - 1) / ks;               // band imbalance: the tile waits for the widest band
+                    const double score = util * ((double)lo / hi * 0.5 + 0.5) * (0.85 + 0.15 * halo) * (1.0 - 0.02 * (ks - 1));
+                    if (score > best) { best = score; Gb = T; }
                 }
-        if (best < 0) smem = shape(1, 1, &W, &TH);
-        threads = ((NBX * NBY * tpb + 31) / 32) * 32;
+        if (best < 0) { snprintf(ctx->err, sizeof ctx->err, "no convolution tile fits shared memory (kc_step %d, kernel width %d)", B, fw); return ZB_ERR_UNSUPPORTED; }
+        G = Gb;
     }
-    if (smem > ZB_SMEM_OPTIN) { snprintf(ctx->err, sizeof ctx->err, "convolution tile needs %zu bytes of shared memory", smem); return ZB_ERR_UNSUPPORTED; }
+    const size_t smem = conv_plan(G, B, fw, TXr, TYr, CHr, have_rms);
+    G.nbx_max = nbx_max; G.nby_max = nby_max;
     if (blk_row1 > nby_max) blk_row1 = nby_max;
     if (blk_row0 < 0) blk_row0 = 0;
-    dim3 gc((nbx_max + NBX - 1) / NBX, (blk_row1 - blk_row0 + NBY - 1) / NBY, nR);
+    G.blk_row0 = blk_row0; G.blk_row1 = blk_row1;
+    G.have_rms = have_rms ? 1 : 0;
+    int nt = 0;
+    for (int r = 0; r < nR; r++) {
+        const ZbRegion &R = H->reg[r];
+        G.first[r] = nt;
+        if (R.skip) continue;
+        const int nbx = (R.rpx + B - 1) / B, nby = min_i((R.rpy + B - 1) / B, blk_row1);
+        if (nby <= blk_row0) continue;
+        nt += ((nbx + G.NBX - 1) / G.NBX) * ((nby - blk_row0 + G.NBY - 1) / G.NBY);
+    }
+    for (int r = nR; r <= ZB_MAX_REGIONS; r++) G.first[r] = nt;
+    G.n_tiles = nt;
+
+    dim3 gk((nbx_max * nby_max + 1 + MK_NB - 1) / MK_NB + 1, nR);
+    k_make_kernels<<<gk, 256, 0, st>>>(ctx->d_dev, ctx->d_sol, ctx->d_kvec, ctx->d_kern, ctx->d_kernr, G.fwp, ctx->d_kstat, ctx->d_kaks, nbx_max, nby_max,
+                                       ctx->d_kern32, G.kstride, ctx->d_ksumb, ctx->d_csky, ctx->d_stamps); ZB_DBG("k_make_kernels");
+    CUtensorMap tm_img, tm_rms;
+    memset(&tm_img, 0, sizeof tm_img); memset(&tm_rms, 0, sizeof tm_rms);
+    static int env_notma = -1;
+    if (env_notma < 0) { const char *e = getenv("ZB_CONV_NOTMA"); env_notma = (e && e[0] == '1') ? 1 : 0; }
+    G.use_tma = !env_notma && conv_tensor_map(&tm_img, P.conv, p.nx, p.ny, G.WR, G.TH) &&
+                (!have_rms || conv_tensor_map(&tm_rms, P.conv_rms, p.nx, p.ny, G.WR, G.TH));
+    int grid = ctx->n_sm > 0 ? ctx->n_sm : 148;
+    if (grid > nt) grid = nt;
     cudaEventRecord(ctx->ev[10], st);          // k_convolve alone: the kernel bench.py's roofline is quoted on
-#define ZB_CONV_LAUNCH2(TX_, TY_, CH_, EX_, KK_) do { \
-        cudaFuncSetAttribute(k_convolve<TX_, TY_, CH_, EX_, KK_>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN); \
-        k_convolve<TX_, TY_, CH_, EX_, KK_><<<gc, threads, smem, st>>>(ctx->d_dev, P, ctx->d_sol, ctx->d_kernr, ctx->d_kstat, ctx->d_kaks, nbx_max, nby_max, \
-            NBX, NBY, GX, GY, W, TH, blk_row0, blk_row1, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask); } while (0)
-#define ZB_CONV_LAUNCH(TX_, TY_, CH_) do { \
-        const bool ex_ = (fw % CH_) == 0, kk_ = p.convolve_variance != 0; \
-        if (ex_ && !kk_) ZB_CONV_LAUNCH2(TX_, TY_, CH_, true, false); \
-        else if (!ex_ && !kk_) ZB_CONV_LAUNCH2(TX_, TY_, CH_, false, false); \
-        else ZB_CONV_LAUNCH2(TX_, TY_, CH_, false, true); } while (0)
-    if (B <= 12)      ZB_CONV_LAUNCH(4, 3, 4);
-    else if (B <= 24) ZB_CONV_LAUNCH(7, 3, 7);
-    else              ZB_CONV_LAUNCH(8, 3, 8);
+    if (grid > 0) {
+#define ZB_CONV_LAUNCH2(TX_, TY_, CH_, EX_) do { \
+        cudaFuncSetAttribute(k_convolve<TX_, TY_, CH_, EX_>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN); \
+        k_convolve<TX_, TY_, CH_, EX_><<<grid, CONV_THREADS, smem, st>>>(tm_img, tm_rms, ctx->d_dev, P, G, ctx->d_sol, ctx->d_kern32, ctx->d_kernr, \
+            ctx->d_ksumb, ctx->d_kstat, ctx->d_kaks, ctx->d_csky, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask); } while (0)
+#define ZB_CONV_LAUNCH(TX_, TY_, CH_) do { if ((fw % CH_) == 0) ZB_CONV_LAUNCH2(TX_, TY_, CH_, true); else ZB_CONV_LAUNCH2(TX_, TY_, CH_, false); } while (0)
+        if (B <= 12)      ZB_CONV_LAUNCH(4, 3, 4);
+        else if (B <= 24) ZB_CONV_LAUNCH(7, 3, 7);
+        else              ZB_CONV_LAUNCH(8, 3, 8);
 #undef ZB_CONV_LAUNCH2
 #undef ZB_CONV_LAUNCH
+    }
     ZB_DBG("k_convolve");
     cudaEventRecord(ctx->ev[11], st);
     k_region_frame<<<dim3(64, nR), 256, 0, st>>>(ctx->d_dev, P, ctx->d_sol, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask, row0, row1); ZB_DBG("k_region_frame");

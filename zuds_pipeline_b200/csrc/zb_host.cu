@@ -246,6 +246,7 @@ extern "C" int zb_create(int device, zb_ctx **out) {
     ctx->device = device;
     if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return ZB_ERR_CUDA; }
     for (int i = 0; i <= ZB_NSTAGES; i++) cudaEventCreate(&ctx->ev[i]);
+    if (cudaDeviceGetAttribute(&ctx->n_sm, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || ctx->n_sm <= 0) ctx->n_sm = 148;
     if (cudaEventCreateWithFlags(&ctx->ev_sync, cudaEventBlockingSync | cudaEventDisableTiming) != cudaSuccess) ctx->ev_sync = NULL;
     *out = ctx;
     return ZB_OK;
@@ -257,6 +258,7 @@ static void free_workspace(zb_ctx *ctx) {
                       (void **)&ctx->d_cells, (void **)&ctx->d_stamps, (void **)&ctx->d_vec, (void **)&ctx->d_kref, (void **)&ctx->d_gram,
                       (void **)&ctx->d_rhs, (void **)&ctx->d_wxy, (void **)&ctx->d_mat, (void **)&ctx->d_sol, (void **)&ctx->d_vv,
                       (void **)&ctx->d_indx, (void **)&ctx->d_fit, (void **)&ctx->d_jobs, (void **)&ctx->d_njobs, (void **)&ctx->d_kern, (void **)&ctx->d_kernr, (void **)&ctx->d_kaks,
+                      (void **)&ctx->d_kern32, (void **)&ctx->d_ksumb, (void **)&ctx->d_csky,
                       (void **)&ctx->d_kstat, (void **)&ctx->d_stats, (void **)&ctx->d_qa, (void **)&ctx->d_qpart};
     for (size_t i = 0; i < sizeof dptrs / sizeof dptrs[0]; i++) { if (*dptrs[i]) cudaFree(*dptrs[i]); *dptrs[i] = NULL; }
     void **hptrs[] = {(void **)&ctx->h_dev, (void **)&ctx->h_cells, (void **)&ctx->h_stamps, (void **)&ctx->h_fit, (void **)&ctx->h_njobs, (void **)&ctx->h_stats};
@@ -398,6 +400,9 @@ int zb_configure(zb_ctx *ctx, const zb_params *p) {
     DMALLOC(ctx->d_kern, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * fw * fw * sizeof(double));
     DMALLOC(ctx->d_kernr, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * fw * (fw + 8) * sizeof(double));
     DMALLOC(ctx->d_kaks, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * sizeof(double));
+    DMALLOC(ctx->d_kern32, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * (fw * (fw + 8) + 2) * sizeof(float2));
+    DMALLOC(ctx->d_ksumb, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * sizeof(double));
+    DMALLOC(ctx->d_csky, (size_t)sz.n_regions * sizeof(float));
     DMALLOC(ctx->d_kstat, (size_t)sz.n_regions * 4 * sizeof(double));
     const size_t stat_bytes = (size_t)sz.n_regions * ((size_t)sz.n_comp_total + 512) * sizeof(double) + ns * 8;
     DMALLOC(ctx->d_stats, stat_bytes);   HMALLOC(ctx->h_stats, stat_bytes);
@@ -523,7 +528,7 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
     if (ref_mask && !(ref_mask_dtype == ZB_MASK_U8 || ref_mask_dtype == ZB_MASK_I16 || ref_mask_dtype == ZB_MASK_I32)) { snprintf(ctx->err, sizeof ctx->err, "bad ref_mask_dtype %d", ref_mask_dtype); return ZB_ERR_PARAM; }
     if (cudaSetDevice(ctx->device) != cudaSuccess) return zb_cuda_fail(ctx, cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
     CHECK_RC(zb_configure(ctx, p));
-    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    cudaStream_t st = zb_pick_stream(ctx, stream);
     const zb_sizes &sz = ctx->sz;
     ZbDev *H = ctx->h_dev;
     const int nR = sz.n_regions;

@@ -142,6 +142,10 @@ struct zb_ctx {
     double  *d_kern;             // [region][blocks+1][fw*fw]  K per convolution block (+ the region-centre kernel)
     double  *d_kernr;            // the same kernels reversed, rows padded to the convolution's chunk width (what k_convolve stages)
     double  *d_kaks;             // [region][blocks+1]  sum |K| per block in the reference's tap order
+    float2  *d_kern32;           // [region][blocks+1][kstride]  (K, K^2) float pairs, reversed, rows padded: k_convolve's operand
+    double  *d_ksumb;            // [region][blocks+1]  sum K per block (sky term of k_convolve)
+    float   *d_csky;             // [region]  sky level subtracted before the FP32 products
+    int      n_sm;               // multiprocessors of the device (grid of the persistent kernels)
     double  *d_kstat;            // per-region: ksum, aks
     double  *d_stats;  double *h_stats;   // region QA scratch
     ZbQaStat *d_qa;              // [region][4]
@@ -157,6 +161,11 @@ struct zb_ctx {
 };
 
 int zb_cuda_fail(zb_ctx *ctx, cudaError_t e, const char *what, const char *file, int line);
+// the `stream` argument of the C ABI: ZB_STREAM_OWN -> the context's private stream, NULL -> the legacy default stream
+static inline cudaStream_t zb_pick_stream(zb_ctx *ctx, void *stream) {
+    if (stream == ZB_STREAM_OWN) return ctx->stream;
+    return stream ? (cudaStream_t)stream : cudaStreamLegacy;
+}
 // Wait for the stream: cudaStreamSynchronize (spinning; measured faster: 158 vs 143 pairs/s end to end with 24
 // contexts on 16 cores), or with ZB_SYNC=block a blocking-sync event that yields the core.
 cudaError_t zb_stream_wait(zb_ctx *ctx, cudaStream_t st);

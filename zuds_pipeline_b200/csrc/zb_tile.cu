@@ -96,7 +96,7 @@ extern "C" int zb_tile_begin(zb_ctx *ctx, const zb_params *p, int world, int ran
     T.sci = sci; T.ref = ref; T.sci_rms = sci_rms; T.ref_rms = ref_rms;
     T.smask = sci_mask; T.sdt = sci_mask_dtype; T.tmask = ref_mask; T.tdt = ref_mask_dtype;
     T.diff = diff; T.noise = noise; T.out_mask = out_mask;
-    T.st = stream ? (cudaStream_t)stream : ctx->stream;
+    T.st = zb_pick_stream(ctx, stream);
     T.kft = p->ker_fit_thresh; T.retried = 0; T.pending_cell = -1;
     T.cell_lo = T.info.cell_row0 * ctx->sz.nstamp_x; T.cell_hi = T.info.cell_row1 * ctx->sz.nstamp_x;
     T.slot_lo = T.slot_hi = 0; T.n_kept = 0;

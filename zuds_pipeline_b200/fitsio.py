@@ -13,11 +13,14 @@ import numpy as np
 
 BLOCK = 2880
 _DT = {8: ">u1", 16: ">i2", 32: ">i4", -32: ">f4", -64: ">f8"}
-_BITPIX = {"uint8": 8, "int16": 16, "int32": 32, "float32": -32, "float64": -64}
+_BITPIX = {"uint8": 8, "int16": 16, "uint16": 16, "int32": 32, "float32": -32, "float64": -64}
 
 
 class Header:
     """Ordered list of (key, value, comment) cards; dict-style access by key."""
+
+    def remove(self, key):
+        self.cards = [c for c in self.cards if c[0] != key]
 
     def __init__(self, cards=None):
         self.cards = list(cards) if cards else []
@@ -189,6 +192,10 @@ def read_hdus(path):
                         data = data.astype(np.uint16)
                     else:
                         data = data.astype(np.float32)
+                    # the scaling is applied: the cards must not travel with the physical values (a header
+                    # copied onto another product would scale it a second time when read back)
+                    hdr.remove("BSCALE")
+                    hdr.remove("BZERO")
                 else:
                     data = data.astype(data.dtype.newbyteorder("="))
         off += ((nbytes + BLOCK - 1) // BLOCK) * BLOCK
@@ -219,10 +226,24 @@ def write_image(path, data, header=None, extra_hdus=()):
                     ("NAXIS2", data.shape[0], "length of data axis 2")):
         cards += _cards_for(k, v, c)
     skip = {"SIMPLE", "BITPIX", "NAXIS", "NAXIS1", "NAXIS2", "END"}
+    unsigned16 = data.dtype == np.uint16          # FITS has no unsigned 16-bit type: int16 + BZERO 32768
     if header is not None:
         for k, v, c in header.cards:
-            if k not in skip:
-                cards += _cards_for(k, v, c)
+            if k in skip:
+                continue
+            if k in ("BSCALE", "BZERO"):
+                # pixels are written as they are: only the neutral values may stay in the header (hotpants writes
+                # BZERO 0 / BSCALE 1 on its difference image, main.c:268-276)
+                try:
+                    neutral = float(str(v)) == (1.0 if k == "BSCALE" else 0.0)
+                except ValueError:
+                    neutral = False
+                if unsigned16 or not neutral:
+                    continue
+            cards += _cards_for(k, v, c)
+    if unsigned16:
+        cards += _cards_for("BSCALE", 1, "") + _cards_for("BZERO", 32768, "offset data range to that of unsigned short")
+        data = (data.astype(np.int32) - 32768).astype(np.int16)
     with open(path, "wb") as f:
         f.write(_header_bytes(cards))
         raw = data.astype(_DT[bitpix]).tobytes()

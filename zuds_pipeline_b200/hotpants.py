@@ -217,23 +217,25 @@ class HotpantsError(subprocess.CalledProcessError):
 _ctx_cache = {}
 
 # Where the wrapper's own pre-step (quick_background_estimate: two medians and two MADs of 9.5 Mpx per
-# pair, ~0.4 s of numpy in the reference) runs: "gpu" (zb_background_estimate, fails without a device),
-# "host" (the reference's numpy code), or "auto" (GPU when a context can be created).  Both give the
-# same numbers bit for bit, so the hotpants command line does not depend on the choice.
-prestep = os.environ.get("ZB_PRESTEP", "auto")
+# pair, ~0.4 s of numpy in the reference) runs: "gpu" (zb_background_estimate; the default, and it fails
+# loudly without a CUDA device like the rest of the path) or "host" (the reference's numpy code, only when
+# asked for: ZB_PRESTEP=host or hotpants.prestep = "host"; announced on stderr).  Both give the same
+# numbers bit for bit, so the hotpants command line does not depend on the choice.
+prestep = os.environ.get("ZB_PRESTEP", "gpu")
 DEVICE = int(os.environ.get("ZB_DEVICE", os.environ.get("LOCAL_RANK", "0")))
+_host_prestep_announced = False
 
 
 def _prestep_context():
+    global _host_prestep_announced
     if prestep == "host":
+        if not _host_prestep_announced:
+            sys.stderr.write("zuds_pipeline_b200.hotpants: quick_background_estimate on the host (numpy) as requested\n")
+            _host_prestep_announced = True
         return None
-    from . import _lib
-    try:
-        return _context(DEVICE)
-    except (_lib.ZbError, ImportError):
-        if prestep == "gpu":
-            raise
-        return None
+    if prestep != "gpu":
+        raise ValueError("hotpants.prestep must be 'gpu' or 'host', not %r" % (prestep,))
+    return _context(DEVICE)
 
 
 def _context(device):
@@ -272,7 +274,7 @@ def write_outputs(args, sci_header, result, argv0="hotpants"):
         fitsio.write_image(args.files["out_mask"], (m & 0xffff).astype(np.int32), mh)
 
 
-def run_hotpants(command, device=0, ctx=None):
+def run_hotpants(command, device=None, ctx=None):
     """Drop-in for ``subprocess.check_call(command.split())`` with ``command`` from prepare_hotpants.
 
     Returns the ``_lib.Result`` (arrays + per-region QA) after writing the FITS products."""
@@ -299,7 +301,7 @@ def run_hotpants(command, device=0, ctx=None):
                 return None
             m = fitsio.read_image(args.files[key])[0]
             if m.dtype.kind == "f":
-                m = m.astype(np.int32)
+                m = np.rint(m).astype(np.int32)       # cfitsio's fits_read_subset_int rounds to nearest (main.c:781,792)
             return np.ascontiguousarray(m.astype(np.int32) if m.dtype.name not in _lib.MASK_DTYPES else m)
         sci_mask, ref_mask = rd_mask("i_mask"), rd_mask("t_mask")
     except (IOError, OSError, KeyError) as e:
@@ -307,7 +309,7 @@ def run_hotpants(command, device=0, ctx=None):
         raise HotpantsError(104, argv) from e             # cfitsio FILE_NOT_OPENED
     p = args.params
     p.ny, p.nx = sci.shape
-    c = ctx or _context(device)
+    c = ctx or _context(DEVICE if device is None else device)
     try:
         res = c.subtract_host(p, sci, ref, sci_rms, ref_rms, sci_mask, ref_mask, want_mask=True)
     except _lib.ZbError as e:

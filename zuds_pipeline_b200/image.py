@@ -21,8 +21,9 @@ __all__ = ["FITSImage", "MaskImageBase", "CalibratableImageBase", "quick_backgro
 
 
 def quick_background_estimate(image, nsamp=None, mask_image=None, ctx=None):
-    """zuds/utils.py:32-53.  Median and 1.4826 x MAD of the pixels whose mask value is zero, evaluated
-    in float64 (matches the reference under its pinned numpy 1.x).
+    """zuds/utils.py:32-53.  Median and 1.4826 x MAD of the pixels whose mask value is zero, evaluated in the
+    pixels' dtype as the reference's numpy does (float32 medians and deviations; the 1.4826 factor in double,
+    numpy 1.x scalar promotion).
 
     ``ctx`` (a ``_lib.Context``): run it on the GPU (``zb_background_estimate_host``: exact radix
     selection, same two numbers bit for bit); without one this is the reference's own numpy code."""
@@ -30,12 +31,12 @@ def quick_background_estimate(image, nsamp=None, mask_image=None, ctx=None):
         mask_image = image.mask_image
     if ctx is not None and nsamp is None:
         return ctx.background_estimate(np.asarray(image.data), np.asarray(mask_image.data))
-    bkgpix = np.asarray(image.data)[np.asarray(mask_image.data) == 0].astype(np.float64)
+    bkgpix = np.asarray(image.data)[np.asarray(mask_image.data) == 0]
     if nsamp is not None:
         bkgpix = np.random.choice(bkgpix, size=nsamp)
     bkg = np.median(bkgpix)
-    bkgstd = 1.4826 * np.median(np.abs(bkgpix - bkg))
-    return float(bkg), float(bkgstd)
+    mad = np.median(np.abs(bkgpix - bkg))
+    return float(bkg), 1.4826 * float(mad)
 
 
 class FITSImage:

@@ -210,11 +210,13 @@ def hotpants_command(scipath, refpath, outname, scirms, refrms, submask, seeing,
 
 
 def quick_background_estimate(data, mask):
-    """zuds/utils.py:32-53: median and 1.4826*MAD of the unmasked pixels (float64 arithmetic)."""
-    bkgpix = np.asarray(data)[np.asarray(mask) == 0].astype(np.float64)
+    """zuds/utils.py:32-53: median and 1.4826*MAD of the unmasked pixels, in the pixels' own dtype as numpy
+    evaluates it (float32 data: float32 median and deviations; only the 1.4826 factor is double, which is what
+    numpy 1.x's scalar promotion gives the reference)."""
+    bkgpix = np.asarray(data)[np.asarray(mask) == 0]
     bkg = np.median(bkgpix)
-    bkgstd = 1.4826 * np.median(np.abs(bkgpix - bkg))
-    return float(bkg), float(bkgstd)
+    mad = np.median(np.abs(bkgpix - bkg))
+    return float(bkg), 1.4826 * float(mad)
 
 
 def params_for_pair(pair, nreg_side=3, hotpants_kws=None):

@@ -231,7 +231,7 @@ def subtract_tiled(ctx, comm, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=
     me = infos[rank]
     stream = torch.cuda.current_stream(dev)
     if stream.cuda_stream == 0:
-        raise ValueError("subtract_tiled must run under a non-default torch.cuda.stream (the C ABI treats stream 0 as 'use the context stream')")
+        raise ValueError("subtract_tiled must run under a non-default torch.cuda.stream (the one its collectives use)")
     moved = [0, 0]
     profile = bool(stats is not None and stats.get("profile"))
     phases, t_last = {}, [0.0]
