@@ -10,7 +10,7 @@ ARCH="-gencode arch=compute_100a,code=sm_100a"
 COMMON="-O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-ffp-contract=off $ARCH"
 mkdir -p ../../build
 NOFMAD="zb_host zb_stamps zb_fit zb_stats zb_tile zb_bkg"
-FMAD="zb_mask zb_conv"
+FMAD="zb_mask zb_conv zb_prepost"
 pids=()
 for f in $NOFMAD $FMAD; do rm -f ../../build/$f.o; done
 for f in $NOFMAD; do nvcc $COMMON -fmad=false -c $f.cu -o ../../build/$f.o & pids+=($!); done

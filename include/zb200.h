@@ -180,27 +180,68 @@ int zb_subtract_host(zb_ctx *ctx, const zb_params *p,
                      float *diff, float *noise, int32_t *out_mask,
                      zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps);
 
+/* npairs subtractions from HOST buffers, software-pipelined inside the context: the inputs of pair
+ * n+1 are copied to the device and the products of pair n-1 back to the host while pair n is computed; one
+ * cudaMemcpyAsync per array, pinned caller buffers make them asynchronous.  What a batch driver in any language calls
+ * instead of running many contexts side by side for the overlap (zuds: one hotpants process per pair, srun -n 64).
+ *   params   [npairs]                         one parameter set per pair (same frame size; thresholds usually differ)
+ *   pairs    [npairs]                         host pointers of each pair (out_mask NULL: the int mask stays on the device,
+ *                                             as with a zuds command line, which has no -omi)
+ *   regions  [npairs * n_regions], kernel_sol [npairs * n_regions * (n_comp_total+1)] or NULL, stamps [...] or NULL
+ *   rcs      [npairs] per-pair status, or NULL.  Returns the first non-OK status after the whole batch has run. */
+typedef struct zb_host_pair {
+    const float *sci, *ref, *sci_rms, *ref_rms;
+    const void  *sci_mask, *ref_mask;
+    int32_t      sci_mask_dtype, ref_mask_dtype;
+    float       *diff, *noise;
+    int32_t     *out_mask;
+} zb_host_pair;
+int zb_subtract_batch(zb_ctx *ctx, int npairs, const zb_params *params, const zb_host_pair *pairs,
+                      zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps, int *rcs);
+
 /* Timing/diagnostics of the last zb_subtract on this ctx (ms per stage, CUDA events). */
 #define ZB_NSTAGES 12
 int zb_last_timings(const zb_ctx *ctx, float *ms, int n);
 const char *zb_stage_name(int i);
 /* number of kernel launches issued by this ctx since creation */
 long long zb_launch_count(const zb_ctx *ctx);
-/* sizeof() of the public structs as built (0 zb_params, 1 zb_sizes, 2 zb_region_info, 3 zb_stamp_info):
+/* sizeof() of the public structs as built (0 zb_params, 1 zb_sizes, 2 zb_region_info, 3 zb_stamp_info, 4 zb_tile_info, 5 zb_host_pair):
    lets a binding verify its own struct mirror before the first call */
 int zb_abi_sizeof(int which);
 
 /* ------------------------------------------------------------------------------------------
  * Wrapper pre-step on the GPU: zuds.utils.quick_background_estimate, zuds/utils.py:32-53.
  *   bkg = median(data[mask == 0]);  bkgstd = 1.4826 * median(|data[mask == 0] - bkg|)
- * float32 pixels promoted to float64, the two central values of an even count averaged (np.median);
- * NaN when nothing is unmasked or an unmasked pixel is NaN.  Exact order statistics (radix selection),
+ * evaluated as numpy does on float32 pixels: float32 medians (the two central values of an even count are added
+ * and halved in float32), float32 deviations, the factor 1.4826 in double; NaN when nothing is unmasked or an
+ * unmasked pixel is NaN.  Exact order statistics (radix selection),
  * so the -il/-tl thresholds zuds derives from them are identical to the host computation.
  * mask may be NULL (every pixel used); n = number of pixels. */
 int zb_background_estimate(zb_ctx *ctx, const float *data /* device */, const void *mask /* device */, int mask_dtype,
                            long long n, double *bkg, double *bkgstd, void *stream);
 int zb_background_estimate_host(zb_ctx *ctx, const float *data /* host */, const void *mask /* host */, int mask_dtype,
                                 long long n, double *bkg, double *bkgstd);
+
+/* ------------------------------------------------------------------------------------------
+ * The other elementwise steps zuds does around the hotpants call, on DEVICE pointers so that a
+ * caller holding its images in HBM never returns to the host between them, zb_background_estimate and zb_subtract.
+ * All bit-identical to the numpy statements they replace (integer work / correctly rounded float32).
+ *   zb_mask_combine        badpix = refmask | scimask (zuds/subtraction.py:135) into out_or (int32, may be NULL) and
+ *                          its boolean (badpix & bad_sum) > 0 (zuds/mask.py:42-72; bad_sum = 202749 for ZTF) into
+ *                          out_bool (uint8 0/1, what -imi reads; may be NULL).  Either input mask may be NULL (= 0).
+ *   zb_mask_flag_sentinel  mask |= bit_value where diff == sentinel, exact float equality
+ *                          (zuds/subtraction.py:167-177: sentinel 1e-30f, bit_value 2**17)
+ *   zb_rms_from_weight     rms = 1/sqrt(weight); big_rms where bad[i] != 0 or data[i] >= sat_level (zuds/image.py:179-190;
+ *                          sat_level = (float)(0.9 * SATURATE); bad and data may be NULL)
+ *   zb_weight_from_rms     weight = 1/rms^2; 0 where bad[i] != 0 or data[i] >= sat_level (zuds/image.py:146-149)
+ * n = number of pixels; `stream` as in zb_subtract; the calls do not synchronise. */
+int zb_mask_combine(zb_ctx *ctx, const void *sci_mask, int sci_dtype, const void *ref_mask, int ref_dtype, long long n,
+                    int bad_sum, int32_t *out_or, uint8_t *out_bool, void *stream);
+int zb_mask_flag_sentinel(zb_ctx *ctx, int32_t *mask, const float *diff, long long n, float sentinel, int bit_value, void *stream);
+int zb_rms_from_weight(zb_ctx *ctx, const float *weight, const uint8_t *bad, const float *data, float sat_level, float big_rms,
+                       long long n, float *rms, void *stream);
+int zb_weight_from_rms(zb_ctx *ctx, const float *rms, const uint8_t *bad, const float *data, float sat_level,
+                       long long n, float *weight, void *stream);
 
 /* ------------------------------------------------------------------------------------------
  * Row-tile sessions: ONE oversized frame fitted by a single region (nreg_x == nreg_y == 1,

@@ -36,6 +36,7 @@ def test_struct_layouts_match_header():
     assert lib.zb_abi_sizeof(3) == C.sizeof(P.ZbStampInfo)
     from zuds_pipeline_b200 import tiles
     assert lib.zb_abi_sizeof(4) == C.sizeof(tiles.ZbTileInfo)
+    assert lib.zb_abi_sizeof(5) == C.sizeof(P.ZbHostPair)
 
 
 def test_defaults_match_python_and_oracle(oracle):

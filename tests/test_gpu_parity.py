@@ -117,6 +117,25 @@ def test_repeatable_and_context_reuse(gpu_ctx):
     assert np.array_equal(r1.sol, r2.sol)
 
 
+def test_batch_call_equals_single_calls(gpu_ctx):
+    """zb_subtract_batch (copies of neighbouring pairs overlap the computation) gives what zb_subtract_host gives pair by pair."""
+    base = CS.SMALL[0]
+    cases = [CS.Case(base.name, base.shape, base.seeing, base.nreg_side, base.hotpants_kws, base.synth_kws, seed=3000 + k) for k in range(5)]
+    pairs = [CS.make_pair(c) for c in cases]
+    params = [CS.params_of(c, p) for c, p in zip(cases, pairs)]
+    ins = [CS.inputs_of(c, p) for c, p in zip(cases, pairs)]
+    single = [gpu_ctx.subtract_host(p, *i) for p, i in zip(params, ins)]
+    for want_mask in (True, False):
+        got = gpu_ctx.subtract_batch(params, ins, want_mask=want_mask)
+        assert len(got) == 5
+        for a, b in zip(single, got):
+            assert np.array_equal(a.diff, b.diff) and np.array_equal(a.noise, b.noise) and np.array_equal(a.sol, b.sol)
+            assert (b.mask is None) == (not want_mask)
+            if want_mask:
+                assert np.array_equal(a.mask, b.mask)
+            assert H.stamp_table(a) == H.stamp_table(b)
+
+
 def test_bad_params_are_refused(gpu_ctx):
     from zuds_pipeline_b200 import _lib
     case = CS.SMALL[0]

@@ -17,19 +17,20 @@ from . import params as P
 os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libzb200.so")
+LIB_PATH = os.environ.get("ZB_LIB") or os.path.join(_HERE, "libzb200.so")      # ZB_LIB: an experimental build (tools/)
 ZB_NSTAGES = 12
 MASK_DTYPES = {"uint8": 1, "bool": 1, "int16": 2, "int32": 4}
 
 EXPORTS = ("zb_version", "zb_params_default", "zb_params_check", "zb_sizes_of", "zb_create", "zb_destroy",
-           "zb_last_error", "zb_subtract", "zb_subtract_host", "zb_last_timings", "zb_stage_name", "zb_launch_count", "zb_abi_sizeof",
+           "zb_last_error", "zb_subtract", "zb_subtract_host", "zb_subtract_batch", "zb_last_timings", "zb_stage_name", "zb_launch_count", "zb_abi_sizeof",
            # row-tile sessions (bound by tiles.py)
            "zb_tile_plan", "zb_tile_begin", "zb_tile_begin_retry", "zb_tile_cells_export", "zb_tile_cells_import",
            "zb_tile_resolve", "zb_tile_research", "zb_tile_rows", "zb_tile_fill", "zb_tile_normal_export",
            "zb_tile_normal_import", "zb_tile_solve", "zb_tile_sig_export", "zb_tile_sig_import", "zb_tile_clip",
            "zb_tile_convolve", "zb_tile_finish",
-           # wrapper pre-step (zuds.utils.quick_background_estimate)
-           "zb_background_estimate", "zb_background_estimate_host")
+           # wrapper pre/post steps (zuds.utils.quick_background_estimate, mask OR / boolean / bit 17, rms <-> weight)
+           "zb_background_estimate", "zb_background_estimate_host",
+           "zb_mask_combine", "zb_mask_flag_sentinel", "zb_rms_from_weight", "zb_weight_from_rms")
 
 
 class ZbError(RuntimeError):
@@ -62,6 +63,8 @@ def load():
                 C.POINTER(P.ZbRegionInfo), vp, C.POINTER(P.ZbStampInfo)]
     lib.zb_subtract.argtypes = sub_args + [vp]
     lib.zb_subtract_host.argtypes = sub_args
+    lib.zb_subtract_batch.argtypes = [vp, C.c_int, C.POINTER(P.ZbParams), C.POINTER(P.ZbHostPair), C.POINTER(P.ZbRegionInfo), vp,
+                                      C.POINTER(P.ZbStampInfo), C.POINTER(C.c_int)]
     lib.zb_last_timings.argtypes = [vp, C.POINTER(C.c_float), C.c_int]
     lib.zb_stage_name.argtypes = [C.c_int]
     lib.zb_stage_name.restype = C.c_char_p
@@ -70,6 +73,10 @@ def load():
     dp = C.POINTER(C.c_double)
     lib.zb_background_estimate.argtypes = [vp, vp, vp, C.c_int, C.c_longlong, dp, dp, vp]
     lib.zb_background_estimate_host.argtypes = [vp, vp, vp, C.c_int, C.c_longlong, dp, dp]
+    lib.zb_mask_combine.argtypes = [vp, vp, C.c_int, vp, C.c_int, C.c_longlong, C.c_int, vp, vp, vp]
+    lib.zb_mask_flag_sentinel.argtypes = [vp, vp, vp, C.c_longlong, C.c_float, C.c_int, vp]
+    lib.zb_rms_from_weight.argtypes = [vp, vp, vp, vp, C.c_float, C.c_float, C.c_longlong, vp, vp]
+    lib.zb_weight_from_rms.argtypes = [vp, vp, vp, vp, C.c_float, C.c_longlong, vp, vp]
     _lib = lib
     return lib
 
@@ -172,6 +179,77 @@ class Context:
             self._err(rc)
         return bkg.value, std.value
 
+    # -- the other wrapper steps: torch CUDA tensors in and out, nothing returns to the host -------------
+    def _dev(self, t, dtypes=None):
+        import torch
+        assert isinstance(t, torch.Tensor) and t.is_cuda and t.is_contiguous() and t.device.index == self.device, \
+            "contiguous CUDA tensor on device %d expected" % self.device
+        if dtypes is not None:
+            assert t.dtype in dtypes, "dtype %s not in %s" % (t.dtype, dtypes)
+        return C.c_void_p(t.data_ptr())
+
+    @staticmethod
+    def _mask_dt(t):
+        return 0 if t is None else MASK_DTYPES[str(t.dtype).replace("torch.", "")]
+
+    def _stream(self, ref_tensor, stream):
+        import torch
+        if stream is None:
+            stream = torch.cuda.current_stream(ref_tensor.device)
+        return C.c_void_p(stream.cuda_stream)
+
+    def mask_combine(self, sci_mask, ref_mask, bad_sum, want_or=True, want_bool=True, stream=None):
+        """``badpix = ref_mask | sci_mask`` (int32) and its boolean ``(badpix & bad_sum) > 0`` (uint8):
+        zuds/subtraction.py:135 and zuds/mask.py:42-72.  Either mask may be None."""
+        import torch
+        some = sci_mask if sci_mask is not None else ref_mask
+        o = torch.empty(some.shape, dtype=torch.int32, device=some.device) if want_or else None
+        b = torch.empty(some.shape, dtype=torch.uint8, device=some.device) if want_bool else None
+        rc = self.lib.zb_mask_combine(self.h, None if sci_mask is None else self._dev(sci_mask), self._mask_dt(sci_mask),
+                                      None if ref_mask is None else self._dev(ref_mask), self._mask_dt(ref_mask),
+                                      some.numel(), int(bad_sum), None if o is None else self._dev(o),
+                                      None if b is None else self._dev(b), self._stream(some, stream))
+        if rc != 0:
+            self._err(rc)
+        return o, b
+
+    def mask_flag_sentinel(self, mask, diff, sentinel=1e-30, bit_value=2 ** 17, stream=None):
+        """In place: ``mask |= bit_value`` where ``diff == float32(sentinel)`` (zuds/subtraction.py:167-177)."""
+        import torch
+        rc = self.lib.zb_mask_flag_sentinel(self.h, self._dev(mask, (torch.int32,)), self._dev(diff, (torch.float32,)),
+                                            mask.numel(), float(np.float32(sentinel)), int(bit_value), self._stream(mask, stream))
+        if rc != 0:
+            self._err(rc)
+        return mask
+
+    def rms_from_weight(self, weight, bad=None, data=None, saturate=None, big_rms=None, stream=None):
+        """zuds/image.py:179-190: ``1/sqrt(weight)``; ``big_rms`` where ``bad`` or ``data >= 0.9 * saturate``."""
+        import torch
+        from .synth import BIG_RMS
+        out = torch.empty_like(weight)
+        sat = float(np.float32(0.9 * saturate)) if (saturate is not None and data is not None) else float("inf")
+        rc = self.lib.zb_rms_from_weight(self.h, self._dev(weight, (torch.float32,)),
+                                         None if bad is None else self._dev(bad, (torch.uint8, torch.bool)),
+                                         None if (data is None or saturate is None) else self._dev(data, (torch.float32,)), sat,
+                                         float(np.float32(BIG_RMS if big_rms is None else big_rms)), weight.numel(),
+                                         self._dev(out), self._stream(weight, stream))
+        if rc != 0:
+            self._err(rc)
+        return out
+
+    def weight_from_rms(self, rms, bad=None, data=None, saturate=None, stream=None):
+        """zuds/image.py:146-149: ``1/rms**2``; 0 where ``bad`` or ``data >= 0.9 * saturate``."""
+        import torch
+        out = torch.empty_like(rms)
+        sat = float(np.float32(0.9 * saturate)) if (saturate is not None and data is not None) else float("inf")
+        rc = self.lib.zb_weight_from_rms(self.h, self._dev(rms, (torch.float32,)),
+                                         None if bad is None else self._dev(bad, (torch.uint8, torch.bool)),
+                                         None if (data is None or saturate is None) else self._dev(data, (torch.float32,)), sat,
+                                         rms.numel(), self._dev(out), self._stream(rms, stream))
+        if rc != 0:
+            self._err(rc)
+        return out
+
     def subtract_host(self, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=None, ref_mask=None,
                       want_mask=True, out=None):
         """numpy host arrays in, numpy host arrays out (H2D/D2H inside the call)."""
@@ -204,6 +282,59 @@ class Context:
         if rc != 0:
             self._err(rc)
         return r
+
+    def subtract_batch(self, params, inputs, outs=None, want_mask=False):
+        """``zb_subtract_batch``: several pairs of one frame size from host (ideally pinned) numpy arrays, the copies of
+        neighbouring pairs overlapping the computation inside this context.  ``params``: list of zb_params;
+        ``inputs``: list of (sci, ref, sci_rms, ref_rms, sci_mask, ref_mask); ``outs``: list of (diff, noise, mask-or-None)
+        arrays to fill (allocated when None).  Returns a list of Result."""
+        n = len(params)
+        assert n == len(inputs) and n > 0
+        sz = sizes_of(params[0])
+        ny, nx = inputs[0][0].shape
+        pa = (P.ZbParams * n)(*params)
+        hp = (P.ZbHostPair * n)()
+        regions = (P.ZbRegionInfo * (n * sz.n_regions))()
+        sol = np.zeros((n, sz.n_regions, sz.n_comp_total + 1), np.float64)
+        stamps = (P.ZbStampInfo * (n * sz.n_regions * sz.n_stamps))()
+        rcs = (C.c_int * n)()
+        keep, res = [], []
+
+        def ptr(a):
+            return None if a is None else a.ctypes.data
+
+        for i in range(n):
+            f = [None if a is None else np.ascontiguousarray(a, np.float32) for a in inputs[i][:4]]
+            ms = []
+            for m in inputs[i][4:6]:
+                if m is None:
+                    ms.append((None, 0))
+                else:
+                    m = np.ascontiguousarray(m)
+                    m = m.view(np.uint8) if m.dtype == np.bool_ else m
+                    ms.append((m, MASK_DTYPES[m.dtype.name]))
+            if outs is not None:
+                d, nz, mk = outs[i]
+            else:
+                d, nz = np.empty((ny, nx), np.float32), np.empty((ny, nx), np.float32)
+                mk = np.empty((ny, nx), np.int32) if want_mask else None
+            keep.append((f, ms, d, nz, mk))
+            hp[i].sci, hp[i].ref, hp[i].sci_rms, hp[i].ref_rms = ptr(f[0]), ptr(f[1]), ptr(f[2]), ptr(f[3])
+            hp[i].sci_mask, hp[i].sci_mask_dtype = ptr(ms[0][0]), ms[0][1]
+            hp[i].ref_mask, hp[i].ref_mask_dtype = ptr(ms[1][0]), ms[1][1]
+            hp[i].diff, hp[i].noise, hp[i].out_mask = ptr(d), ptr(nz), ptr(mk)
+        rc = self.lib.zb_subtract_batch(self.h, n, pa, hp, regions, sol.ctypes.data_as(C.c_void_p), stamps, rcs)
+        if rc != 0:
+            self._err(rc)
+        for i in range(n):
+            r = Result()
+            r.sizes = sz
+            r.regions = (P.ZbRegionInfo * sz.n_regions).from_buffer(regions, i * sz.n_regions * C.sizeof(P.ZbRegionInfo))
+            r.sol = sol[i]
+            r.stamps = (P.ZbStampInfo * (sz.n_regions * sz.n_stamps)).from_buffer(stamps, i * sz.n_regions * sz.n_stamps * C.sizeof(P.ZbStampInfo))
+            r.diff, r.noise, r.mask = keep[i][2], keep[i][3], keep[i][4]
+            res.append(r)
+        return res
 
     def subtract(self, p, sci, ref, sci_rms=None, ref_rms=None, sci_mask=None, ref_mask=None,
                  want_mask=True, out=None, stream=None):

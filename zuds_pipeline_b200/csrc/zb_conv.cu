@@ -9,10 +9,11 @@
 //   k_region_frame   the hwKernel frame spatial_convolve never touches (main.c:1089,1320-1331; alard.c:1264)
 //
 // Bound: one dense (2hw+1)^2 kernel per block, image AND variance convolved: 2*(2hw+1)^2 multiply-adds
-// per pixel against 29 bytes of traffic, so the pass is arithmetic-bound for hw >= 5.  The arithmetic is
-// packed FP32 (fma.rn.f32x2: image and variance of one tap in one instruction) on the sky-subtracted
-// image, each kernel row's 2hw+1 products summed in FP32 and folded into an FP64 total; the measured
-// decision between this, the FP64 form of round 1 and a tensor-core form is in profiles/r02_conv_arith.md.
+// per pixel against 29 bytes of traffic, so the pass is arithmetic-bound for hw >= 5.  The image term runs on
+// the FP64 pipe exactly as the reference accumulates it (float x double products summed in double), the
+// variance term — positive terms, needed to 1e-4 relative — on the otherwise idle FP32 pipe, so the two
+// halves of the work overlap; the measured decision between this split, the all-FP64 form of round 1, packed
+// FP32 for both terms and a tensor-core form is in profiles/r02_conv_arith.md.
 // Structure (persistent, warp-specialised, one CTA per SM):
 //   warp 0        producer: TMA (cp.async.bulk.tensor.2d) of the next tile's float image / rms boxes and
 //                 bulk copies of its blocks' kernels, signalled through mbarriers
@@ -27,12 +28,12 @@
 // ----------------------------------------------------------------------- kernels table
 
 #define MK_NB 16      // convolution blocks per CTA of k_make_kernels
+struct __align__(16) KTap { double k; float k2; float pad; };   // one kernel tap as k_convolve reads it (one LDS.128)
 __global__ void __launch_bounds__(256)
 k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, const double *__restrict__ kvec,
                double *__restrict__ kern, double *__restrict__ kernr, int fwp,
                double *__restrict__ ksum_out, double *__restrict__ kaks, int nbx_max, int nby_max,
-               float2 *__restrict__ kern32, int kstride, double *__restrict__ ksumb, float *__restrict__ csky,
-               const ZbStamp *__restrict__ stamps)
+               KTap *__restrict__ ktap, int kstride)
 {
     __shared__ double coef[MK_NB][ZB_MAX_BASIS];
     const int r = blockIdx.y;
@@ -46,14 +47,6 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
     if (b0 > nb) return;
     const double *sol = sols + (long long)r * (D->sz.n_comp_total + 1);
     const int tid = threadIdx.x;
-    const bool kkonly = D->p.convolve_variance != 0;          // -convvar: the variance sees K, not K^2 (alard.c:1300-1306)
-    if (blockIdx.x == 0 && tid == 0) {
-        // sky level the convolution subtracts before its FP32 products and adds back as sky * sum(K): the
-        // histogram mode of the region's first kept stamp (getStampStats3 of the image being convolved).  Any
-        // constant is exact in exact arithmetic; a value near the sky keeps the FP32 products small.
-        const double m = stamps[R.stamp_base].mode;
-        csky[r] = (m * 0.0 == 0.0 && fabs(m) < 1e30) ? (float)m : 0.f;
-    }
     // coefficients of every basis at the block centre, terms in the reference order
     for (int it = tid; it < MK_NB * nK; it += blockDim.x) {
         int lb = it / nK, i1 = it - lb * nK, b = b0 + lb;
@@ -94,9 +87,10 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
             // the same kernel reversed (image coordinates ascending) with rows padded to fwp: what k_convolve
             // copies straight into shared memory
             kernr[((long long)r * per_region + b) * fw * fwp + roff] = acc[lb];
-            // (K, K^2) float pairs, same reversed / row-padded layout: one fma.rn.f32x2 operand per tap
-            const float kf = (float)acc[lb];
-            kern32[((long long)r * per_region + b) * kstride + roff] = make_float2(kf, kkonly ? kf : (float)(acc[lb] * acc[lb]));
+            // k_convolve's operand, same reversed / row-padded layout: K for the image term (double) and K^2
+            // for the variance term (float), one 16-byte record per tap
+            KTap kt; kt.k = acc[lb]; kt.k2 = (float)(acc[lb] * acc[lb]); kt.pad = 0.f;
+            ktap[((long long)r * per_region + b) * kstride + roff] = kt;
         }
     }
     for (int lb = 0; lb < MK_NB; lb++) {                      // zero padding of the reversed rows
@@ -104,23 +98,19 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
         if (b > nb || npad <= 0) continue;
         for (int t = tid; t < fw * npad; t += blockDim.x) {
             kernr[((long long)r * per_region + b) * fw * fwp + (t / npad) * fwp + fw + t % npad] = 0.0;
-            kern32[((long long)r * per_region + b) * kstride + (t / npad) * fwp + fw + t % npad] = make_float2(0.f, 0.f);
+            KTap z; z.k = 0.0; z.k2 = 0.f; z.pad = 0.f;
+            ktap[((long long)r * per_region + b) * kstride + (t / npad) * fwp + fw + t % npad] = z;
         }
     }
-    for (int lb = 0; lb < MK_NB; lb++) {                      // tail of the 16-byte padded block record
-        const int b = b0 + lb;
-        if (b > nb) continue;
-        for (int t = fw * fwp + tid; t < kstride; t += blockDim.x) kern32[((long long)r * per_region + b) * kstride + t] = make_float2(0.f, 0.f);
-    }
+
     __syncthreads();
     // aks = sum |K| in spatial_convolve's tap order (image coordinates ascending = kernel index descending,
     // alard.c:1289-1304): one dependent chain per block, needed only where a bad pixel lies under a footprint
     if (tid < MK_NB && b0 + tid < nb) {
         const double *o = kern + ((long long)r * per_region + b0 + tid) * fw2;
-        double s = 0.0, ks = 0.0;
-        for (int i = fw2 - 1; i >= 0; i--) { s = __dadd_rn(s, fabs(o[i])); ks = __dadd_rn(ks, o[i]); }
+        double s = 0.0;
+        for (int i = fw2 - 1; i >= 0; i--) s = __dadd_rn(s, fabs(o[i]));
         kaks[(long long)r * per_region + b0 + tid] = s;
-        ksumb[(long long)r * per_region + b0 + tid] = ks;     // sum K of the block: the sky term of k_convolve
     }
     if (b0 <= nb && nb < b0 + MK_NB) {                             // this CTA made the centre kernel
         if (tid == MK_NB) {
@@ -155,7 +145,7 @@ __device__ static inline int user_bits(const void *m, int dt, long long g) {
     return v | (ZB_FLAG_INPUT_MASK * (v > 0));
 }
 
-__device__ __noinline__ static double background_at(const ZbDev *D, const ZbRegion &R, const double *sol, int xi, int yi) {
+__device__ __forceinline__ static double background_at(const ZbDev *D, const ZbRegion &R, const double *sol, int xi, int yi) {
     const int ncompBG = (D->sz.n_comp_ker - 1) * D->sz.n_comp + 1, bgo = D->p.bg_order;
     double xf = (xi - 0.5 * R.rpx) / (0.5 * R.rpx), yf = (yi - 0.5 * R.rpy) / (0.5 * R.rpy);
     double bg = 0.0, ax = 1.0; int k = 1;
@@ -230,13 +220,13 @@ __device__ static inline void finish_pixel(const ZbDev *D, const ZbRegion &R, co
 //                       convolved image and its rms map (+halo) into `raw`, bulk copies (cp.async.bulk) of the
 //                       blocks' (K, K^2) float pairs into `kbuf`, completion on mbarriers.  The boxes of tile
 //                       n+1 land while tile n is being multiplied.
-//   warps 4-11 (FMA)    convert `raw` once into `comp` = (image - sky, variance) float pairs + flag bit rows,
-//                       then the register-tiled FMA/LDS loop: a thread owns TX x TY outputs of one block and
-//                       (K-split KS) a band of kernel rows; it walks the tile rows, each row's window of
-//                       TX+CH-1 pairs feeding the TY output rows whose footprint contains it.  One
-//                       fma.rn.f32x2 per tap and output (image and variance together); every kernel row's
-//                       2hw+1 products are summed in FP32 and folded into an FP64 (image) / FP32 (variance)
-//                       total.  Sums go to `res`.
+//   warps 4-11 (FMA)    convert `raw` once into `compd` (image widened to double) and `compv` (variance, float)
+//                       + flag bit rows, then the register-tiled FMA/LDS loop: a thread owns TX x TY outputs
+//                       of one block and (K-split KS) a band of kernel rows; it walks the tile rows, each row's
+//                       window of TX+CH-1 values feeding the TY output rows whose footprint contains it.  Per
+//                       tap and output: one DFMA (image x K, the reference's float x double products summed in
+//                       double, alard.c:1289-1299) and one FFMA (variance x K^2, alard.c:1300-1306) — two
+//                       pipes that run side by side.  Sums go to `res` (bands add in band order).
 //   warps 1-3 (epilogue) everything after the sum for tile n-1 while tile n is multiplied: sky term, background,
 //                       noise, mask propagation incl. the uks/aks test, subtraction, scaling, output masking,
 //                       global stores (main.c:1126-1173, 1399-1454, 1584-1605).
@@ -245,31 +235,33 @@ __device__ static inline void finish_pixel(const ZbDev *D, const ZbRegion &R, co
 // the 2hw+1 rows of a footprint; "is there a flagged pixel under this output's footprint" is a shift and a
 // mask, and the bad taps of a footprint row are the set bits of a word.
 //
-// Arithmetic note (profiles/r02_conv_arith.md): the reference accumulates float x double products in
-// double.  Here the image enters as I - sky (exact in FP32 near the sky, error proportional to the flux
-// elsewhere), K and K^2 as floats, and the sky term is added back in FP64 as sky * sum(K).  Worst pixel
-// measured over the parity seeds: see that file; the north-star bound is 1e-4 of the local noise.
+// Arithmetic note (profiles/r02_conv_arith.md): the image term is the reference's arithmetic (the taps of an
+// output are visited in the reference's order; DFMA contracts the product and the add, and the KS bands of
+// kernel rows are added at the end, which moves the last bit of the double sum at most and the float result
+// in practice never).  The variance term is a sum of positive FP32 products: relative error ~1e-6 against the
+// north star's 1e-4.  With -convvar (variance x K, terms of both signs, alard.c:1300-1306) it runs in FP64 too.
 
 typedef unsigned long long u64;
 
+#define ZB_SMEM_CONV (227 * 1024)   // dynamic shared memory opt-in of k_convolve (the same constant for every launch, see ZB_SMEM_OPTIN)
 #define CONV_THREADS 384            // warp group 0: producer + 3 epilogue warps; warp groups 1, 2: FMA warps
 #define CONV_FMA_THREADS 256
 #define CONV_EPI_WARPS 3
 #define CONV_MAX_KS 4
 #define CONV_MAX_NB 64
-#define CONV_REGS_LIGHT 96          // setmaxnreg of warp group 0
-#define CONV_REGS_FMA 200           // setmaxnreg of the FMA warp groups: 128*96 + 256*200 = 63488 <= 65536
+#define CONV_REGS_LIGHT 128          // setmaxnreg of warp group 0
+#define CONV_REGS_FMA 184           // setmaxnreg of the FMA warp groups: 128*LIGHT + 256*FMA <= 65536
 
 struct ConvGeom {
     int NBX, NBY, KS, GX, GY;       // blocks per tile, kernel-row split, thread grid per block
     int Wt, TH;                     // tile columns / rows actually used (outputs + halo + chunk padding)
     int WR;                         // raw row pitch in floats = TMA box width (multiple of 4)
-    int Wc;                         // comp row pitch in float2
+    int Wc, Wv;                     // row pitch of the double image plane / the float variance plane
     int NW;                         // 32-bit words per flag row (incl. 2 zero words of padding)
-    int fwp, kstride;               // kernel row pitch / block stride in float2
+    int fwp, kstride;               // kernel row pitch / block stride in taps (KTap records)
     int nbx_max, nby_max, blk_row0, blk_row1;
     int use_tma, have_rms;
-    unsigned o_raw_img, o_raw_rms, o_comp, o_k, o_res, o_rmask, o_vmask, o_misc;   // shared-memory offsets
+    unsigned o_raw_img, o_raw_rms, o_compd, o_compv, o_k, o_resq, o_resv, o_rmask, o_vmask, o_pre, o_resm, o_misc;   // shared-memory offsets
     int n_tiles;
     int first[ZB_MAX_REGIONS + 1];  // tiles of region r: [first[r], first[r+1])
 };
@@ -292,10 +284,6 @@ __device__ __forceinline__ void bulk_load(void *dst, const void *src, unsigned b
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
-__device__ __forceinline__ u64 pack2(float a, float b) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
-__device__ __forceinline__ void unpack2(u64 v, float &a, float &b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
-__device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) { u64 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
-__device__ __forceinline__ u64 fmul2(u64 a, u64 b) { u64 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
 
 // n (<= 64) bits of a flag row starting at bit x; rows carry two zero words of padding
 __device__ __forceinline__ u64 bits_at(const unsigned *row, int x, int n) {
@@ -305,19 +293,28 @@ __device__ __forceinline__ u64 bits_at(const unsigned *row, int x, int n) {
     return n >= 64 ? v : (v & ((1ull << n) - 1ull));
 }
 
-// alard.c:1304-1308,1327: sum |K| over all taps (aks) and over the taps whose pixel is not INPUT_ISBAD (uks),
-// both in the reference's tap order; true when uks/aks < kerFracMask.  Kb: the block's kernel in double,
-// reversed (image coordinates ascending), rows padded to fwp; rbad: R_bad row of the footprint's first row.
-__device__ __noinline__ static bool conv_kernel_fraction_low(const double *__restrict__ Kb, const unsigned *rbad, int NW, int ox,
-                                                             int fw, int fwp, float kfm, double aks_blk)
+// alard.c:1304-1308,1327: sum |K| over all taps (aks) and over the taps whose pixel is not INPUT_ISBAD (uks), both in
+// the reference's tap order; true when uks/aks < kerFracMask.  Fast decision: uks = aks - (the bad taps), the bad taps
+// of a footprint row summed run by run from the row's prefix sums of |K| (a dead column or the frame border is one
+// run per row), accurate to ~1e-13 relative; the reference's sequentially rounded sums are only reproduced when the
+// ratio is within 1e-9 of the threshold.
+//   pre   [fw][fwp+1] prefix sums of |K| along each (reversed) kernel row of the output's block
+//   Kb    the block's taps (reversed, rows padded to fwp)
+//   rbad  R_bad row of the footprint's first row; rows: bit dy set when tile row (first row + dy) holds any bad pixel
+__device__ __forceinline__ static bool conv_kernel_fraction_low(const double *__restrict__ pre, const KTap *__restrict__ Kb, const unsigned *rbad,
+                                                                 int NW, int ox, u64 rows, int fw, int fwp, float kfm, double aks_blk)
 {
-    // Fast decision: uks = aks - (the bad taps), accurate to ~1e-13 relative; the reference's sequentially
-    // rounded sums are only reproduced when the ratio is within 1e-9 of the threshold.
     double bs = 0.0;
-    for (int dy = 0; dy < fw; dy++) {
+    while (rows) {
+        const int dy = __ffsll((long long)rows) - 1; rows &= rows - 1;
         u64 rb = bits_at(rbad + (size_t)dy * NW, ox, fw);
-        const double *kr = Kb + dy * fwp;
-        while (rb) { const int dx = __ffsll((long long)rb) - 1; rb &= rb - 1; bs += fabs(__ldg(kr + dx)); }
+        const double *pr = pre + dy * (fwp + 1);
+        while (rb) {
+            const int lo = __ffsll((long long)rb) - 1;
+            const int len = __ffsll((long long)~(rb >> lo)) - 1;     // run of bad taps lo .. lo+len-1 (fw < 64: a zero bit always follows)
+            bs += pr[lo + len] - pr[lo];
+            rb &= ~(((1ull << len) - 1ull) << lo);
+        }
     }
     const double ratio = (aks_blk - bs) / aks_blk;
     if (fabs(ratio - (double)kfm) > 1e-9) return ratio < (double)kfm;
@@ -325,7 +322,7 @@ __device__ __noinline__ static bool conv_kernel_fraction_low(const double *__res
     for (int dy = 0; dy < fw; dy++) {
         const u64 rb = bits_at(rbad + (size_t)dy * NW, ox, fw);
         for (int dx = 0; dx < fw; dx++) {
-            const double ak = fabs(__ldg(Kb + dy * fwp + dx));
+            const double ak = fabs(Kb[dy * fwp + dx].k);
             aks = __dadd_rn(aks, ak);
             if (!((rb >> dx) & 1ull)) uks = __dadd_rn(uks, ak);
         }
@@ -349,69 +346,83 @@ __device__ __forceinline__ bool conv_tile(const ZbDev *D, const ConvGeom &G, int
     return !(R.skip || T.by0 >= T.nby || T.bx0 >= T.nbx || T.by0 * B + hw >= R.rpy - hw || T.bx0 * B + hw >= R.rpx - hw);
 }
 
-// One chunk of CH kernel columns for the TY output rows of a thread.  FIRST: the row sums start here.
-template <int TX, int TY, int CH, bool EXACT, bool FIRST>
-__device__ __forceinline__ void conv_chunk(const u64 *__restrict__ trow, const u64 *__restrict__ Kb, int ch, int s, int fw, int fwp,
-                                           int dy0, int dy1, bool steady, u64 (&ra)[TY][TX])
+// One chunk of CH kernel columns for the TY output rows of a thread.  VAR64 (-convvar): the variance is convolved
+// with K itself, in double.
+template <int TX, int TY, int CH, bool EXACT, bool VAR64, typename AV>
+__device__ __forceinline__ void conv_chunk(const double *__restrict__ trd, const float *__restrict__ trv, const KTap *__restrict__ Kb,
+                                           int ch, int s, int fw, int fwp, int dy0, int dy1, bool steady,
+                                           double (&aq)[TY][TX], AV (&av)[TY][TX])
 {
-    u64 w[TX + CH - 1];
+    double wd[TX + CH - 1]; AV wv[TX + CH - 1];
 #pragma unroll
-    for (int q = 0; q < TX + CH - 1; q++) w[q] = trow[ch + q];
+    for (int q = 0; q < TX + CH - 1; q++) { wd[q] = trd[ch + q]; wv[q] = (AV)trv[ch + q]; }
 #pragma unroll
     for (int oy = 0; oy < TY; oy++) {
         const int dy = s - oy;
         if (!steady && (dy < dy0 || dy >= dy1)) continue;       // warp-uniform
-        const u64 *krow = Kb + dy * fwp + ch;
+        const KTap *krow = Kb + dy * fwp + ch;
         if (EXACT || ch + CH <= fw) {
-            u64 k[CH];
+            double2 kk[CH];                                      // one LDS.128 per tap: (K, [K^2 float | pad])
 #pragma unroll
-            for (int dx = 0; dx < CH; dx++) k[dx] = krow[dx];
+            for (int dx = 0; dx < CH; dx++) kk[dx] = reinterpret_cast<const double2 *>(krow)[dx];
 #pragma unroll
-            for (int dx = 0; dx < CH; dx++)
+            for (int dx = 0; dx < CH; dx++) {
+                const double k = kk[dx].x;
+                const float k2 = __int_as_float(__double2loint(kk[dx].y));
 #pragma unroll
-                for (int t = 0; t < TX; t++)
-                    ra[oy][t] = (FIRST && dx == 0) ? fmul2(w[t], k[0]) : ffma2(w[t + dx], k[dx], ra[oy][t]);
+                for (int t = 0; t < TX; t++) {
+                    aq[oy][t] = fma(wd[t + dx], k, aq[oy][t]);
+                    if (VAR64) av[oy][t] = (AV)fma((double)wv[t + dx], k, (double)av[oy][t]);
+                    else av[oy][t] = (AV)fmaf((float)wv[t + dx], k2, (float)av[oy][t]);
+                }
+            }
         } else {
 #pragma unroll
             for (int dx = 0; dx < CH; dx++) {
                 if (ch + dx >= fw) break;                        // padded taps are never multiplied (0 x NaN)
-                const u64 k = krow[dx];
+                const KTap k = krow[dx];
 #pragma unroll
-                for (int t = 0; t < TX; t++)
-                    ra[oy][t] = (FIRST && dx == 0) ? fmul2(w[t], k) : ffma2(w[t + dx], k, ra[oy][t]);
+                for (int t = 0; t < TX; t++) {
+                    aq[oy][t] = fma(wd[t + dx], k.k, aq[oy][t]);
+                    if (VAR64) av[oy][t] = (AV)fma((double)wv[t + dx], k.k, (double)av[oy][t]);
+                    else av[oy][t] = (AV)fmaf((float)wv[t + dx], k.k2, (float)av[oy][t]);
+                }
             }
         }
     }
 }
 
-template <int TX, int TY, int CH, bool EXACT>
+template <int TX, int TY, int CH, bool EXACT, bool VAR64>
 __global__ void __launch_bounds__(CONV_THREADS, 1)
 k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ CUtensorMap tm_rms,
            const ZbDev *__restrict__ D, const PixCtx P, const __grid_constant__ ConvGeom G,
-           const double *__restrict__ sols, const float2 *__restrict__ kern32, const double *__restrict__ kernr,
-           const double *__restrict__ ksumb, const double *__restrict__ ksums, const double *__restrict__ kaks,
-           const float *__restrict__ csky,
+           const double *__restrict__ sols, const KTap *__restrict__ ktap, const double *__restrict__ kernr,
+           const double *__restrict__ ksums, const double *__restrict__ kaks,
            float *__restrict__ rdiff, float *__restrict__ rnoise, int32_t *__restrict__ omask,
            float *__restrict__ diff, float *__restrict__ noise, int32_t *__restrict__ out_mask)
 {
     extern __shared__ __align__(128) unsigned char dyn[];
     float *raw_img = (float *)(dyn + G.o_raw_img);             // [TH][WR]
     float *raw_rms = (float *)(dyn + G.o_raw_rms);             // [TH][WR]
-    u64 *comp = (u64 *)(dyn + G.o_comp);                       // [TH][Wc]  (image - sky, variance)
-    u64 *kbuf = (u64 *)(dyn + G.o_k);                          // [NB][kstride]  (K, K^2) reversed, rows padded to fwp
-    float2 *res = (float2 *)(dyn + G.o_res);                   // [KS][OH][OW]  partial (conv, var) sums
+    double *compd = (double *)(dyn + G.o_compd);               // [TH][Wc]  image, widened once
+    float *compv = (float *)(dyn + G.o_compv);                 // [TH][Wv]  variance
+    KTap *kbuf = (KTap *)(dyn + G.o_k);                        // [NB][kstride]  (K, K^2) reversed, rows padded to fwp
+    double *resq = (double *)(dyn + G.o_resq);                 // [OH][OW]  convolved image (sum over the KS bands)
+    float *resv = (float *)(dyn + G.o_resv);                   // [OH][OW]  convolved variance
     unsigned *rmask = (unsigned *)(dyn + G.o_rmask);           // [2 parity][2 any/bad][TH][NW]
     unsigned *vmask = (unsigned *)(dyn + G.o_vmask);           // [2 parity][2 any/bad][OH][NW]
     uint64_t *bars = (uint64_t *)(dyn + G.o_misc);             // raw_full, raw_empty, k_full, k_empty, res_full, res_empty
     int *s_any = (int *)(bars + 6);                            // [2 parity]
-    double *s_qsky = (double *)(bars + 8);                     // [2 parity][CONV_MAX_NB] sky * sum(K) of the tile's blocks (epilogue)
+    double *s_pre = (double *)(dyn + G.o_pre);                 // [NB][fw][fwp+1]  prefix sums of |K| along each kernel row (uks/aks test)
+    unsigned short *resm = (unsigned short *)(dyn + G.o_resm); // [OH][OW]  mask bits the convolution contributes (alard.c:1312-1332)
+    unsigned *s_rowbad = (unsigned *)(bars + 8);               // [2 parity][16]  bit per tile row: the row holds a bad pixel
     uint64_t *raw_full = bars, *raw_empty = bars + 1, *k_full = bars + 2, *k_empty = bars + 3, *res_full = bars + 4, *res_empty = bars + 5;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int hw = D->p.hw_kernel, fw = D->sz.fw_kernel, B = D->sz.kc_step;
     const int NBX = G.NBX, NBY = G.NBY, NB = NBX * NBY, KS = G.KS;
     const int OW = NBX * B, OH = NBY * B;
-    const int TH = G.TH, Wt = G.Wt, WR = G.WR, Wc = G.Wc, NW = G.NW, fwp = G.fwp;
+    const int TH = G.TH, Wt = G.Wt, WR = G.WR, Wc = G.Wc, Wv = G.Wv, NW = G.NW, fwp = G.fwp;
     const int per_region = G.nbx_max * G.nby_max + 1;
     const int nxi = D->nx, nyi = D->ny;
     const float fill = D->p.fill_val;
@@ -428,7 +439,9 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
     __syncthreads();
 
     if (warp < 4) {
+#ifndef CONV_NO_SETMAXNREG
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(CONV_REGS_LIGHT));
+#endif
         if (warp == 0) {
             // ================================================================== producer
             int it = 0;
@@ -436,7 +449,9 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                 TileRef T; ZbRegion R;
                 if (!conv_tile(D, G, t, T, R)) continue;
                 const unsigned par = it & 1; it++;
-                const int gx0 = R.bx0 + T.bx0 * B, gy0 = R.by0 + T.by0 * B;     // tile origin, image coordinates
+                // tile origin, image coordinates; the box starts at the 16-byte aligned column at or before it: a tensor
+                // load whose innermost start is not 16-byte aligned raises an illegal-instruction trap (tools/tma_probe.cu)
+                const int gx0 = (R.bx0 + T.bx0 * B) & ~3, gy0 = R.by0 + T.by0 * B;
                 if (lane == 0) mbar_wait(raw_empty, par ^ 1);
                 __syncwarp();
                 if (G.use_tma) {
@@ -450,7 +465,7 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                     // row pitch or base address not TMA-encodable (nx % 4 != 0): the warp copies the box itself
                     for (int ty = 0; ty < TH; ty++) {
                         const int gy = gy0 + ty;
-                        for (int tx = lane; tx < Wt; tx += 32) {
+                        for (int tx = lane; tx < Wt + 3; tx += 32) {
                             const int gx = gx0 + tx;
                             const bool in = gx < nxi && gy < nyi;
                             raw_img[ty * WR + tx] = in ? P.conv[(long long)gy * nxi + gx] : 0.f;
@@ -464,19 +479,29 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                     mbar_wait(k_empty, par ^ 1);
                     int nex = 0;
                     for (int lb = 0; lb < NB; lb++) { const int lby = lb / NBX, lbx = lb - lby * NBX; nex += (T.bx0 + lbx < T.nbx && T.by0 + lby < T.nby); }
-                    mbar_expect_tx(k_full, (unsigned)(nex * G.kstride * 8));
+                    mbar_expect_tx(k_full, (unsigned)(nex * G.kstride * sizeof(KTap)));
                     for (int lb = 0; lb < NB; lb++) {
                         const int lby = lb / NBX, lbx = lb - lby * NBX;
                         if (!(T.bx0 + lbx < T.nbx && T.by0 + lby < T.nby)) continue;
-                        const float2 *src = kern32 + ((long long)T.r * per_region + (long long)(T.by0 + lby) * T.nbx + (T.bx0 + lbx)) * G.kstride;
-                        bulk_load(kbuf + (size_t)lb * G.kstride, src, (unsigned)(G.kstride * 8), k_full);
+                        const KTap *src = ktap + ((long long)T.r * per_region + (long long)(T.by0 + lby) * T.nbx + (T.bx0 + lbx)) * G.kstride;
+                        bulk_load(kbuf + (size_t)lb * G.kstride, src, (unsigned)(G.kstride * sizeof(KTap)), k_full);
                     }
                 }
                 __syncwarp();
             }
         } else {
             // ================================================================== epilogue (warps 1-3)
-            const int ew = warp - 1, et = tid - 32;
+            // A warp owns output rows ew, ew+3, ...; lanes own columns.  The global loads of a row (other image, its
+            // rms, its user mask: up to EPC column chunks of 32) are issued one row ahead of their use.
+            const int ew = warp - 1;
+            constexpr int EPC = 3;                                                 // column chunks handled per pass over a row
+            const bool conv_t = D->conv_template != 0;
+            const bool do_scale = conv_t ? (D->p.phot_normalize == 't') : (D->p.phot_normalize == 'i');
+            const bool bg_const = D->p.bg_order == 0;
+            const bool have_orms = P.other_rms != nullptr;
+            const double o_qq = __fmul_rn(P.o_quad, P.o_quad);
+            const float fill_noise = D->p.fill_val_noise;
+            const bool mask_out = D->p.kf_spread_mask2 >= 0;
             int it = 0;
             for (int t = blockIdx.x; t < G.n_tiles; t += gridDim.x) {
                 TileRef T; ZbRegion R;
@@ -486,113 +511,71 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                 const int i00 = T.bx0 * B + hw, j00 = T.by0 * B + hw;              // first output pixel, region coordinates
                 const double *sol = sols + (long long)r * (D->sz.n_comp_total + 1);
                 const double ksum = ksums[(size_t)r * 4], inv1 = 1. / ksum;
-                const double csk = (double)csky[r];
-                const bool conv_t = D->conv_template != 0;
-                const bool do_scale = conv_t ? (D->p.phot_normalize == 't') : (D->p.phot_normalize == 'i');
-                const bool bg_const = D->p.bg_order == 0;
                 const double bg0 = background_at(D, R, sol, 0, 0);                 // the whole background when bgo == 0
-                const bool have_orms = P.other_rms != nullptr;
-                const double o_qq = __fmul_rn(P.o_quad, P.o_quad);
-                const float kfm = D->p.ker_frac_mask, fill_noise = D->p.fill_val_noise;
-                const bool mask_out = D->p.kf_spread_mask2 >= 0;
                 const int ox_lim = min(OW, R.rpx - hw - i00), oy_lim = min(min(OH, (T.nby - T.by0) * B), R.rpy - hw - j00);
                 const int own_x0 = R.rx0 - R.bx0 - i00, own_x1 = R.own_x1 - R.bx0 - i00;   // ownership window, tile coords
                 const int own_y0 = R.ry0 - R.by0 - j00, own_y1 = R.own_y1 - R.by0 - j00;
                 const long long gout = (long long)(R.by0 + j00) * nxi + (R.bx0 + i00);
                 const long long lout = R.off + (long long)j00 * R.rpx + i00;
-                const long long blk0 = (long long)r * per_region + (long long)T.by0 * T.nbx + T.bx0;
-                const float invB = 1.0f / (float)B;
-                // sky term of the tile's blocks (global reads issued before the wait)
-                double my_qsky = 0.0;
-                if (et < NB) {
-                    const int lby = et / NBX, lbx = et - lby * NBX;
-                    if (T.bx0 + lbx < T.nbx && T.by0 + lby < T.nby) my_qsky = csk * ksumb[blk0 + (long long)lby * T.nbx + lbx];
-                }
                 mbar_wait(res_full, par);
-                double *qsky = s_qsky + par * CONV_MAX_NB;
-                if (et < NB) qsky[et] = my_qsky;
-                named_bar_sync(2, CONV_EPI_WARPS * 32);
                 const int any = s_any[par];
-                const unsigned *Rany = rmask + (size_t)(par * 2 + 0) * TH * NW, *Rbad = rmask + (size_t)(par * 2 + 1) * TH * NW;
-                const unsigned *Vany = vmask + (size_t)(par * 2 + 0) * OH * NW, *Vbad = vmask + (size_t)(par * 2 + 1) * OH * NW;
-                constexpr int EPB = 4;                                             // pixels per lane with their global loads in flight together
                 const int nchunk = (ox_lim + 31) >> 5;
-                const int nrow = oy_lim > ew ? (oy_lim - ew + CONV_EPI_WARPS - 1) / CONV_EPI_WARPS : 0;
-                const int nitems = nrow * nchunk;
-                const unsigned magic = (65536u + (unsigned)nchunk - 1u) / (unsigned)nchunk;      // item -> (row, chunk): nitems * nchunk << 2^16
-                for (int it0 = 0; it0 < nitems; it0 += EPB) {
-                    float oth[EPB], orv[EPB]; int ub[EPB], eox[EPB], eoy[EPB];
-#pragma unroll
-                    for (int e = 0; e < EPB; e++) {
-                        const int itm = it0 + e, j = (int)(((unsigned)itm * magic) >> 16), c = itm - j * nchunk;
-                        eox[e] = lane + 32 * c; eoy[e] = ew + CONV_EPI_WARPS * j;
-                        oth[e] = 0.f; orv[e] = 0.f; ub[e] = 0;
-                        if (itm >= nitems || eox[e] >= ox_lim) { eox[e] = -1; continue; }
-                        const long long g = gout + (long long)eoy[e] * nxi + eox[e];
-                        oth[e] = P.other[g];
-                        if (have_orms) orv[e] = P.other_rms[g];
-                        ub[e] = zb_read_mask(P.omask_src, P.odt, g);               // raw value: nothing may depend on a load here
-                    }
-                    // ONE copy of the per-pixel code, the batch rotated through element 0: unrolled it is several
-                    // thousand instructions that would share the instruction cache with the FMA loop
+                for (int c0 = 0; c0 < nchunk; c0 += EPC) {
+                    float oth[EPC], orv[EPC]; int ub[EPC];
+                    // loads of row `oy` for the chunks of this pass
+#define CONV_EPI_LOAD(OY, OTH, ORV, UB) do { \
+                        const long long grow_ = gout + (long long)(OY) * nxi; \
+                        _Pragma("unroll") for (int e = 0; e < EPC; e++) { \
+                            const int ox_ = lane + 32 * (c0 + e); \
+                            OTH[e] = 0.f; ORV[e] = 0.f; UB[e] = 0; \
+                            if ((OY) < oy_lim && ox_ < ox_lim) { \
+                                OTH[e] = P.other[grow_ + ox_]; \
+                                if (have_orms) ORV[e] = P.other_rms[grow_ + ox_]; \
+                                UB[e] = zb_read_mask(P.omask_src, P.odt, grow_ + ox_); } } } while (0)   /* raw values: nothing may depend on a load here */
+                    CONV_EPI_LOAD(ew, oth, orv, ub);
+                    for (int oy = ew; oy < oy_lim; oy += CONV_EPI_WARPS) {
+                        float noth[EPC], norv[EPC]; int nub[EPC];
+                        CONV_EPI_LOAD(oy + CONV_EPI_WARPS, noth, norv, nub);       // next row of this warp, in flight while this one is finished
+                        const long long grow = gout + (long long)oy * nxi, lrow = lout + (long long)oy * R.rpx;
+                        const bool own_row = oy >= own_y0 && oy <= own_y1;
+                        const double *rq = resq + (size_t)oy * OW;
+                        const float *rv = resv + (size_t)oy * OW;
+                        const unsigned short *rm = resm + (size_t)oy * OW;
 #pragma unroll 1
-                    for (int e = 0; e < EPB; e++) {
-                        const int ox = eox[0], oy = eoy[0];
-                        const float ov = oth[0], orv0 = orv[0]; const int ub0 = ub[0];
+                        for (int e = 0; e < EPC; e++) {
+                            const int ox = lane + 32 * (c0 + e);
+                            const float ov = oth[0], orv0 = orv[0]; const int ub0 = ub[0];
 #pragma unroll
-                        for (int q = 0; q + 1 < EPB; q++) { eox[q] = eox[q + 1]; eoy[q] = eoy[q + 1]; oth[q] = oth[q + 1]; orv[q] = orv[q + 1]; ub[q] = ub[q + 1]; }
-                        if (ox < 0) continue;
-                        const int obx = __float2int_rz(((float)ox + 0.5f) * invB), oby = __float2int_rz(((float)oy + 0.5f) * invB);
-                        const int lb = oby * NBX + obx;
-                        // mask of the convolved image at this pixel and under the footprint
-                        int m = 0;
-                        if (any) {
-                            const bool f_any = bits_at(Vany + (size_t)oy * NW, ox, fw) != 0ull;
-                            if ((Rany[(size_t)(oy + hw) * NW + ((ox + hw) >> 5)] >> ((ox + hw) & 31)) & 1u) {
-                                const long long g = gout + (long long)oy * nxi + ox;
-                                const int cm = user_bits(P.cmask_src, P.cdt, g) | value_bits(P.conv[g], fill, P.cU, P.cL);
-                                m |= cm;
-                                if (cm & ZB_FLAG_INPUT_ISBAD) m |= ZB_FLAG_OUTPUT_ISBAD;
+                            for (int q = 0; q + 1 < EPC; q++) { oth[q] = oth[q + 1]; orv[q] = orv[q + 1]; ub[q] = ub[q + 1]; }
+                            if (ox >= ox_lim) continue;
+                            int m = any ? (int)rm[ox] : 0;                     // what the convolution contributes (FMA warps)
+                            const float conv_out = (float)rq[ox];
+                            const float var = rv[ox];
+                            const int ob = value_bits(ov, fill, P.oU, P.oL);
+                            if (ob) m |= ob | ZB_FLAG_OUTPUT_ISBAD;
+                            const int ubit = ub0 | (ZB_FLAG_INPUT_MASK * (ub0 > 0));       // user_bits() of the prefetched raw mask value
+                            m |= ubit;
+                            if (ubit & ZB_FLAG_INPUT_ISBAD) m |= ZB_FLAG_OUTPUT_ISBAD;
+                            float ovar;
+                            if (have_orms) ovar = __fmul_rn(orv0, orv0);
+                            else ovar = (float)__dadd_rn(__dmul_rn(fabs((double)ov), (double)P.o_invgain), o_qq);
+                            // (float)sqrt((double)x) == sqrtf(x) correctly rounded: 53 >= 2*24+2 makes the double rounding innocuous
+                            float nz = __fsqrt_rn(__fadd_rn(ovar, var));
+                            const double bg = bg_const ? bg0 : background_at(D, R, sol, i00 + ox, j00 + oy);
+                            float d = __fsub_rn((float)__dadd_rn((double)conv_out, bg), ov);
+                            if (do_scale) { d = (float)__dmul_rn((double)d, inv1); nz = (float)__dmul_rn((double)nz, inv1); }
+                            if (conv_t) d = -d;
+                            rdiff[lrow + ox] = d; rnoise[lrow + ox] = nz; omask[lrow + ox] = m;
+                            if (own_row && ox >= own_x0 && ox <= own_x1) {
+                                if (mask_out && (m & ZB_FLAG_OUTPUT_ISBAD)) { d = fill; nz = fill_noise; }
+                                diff[grow + ox] = d; noise[grow + ox] = nz;
+                                if (out_mask) out_mask[grow + ox] = m;
                             }
-                            if (f_any) {
-                                bool low = false;                                  // no bad tap: uks == aks exactly
-                                if (bits_at(Vbad + (size_t)oy * NW, ox, fw) != 0ull) {
-                                    const long long blk = blk0 + (long long)oby * T.nbx + obx;
-                                    low = conv_kernel_fraction_low(kernr + blk * fw * fwp, Rbad + (size_t)oy * NW, NW, ox, fw, fwp, kfm, kaks[blk]);
-                                }
-                                if (low) m |= (ZB_FLAG_OUTPUT_ISBAD | ZB_FLAG_BAD_CONV);
-                                else m |= ZB_FLAG_OK_CONV;
-                            }
                         }
-                        double q = qsky[lb]; float var = 0.f;
-                        for (int g2 = 0; g2 < KS; g2++) {
-                            const float2 pr = res[((size_t)g2 * OH + oy) * OW + ox];
-                            q += (double)pr.x; var += pr.y;
-                        }
-                        const float conv_out = (float)q;
-                        const int ob = value_bits(ov, fill, P.oU, P.oL);
-                        if (ob) m |= ob | ZB_FLAG_OUTPUT_ISBAD;
-                        const int ubit = ub0 | (ZB_FLAG_INPUT_MASK * (ub0 > 0));           // user_bits() of the prefetched raw mask value
-                        m |= ubit;
-                        if (ubit & ZB_FLAG_INPUT_ISBAD) m |= ZB_FLAG_OUTPUT_ISBAD;
-                        float ovar;
-                        if (have_orms) ovar = __fmul_rn(orv0, orv0);
-                        else ovar = (float)__dadd_rn(__dmul_rn(fabs((double)ov), (double)P.o_invgain), o_qq);
-                        // (float)sqrt((double)x) == sqrtf(x) correctly rounded: 53 >= 2*24+2 makes the double rounding innocuous
-                        float nz = __fsqrt_rn(__fadd_rn(ovar, var));
-                        const double bg = bg_const ? bg0 : background_at(D, R, sol, i00 + ox, j00 + oy);
-                        float d = __fsub_rn((float)__dadd_rn((double)conv_out, bg), ov);
-                        if (do_scale) { d = (float)__dmul_rn((double)d, inv1); nz = (float)__dmul_rn((double)nz, inv1); }
-                        if (conv_t) d = -d;
-                        const long long l = lout + (long long)oy * R.rpx + ox;
-                        rdiff[l] = d; rnoise[l] = nz; omask[l] = m;
-                        if (ox >= own_x0 && ox <= own_x1 && oy >= own_y0 && oy <= own_y1) {
-                            if (mask_out && (m & ZB_FLAG_OUTPUT_ISBAD)) { d = fill; nz = fill_noise; }
-                            const long long g = gout + (long long)oy * nxi + ox;
-                            diff[g] = d; noise[g] = nz;
-                            if (out_mask) out_mask[g] = m;
-                        }
+#pragma unroll
+                        for (int e = 0; e < EPC; e++) { oth[e] = noth[e]; orv[e] = norv[e]; ub[e] = nub[e]; }
                     }
+#undef CONV_EPI_LOAD
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(res_empty);
@@ -600,7 +583,9 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
         }
     } else {
         // ====================================================================== FMA warps (4-11)
+#ifndef CONV_NO_SETMAXNREG
         asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CONV_REGS_FMA));
+#endif
         const int ft = tid - 128, fwarp = ft >> 5;
         const int Tg = CONV_FMA_THREADS / KS;                                      // threads of one kernel-row band
         const int g = ft / Tg, u = ft - g * Tg;
@@ -617,36 +602,61 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
             TileRef T; ZbRegion R;
             if (!conv_tile(D, G, t, T, R)) continue;
             const unsigned par = it & 1; it++;
-            const float c = csky[T.r];
             const int gx0 = R.bx0 + T.bx0 * B, gy0 = R.by0 + T.by0 * B;
+            const int sh = gx0 & 3;                                                // the raw box starts at the aligned column gx0 - sh
             unsigned *Rany = rmask + (size_t)(par * 2 + 0) * TH * NW, *Rbad = rmask + (size_t)(par * 2 + 1) * TH * NW;
             unsigned *Vany = vmask + (size_t)(par * 2 + 0) * OH * NW, *Vbad = vmask + (size_t)(par * 2 + 1) * OH * NW;
             mbar_wait(raw_full, par);
             if (ft == 0) s_any[par] = 0;
+            if (ft < 16) s_rowbad[par * 16 + ft] = 0u;
             named_bar_sync(1, CONV_FMA_THREADS);                                   // every FMA warp is done with the previous comp tile
-            // ---- convert: raw floats -> (image - sky, variance) pairs, flag bit rows
+            // ---- convert: raw floats -> image widened to double, variance, flag bit rows.  Two copies of the loop: the zuds
+            // call (rms map, no user mask on the convolved image) is a handful of instructions per pixel; everything else
+            // (gain/read-noise variance model, -tmi / -imi mask of the convolved image) takes the general form
             int anyf = 0;
-            for (int ty = fwarp; ty < TH; ty += NFW) {
-                const int gy = gy0 + ty;
-                for (int txb = 0; txb < Wt; txb += 32) {
-                    const int tx = txb + lane;
-                    int f = 0;
-                    if (tx < Wt) {
-                        const float pv = raw_img[ty * WR + tx];
-                        float var;
-                        if (have_rms) { const float rv = raw_rms[ty * WR + tx]; var = __fmul_rn(rv, rv); }
-                        else var = (float)__dadd_rn(__dmul_rn(fabs((double)pv), (double)P.c_invgain), c_qq);
-                        comp[(size_t)ty * Wc + tx] = pack2(__fsub_rn(pv, c), var);
-                        const int gx = gx0 + tx;
-                        if (gx < nxi && gy < nyi) {
-                            int cm = value_bits(pv, fill, P.cU, P.cL);
-                            if (P.cmask_src) cm |= user_bits(P.cmask_src, P.cdt, (long long)gy * nxi + gx);
-                            f = (cm ? 1 : 0) | ((cm & ZB_FLAG_INPUT_ISBAD) ? 2 : 0);
+            const int x_in = nxi - gx0;                                            // tile columns inside the frame
+            if (have_rms && !P.cmask_src) {
+                for (int ty = fwarp; ty < TH; ty += NFW) {
+                    const bool yin = gy0 + ty < nyi;
+                    const float *ri = raw_img + ty * WR + sh, *rr = raw_rms + ty * WR + sh;
+                    double *cd = compd + (size_t)ty * Wc;
+                    float *cv = compv + (size_t)ty * Wv;
+                    for (int txb = 0; txb < Wt; txb += 32) {
+                        const int tx = txb + lane;
+                        int cm = 0;
+                        if (tx < Wt) {
+                            const float pv = ri[tx], rv = rr[tx];
+                            cd[tx] = (double)pv;
+                            cv[tx] = __fmul_rn(rv, rv);
+                            if (yin && tx < x_in) cm = value_bits(pv, fill, P.cU, P.cL);
                         }
+                        const unsigned ba = __ballot_sync(0xffffffffu, cm != 0), bb = __ballot_sync(0xffffffffu, (cm & ZB_FLAG_INPUT_ISBAD) != 0);
+                        if (lane == 0) { Rany[ty * NW + (txb >> 5)] = ba; Rbad[ty * NW + (txb >> 5)] = bb; if (bb) atomicOr(&s_rowbad[par * 16 + (ty >> 5)], 1u << (ty & 31)); }
+                        anyf |= (ba != 0u);
                     }
-                    const unsigned ba = __ballot_sync(0xffffffffu, f & 1), bb = __ballot_sync(0xffffffffu, f & 2);
-                    if (lane == 0) { Rany[(size_t)ty * NW + (txb >> 5)] = ba; Rbad[(size_t)ty * NW + (txb >> 5)] = bb; }
-                    anyf |= (ba != 0u);
+                }
+            } else {
+                for (int ty = fwarp; ty < TH; ty += NFW) {
+                    const int gy = gy0 + ty;
+                    for (int txb = 0; txb < Wt; txb += 32) {
+                        const int tx = txb + lane;
+                        int cm = 0;
+                        if (tx < Wt) {
+                            const float pv = raw_img[ty * WR + tx + sh];
+                            float var;
+                            if (have_rms) { const float rv = raw_rms[ty * WR + tx + sh]; var = __fmul_rn(rv, rv); }
+                            else var = (float)__dadd_rn(__dmul_rn(fabs((double)pv), (double)P.c_invgain), c_qq);
+                            compd[(size_t)ty * Wc + tx] = (double)pv;
+                            compv[(size_t)ty * Wv + tx] = var;
+                            if (tx < x_in && gy < nyi) {
+                                cm = value_bits(pv, fill, P.cU, P.cL);
+                                if (P.cmask_src) cm |= user_bits(P.cmask_src, P.cdt, (long long)gy * nxi + gx0 + tx);
+                            }
+                        }
+                        const unsigned ba = __ballot_sync(0xffffffffu, cm != 0), bb = __ballot_sync(0xffffffffu, (cm & ZB_FLAG_INPUT_ISBAD) != 0);
+                        if (lane == 0) { Rany[ty * NW + (txb >> 5)] = ba; Rbad[ty * NW + (txb >> 5)] = bb; if (bb) atomicOr(&s_rowbad[par * 16 + (ty >> 5)], 1u << (ty & 31)); }
+                        anyf |= (ba != 0u);
+                    }
                 }
             }
             if (lane == 0 && anyf) s_any[par] = 1;
@@ -661,51 +671,99 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                     for (int dy = 0; dy < fw; dy++) v |= src[(size_t)dy * NW];
                     (pl ? Vbad : Vany)[(size_t)oy * NW + w] = v;
                 }
+                named_bar_sync(1, CONV_FMA_THREADS);                               // the band-0 owners read them after the multiply
             }
             // ---- multiply
             const bool active = lb < NB && T.bx0 + lbx < T.nbx && T.by0 + lby < T.nby;
-            double aq[TY][TX]; float av[TY][TX];
+            typedef typename std::conditional<VAR64, double, float>::type AV;
+            double aq[TY][TX]; AV av[TY][TX];
 #pragma unroll
             for (int oy = 0; oy < TY; oy++)
 #pragma unroll
-                for (int tt = 0; tt < TX; tt++) { aq[oy][tt] = 0.0; av[oy][tt] = 0.f; }
+                for (int tt = 0; tt < TX; tt++) { aq[oy][tt] = 0.0; av[oy][tt] = (AV)0; }
             mbar_wait(k_full, par);
+            const bool any_bad = (s_rowbad[par * 16 + 0] | s_rowbad[par * 16 + 1] | s_rowbad[par * 16 + 2] | s_rowbad[par * 16 + 3] |
+                                  s_rowbad[par * 16 + 4] | s_rowbad[par * 16 + 5] | s_rowbad[par * 16 + 6] | s_rowbad[par * 16 + 7] |
+                                  s_rowbad[par * 16 + 8] | s_rowbad[par * 16 + 9] | s_rowbad[par * 16 + 10] | s_rowbad[par * 16 + 11] |
+                                  s_rowbad[par * 16 + 12] | s_rowbad[par * 16 + 13]) != 0u;
+            if (any_bad) {
+                // prefix sums of |K| along every kernel row of the tile's blocks: one thread per row
+                for (int k = ft; k < NB * fw; k += CONV_FMA_THREADS) {
+                    const int b = k / fw, dy = k - b * fw;
+                    const KTap *kr = kbuf + (size_t)b * G.kstride + dy * fwp;
+                    double *pr = s_pre + (size_t)k * (fwp + 1);
+                    double acc = 0.0;
+                    pr[0] = 0.0;
+                    for (int dx = 0; dx < fw; dx++) { acc += fabs(kr[dx].k); pr[dx + 1] = acc; }
+                }
+                named_bar_sync(1, CONV_FMA_THREADS);
+            }
             if (active) {
-                const u64 *Kb = kbuf + (size_t)lb * G.kstride;
-                const u64 *tbase = comp + (size_t)y0 * Wc + x0;
+                const KTap *Kb = kbuf + (size_t)lb * G.kstride;
+                const double *tbd = compd + (size_t)y0 * Wc + x0;
+                const float *tbv = compv + (size_t)y0 * Wv + x0;
                 for (int s = dy0; s < dy1 + TY - 1; s++) {
-                    const u64 *trow = tbase + (size_t)s * Wc;
+                    const double *trd = tbd + (size_t)s * Wc;
+                    const float *trv = tbv + (size_t)s * Wv;
                     const bool steady = (s - (TY - 1) >= dy0) && (s < dy1);        // every output row of the thread sees this tile row
-                    u64 ra[TY][TX];
-                    conv_chunk<TX, TY, CH, EXACT, true>(trow, Kb, 0, s, fw, fwp, dy0, dy1, steady, ra);
-                    for (int ch = CH; ch < fwp; ch += CH) conv_chunk<TX, TY, CH, EXACT, false>(trow, Kb, ch, s, fw, fwp, dy0, dy1, steady, ra);
-#pragma unroll
-                    for (int oy = 0; oy < TY; oy++) {
-                        const int dy = s - oy;
-                        if (!steady && (dy < dy0 || dy >= dy1)) continue;
-#pragma unroll
-                        for (int tt = 0; tt < TX; tt++) {
-                            float a, b; unpack2(ra[oy][tt], a, b);
-                            aq[oy][tt] += (double)a; av[oy][tt] += b;
+                    for (int ch = 0; ch < fwp; ch += CH) conv_chunk<TX, TY, CH, EXACT, VAR64, AV>(trd, trv, Kb, ch, s, fw, fwp, dy0, dy1, steady, aq, av);
+                }
+            }
+            // ---- what the convolution contributes to the mask (alard.c:1304-1332), by the band-0 owner of each output: the
+            // pixel's own bits with OUTPUT_ISBAD when it is bad; OK_CONV when a flagged pixel lies under the footprint, or
+            // BAD_CONV | OUTPUT_ISBAD when too much of the kernel sits on bad pixels
+            mbar_wait(res_empty, par ^ 1);
+            if (active && g == 0 && s_any[par]) {
+                const float kfm = D->p.ker_frac_mask;
+                const u64 fmask = (1ull << fw) - 1ull;
+                const double aks_blk = any_bad ? kaks[(long long)T.r * per_region + (long long)(T.by0 + lby) * T.nbx + (T.bx0 + lbx)] : 1.0;
+                const KTap *Kb = kbuf + (size_t)lb * G.kstride;
+                const double *pre = s_pre + (size_t)lb * fw * (fwp + 1);
+#pragma unroll 1
+                for (int oy = 0; oy < TY; oy++) {
+                    if (gyi * TY + oy >= B) break;
+                    const int yy = y0 + oy;
+                    const u64 wa = bits_at(Vany + (size_t)yy * NW, x0, TX + fw - 1), wb = bits_at(Vbad + (size_t)yy * NW, x0, TX + fw - 1);
+                    const u64 wc = bits_at(Rany + (size_t)(yy + hw) * NW, x0 + hw, TX);
+                    const u64 rows = any_bad ? bits_at(s_rowbad + par * 16, yy, fw) : 0ull;
+#pragma unroll 1
+                    for (int tt = 0; tt < TX; tt++) {
+                        if (gxi * TX + tt >= B) break;
+                        int m = 0;
+                        if ((wc >> tt) & 1ull) {
+                            const float pv = (float)compd[(size_t)(yy + hw) * Wc + x0 + tt + hw];
+                            int cm = value_bits(pv, fill, P.cU, P.cL);
+                            if (P.cmask_src) cm |= user_bits(P.cmask_src, P.cdt, (long long)(gy0 + yy + hw) * nxi + gx0 + x0 + tt + hw);
+                            m |= cm;
+                            if (cm & ZB_FLAG_INPUT_ISBAD) m |= ZB_FLAG_OUTPUT_ISBAD;
                         }
+                        if ((wa >> tt) & fmask) {
+                            bool low = false;                                      // no bad tap: uks == aks exactly
+                            if ((wb >> tt) & fmask) low = conv_kernel_fraction_low(pre, Kb, Rbad + (size_t)yy * NW, NW, x0 + tt, rows, fw, fwp, kfm, aks_blk);
+                            m |= low ? (ZB_FLAG_OUTPUT_ISBAD | ZB_FLAG_BAD_CONV) : ZB_FLAG_OK_CONV;
+                        }
+                        resm[(size_t)yy * OW + x0 + tt] = (unsigned short)m;
                     }
                 }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(k_empty);                                   // kernels (and, with the bar.sync above, comp) are free
-            // ---- hand the sums to the epilogue warps
-            mbar_wait(res_empty, par ^ 1);
-            if (active) {
-                float2 *rp = res + (size_t)g * OH * OW;
+            // ---- hand the sums to the epilogue warps: band 0 stores, the other bands of kernel rows add in band order
+            for (int gb = 0; gb < KS; gb++) {
+                if (active && g == gb) {
 #pragma unroll
-                for (int oy = 0; oy < TY; oy++) {
-                    if (gyi * TY + oy >= B) break;
+                    for (int oy = 0; oy < TY; oy++) {
+                        if (gyi * TY + oy >= B) break;
 #pragma unroll
-                    for (int tt = 0; tt < TX; tt++) {
-                        if (gxi * TX + tt >= B) break;
-                        rp[(size_t)(y0 + oy) * OW + x0 + tt] = make_float2((float)aq[oy][tt], av[oy][tt]);
+                        for (int tt = 0; tt < TX; tt++) {
+                            if (gxi * TX + tt >= B) break;
+                            const size_t k = (size_t)(y0 + oy) * OW + x0 + tt;
+                            if (gb == 0) { resq[k] = aq[oy][tt]; resv[k] = (float)av[oy][tt]; }
+                            else { resq[k] += aq[oy][tt]; resv[k] = (float)((AV)resv[k] + av[oy][tt]); }
+                        }
                     }
                 }
+                if (gb + 1 < KS) named_bar_sync(1, CONV_FMA_THREADS);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(res_full);
@@ -769,43 +827,50 @@ static inline unsigned up128(size_t v) { return (unsigned)((v + 127) & ~(size_t)
 static size_t conv_plan(ConvGeom &G, int B, int fw, int TX, int TY, int CH, bool have_rms) {
     const int nch = (fw + CH - 1) / CH;
     G.fwp = nch * CH;
-    G.kstride = (fw * G.fwp + 1) & ~1;
+    G.kstride = fw * G.fwp;
     G.Wt = (G.NBX - 1) * B + G.GX * TX + G.fwp - 1;
     G.TH = (G.NBY - 1) * B + G.GY * TY + fw - 1;
-    G.WR = (G.Wt + 3) & ~3;
+    G.WR = (G.Wt + 3 + 3) & ~3;      // + up to 3 columns: the box starts at a 16-byte aligned column (TMA traps otherwise)
     G.NW = (G.Wt + 31) / 32 + 2;
-    // comp row pitch: fewest shared-memory conflicts of the window loads (8-byte elements, 16 lanes per
-    // wavefront) for the thread layout of the first two warps of a band
+    // row pitches of the two planes: fewest shared-memory conflicts of the window loads for the thread layout of the
+    // first four half-warps (double plane: 8-byte elements, 16 lanes per wavefront) / two warps (float plane: 32 lanes)
     {
         const int tpb = G.GX * G.GY;
-        int best = -1, bestw = G.Wt;
-        for (int wc = G.Wt; wc < G.Wt + 16; wc++) {
-            int worst = 0;
-            for (int h = 0; h < 4; h++) {
-                int cnt[16] = {0};
-                for (int l = 0; l < 16; l++) {
-                    const int u = h * 16 + l, lb = u / tpb, lt = u - lb * tpb;
-                    const int gx = lt / G.GY, gy = lt - gx * G.GY, lby = lb / G.NBX, lbx = lb - lby * G.NBX;
-                    if (lb >= G.NBX * G.NBY) continue;
-                    const long a = (long)(lby * B + gy * TY) * wc + lbx * B + gx * TX;
-                    cnt[a & 15]++;
+        for (int plane = 0; plane < 2; plane++) {
+            const int lanes = plane == 0 ? 16 : 32, groups = plane == 0 ? 4 : 2;
+            int best = -1, bestw = G.Wt;
+            for (int wc = G.Wt; wc < G.Wt + 2 * lanes; wc++) {
+                int worst = 0;
+                for (int h = 0; h < groups; h++) {
+                    int cnt[32] = {0};
+                    for (int l = 0; l < lanes; l++) {
+                        const int u = h * lanes + l, lb = u / tpb, lt = u - lb * tpb;
+                        const int gx = lt / G.GY, gy = lt - gx * G.GY, lby = lb / G.NBX, lbx = lb - lby * G.NBX;
+                        if (lb >= G.NBX * G.NBY) continue;
+                        const long a = (long)(lby * B + gy * TY) * wc + lbx * B + gx * TX;
+                        cnt[a & (lanes - 1)]++;
+                    }
+                    for (int k = 0; k < lanes; k++) worst = cnt[k] > worst ? cnt[k] : worst;
                 }
-                for (int k = 0; k < 16; k++) worst = cnt[k] > worst ? cnt[k] : worst;
+                if (best < 0 || worst < best) { best = worst; bestw = wc; }
             }
-            if (best < 0 || worst < best) { best = worst; bestw = wc; }
+            if (plane == 0) G.Wc = bestw; else G.Wv = bestw;
         }
-        G.Wc = bestw;
     }
     const int NB = G.NBX * G.NBY, OW = G.NBX * B, OH = G.NBY * B;
     size_t o = 0;
     G.o_raw_img = up128(o); o = G.o_raw_img + (size_t)G.WR * G.TH * 4;
     G.o_raw_rms = up128(o); o = G.o_raw_rms + (have_rms ? (size_t)G.WR * G.TH * 4 : 0);
-    G.o_comp = up128(o);    o = G.o_comp + (size_t)G.Wc * G.TH * 8;
-    G.o_k = up128(o);       o = G.o_k + (size_t)NB * G.kstride * 8;
-    G.o_res = up128(o);     o = G.o_res + (size_t)G.KS * OH * OW * 8;
+    G.o_compd = up128(o);   o = G.o_compd + (size_t)G.Wc * G.TH * 8;
+    G.o_compv = up128(o);   o = G.o_compv + (size_t)G.Wv * G.TH * 4;
+    G.o_k = up128(o);       o = G.o_k + (size_t)NB * G.kstride * sizeof(KTap);
+    G.o_resq = up128(o);    o = G.o_resq + (size_t)OH * OW * 8;
+    G.o_resv = up128(o);    o = G.o_resv + (size_t)OH * OW * 4;
     G.o_rmask = up128(o);   o = G.o_rmask + (size_t)4 * G.TH * G.NW * 4;
     G.o_vmask = up128(o);   o = G.o_vmask + (size_t)4 * OH * G.NW * 4;
-    G.o_misc = up128(o);    o = G.o_misc + 64 + (size_t)2 * CONV_MAX_NB * 8;
+    G.o_pre = up128(o);     o = G.o_pre + (size_t)NB * fw * (G.fwp + 1) * 8;
+    G.o_resm = up128(o);    o = G.o_resm + (size_t)OH * OW * 2;
+    G.o_misc = up128(o);    o = G.o_misc + 64 + 2 * 16 * 4;
     return o;
 }
 
@@ -830,7 +895,7 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
     const float tinv = (float)(1. / p.t_gain), tq = p.t_rdnoise / p.t_gain, iinv = (float)(1. / p.i_gain), iq = p.i_rdnoise / p.i_gain;
     P.c_invgain = ct ? tinv : iinv; P.c_quad = ct ? tq : iq;
     P.o_invgain = ct ? iinv : tinv; P.o_quad = ct ? iq : tq;
-    if (fw > 64) { snprintf(ctx->err, sizeof ctx->err, "kernel width %d > 64 is not built", fw); return ZB_ERR_UNSUPPORTED; }
+    if (fw > 55) { snprintf(ctx->err, sizeof ctx->err, "kernel width %d > 55 is not built", fw); return ZB_ERR_UNSUPPORTED; }
 
     // register tile per kernel-block size: (TX, TY, CH) with GX*TX >= B, GY*TY >= B
     int TXr, TYr, CHr;
@@ -854,9 +919,10 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
                     if (env_nbx > 0 && !(bx == env_nbx && by == env_nby && ks == env_ks)) continue;
                     const int nb = bx * by;
                     if (nb * tpb > CONV_FMA_THREADS / ks || nb > CONV_MAX_NB || ks > fw) continue;
+                    if (p.convolve_variance && ks > 1) continue;               // -convvar: the double variance sum is not split into bands
                     ConvGeom T = G; T.NBX = bx; T.NBY = by; T.KS = ks;
                     const size_t sm = conv_plan(T, B, fw, TXr, TYr, CHr, have_rms);
-                    if (sm > (size_t)ZB_SMEM_OPTIN || T.WR > 256 || T.TH > 256) continue;
+                    if (sm > (size_t)ZB_SMEM_CONV || T.WR > 256 || T.TH > 256 || T.TH > 16 * 32 - 64) continue;
                     const double util = (double)(nb * tpb * ks) / CONV_FMA_THREADS;
                     const double halo = (double)(nb * B * B) / ((double)T.Wt * T.TH);
                     const int lo = fw / ks, hi = (fw + ks - 1) / ks;               // band imbalance: the tile waits for the widest band
@@ -886,7 +952,7 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
 
     dim3 gk((nbx_max * nby_max + 1 + MK_NB - 1) / MK_NB + 1, nR);
     k_make_kernels<<<gk, 256, 0, st>>>(ctx->d_dev, ctx->d_sol, ctx->d_kvec, ctx->d_kern, ctx->d_kernr, G.fwp, ctx->d_kstat, ctx->d_kaks, nbx_max, nby_max,
-                                       ctx->d_kern32, G.kstride, ctx->d_ksumb, ctx->d_csky, ctx->d_stamps); ZB_DBG("k_make_kernels");
+                                       (KTap *)ctx->d_ktap, G.kstride); ZB_DBG("k_make_kernels");
     CUtensorMap tm_img, tm_rms;
     memset(&tm_img, 0, sizeof tm_img); memset(&tm_rms, 0, sizeof tm_rms);
     static int env_notma = -1;
@@ -897,11 +963,14 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
     if (grid > nt) grid = nt;
     cudaEventRecord(ctx->ev[10], st);          // k_convolve alone: the kernel bench.py's roofline is quoted on
     if (grid > 0) {
-#define ZB_CONV_LAUNCH2(TX_, TY_, CH_, EX_) do { \
-        cudaFuncSetAttribute(k_convolve<TX_, TY_, CH_, EX_>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN); \
-        k_convolve<TX_, TY_, CH_, EX_><<<grid, CONV_THREADS, smem, st>>>(tm_img, tm_rms, ctx->d_dev, P, G, ctx->d_sol, ctx->d_kern32, ctx->d_kernr, \
-            ctx->d_ksumb, ctx->d_kstat, ctx->d_kaks, ctx->d_csky, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask); } while (0)
-#define ZB_CONV_LAUNCH(TX_, TY_, CH_) do { if ((fw % CH_) == 0) ZB_CONV_LAUNCH2(TX_, TY_, CH_, true); else ZB_CONV_LAUNCH2(TX_, TY_, CH_, false); } while (0)
+#define ZB_CONV_LAUNCH2(TX_, TY_, CH_, EX_, V64_) do { \
+        cudaFuncSetAttribute(k_convolve<TX_, TY_, CH_, EX_, V64_>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_CONV); \
+        k_convolve<TX_, TY_, CH_, EX_, V64_><<<grid, CONV_THREADS, smem, st>>>(tm_img, tm_rms, ctx->d_dev, P, G, ctx->d_sol, (const KTap *)ctx->d_ktap, ctx->d_kernr, \
+            ctx->d_kstat, ctx->d_kaks, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask); } while (0)
+#define ZB_CONV_LAUNCH(TX_, TY_, CH_) do { \
+        if (p.convolve_variance) ZB_CONV_LAUNCH2(TX_, TY_, CH_, false, true); \
+        else if ((fw % CH_) == 0) ZB_CONV_LAUNCH2(TX_, TY_, CH_, true, false); \
+        else ZB_CONV_LAUNCH2(TX_, TY_, CH_, false, false); } while (0)
         if (B <= 12)      ZB_CONV_LAUNCH(4, 3, 4);
         else if (B <= 24) ZB_CONV_LAUNCH(7, 3, 7);
         else              ZB_CONV_LAUNCH(8, 3, 8);

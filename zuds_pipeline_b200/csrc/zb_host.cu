@@ -258,7 +258,7 @@ static void free_workspace(zb_ctx *ctx) {
                       (void **)&ctx->d_cells, (void **)&ctx->d_stamps, (void **)&ctx->d_vec, (void **)&ctx->d_kref, (void **)&ctx->d_gram,
                       (void **)&ctx->d_rhs, (void **)&ctx->d_wxy, (void **)&ctx->d_mat, (void **)&ctx->d_sol, (void **)&ctx->d_vv,
                       (void **)&ctx->d_indx, (void **)&ctx->d_fit, (void **)&ctx->d_jobs, (void **)&ctx->d_njobs, (void **)&ctx->d_kern, (void **)&ctx->d_kernr, (void **)&ctx->d_kaks,
-                      (void **)&ctx->d_kern32, (void **)&ctx->d_ksumb, (void **)&ctx->d_csky,
+                      (void **)&ctx->d_ktap,
                       (void **)&ctx->d_kstat, (void **)&ctx->d_stats, (void **)&ctx->d_qa, (void **)&ctx->d_qpart};
     for (size_t i = 0; i < sizeof dptrs / sizeof dptrs[0]; i++) { if (*dptrs[i]) cudaFree(*dptrs[i]); *dptrs[i] = NULL; }
     void **hptrs[] = {(void **)&ctx->h_dev, (void **)&ctx->h_cells, (void **)&ctx->h_stamps, (void **)&ctx->h_fit, (void **)&ctx->h_njobs, (void **)&ctx->h_stats};
@@ -272,6 +272,11 @@ extern "C" void zb_destroy(zb_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     free_workspace(ctx);
     for (int i = 0; i < 9; i++) if (ctx->d_stage[i]) cudaFree(ctx->d_stage[i]);
+    for (int i = 0; i < 9; i++) if (ctx->d_stage_b[i]) cudaFree(ctx->d_stage_b[i]);
+    if (ctx->batch_ready) {
+        cudaStreamDestroy(ctx->st_h2d); cudaStreamDestroy(ctx->st_d2h);
+        for (int i = 0; i < 2; i++) { cudaEventDestroy(ctx->ev_h2d[i]); cudaEventDestroy(ctx->ev_d2h[i]); cudaEventDestroy(ctx->ev_done[i]); }
+    }
     if (ctx->d_search_scratch) cudaFree(ctx->d_search_scratch);
     if (ctx->d_bkg) cudaFree(ctx->d_bkg);
     if (ctx->h_bkg) cudaFreeHost(ctx->h_bkg);
@@ -400,9 +405,7 @@ int zb_configure(zb_ctx *ctx, const zb_params *p) {
     DMALLOC(ctx->d_kern, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * fw * fw * sizeof(double));
     DMALLOC(ctx->d_kernr, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * fw * (fw + 8) * sizeof(double));
     DMALLOC(ctx->d_kaks, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * sizeof(double));
-    DMALLOC(ctx->d_kern32, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * (fw * (fw + 8) + 2) * sizeof(float2));
-    DMALLOC(ctx->d_ksumb, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * sizeof(double));
-    DMALLOC(ctx->d_csky, (size_t)sz.n_regions * sizeof(float));
+    DMALLOC(ctx->d_ktap, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * fw * (fw + 8) * 16);
     DMALLOC(ctx->d_kstat, (size_t)sz.n_regions * 4 * sizeof(double));
     const size_t stat_bytes = (size_t)sz.n_regions * ((size_t)sz.n_comp_total + 512) * sizeof(double) + ns * 8;
     DMALLOC(ctx->d_stats, stat_bytes);   HMALLOC(ctx->h_stats, stat_bytes);
@@ -707,6 +710,89 @@ extern "C" int zb_subtract_host(zb_ctx *ctx, const zb_params *p,
     return ZB_OK;
 }
 
+// ------------------------------------------------------------ batched host-buffer entry
+
+static int stage_buf_set(zb_ctx *ctx, int set, int i, size_t bytes) {
+    void **buf = set ? &ctx->d_stage_b[i] : &ctx->d_stage[i];
+    size_t *have = set ? &ctx->stage_b_bytes[i] : &ctx->stage_bytes[i];
+    if (*have >= bytes && *buf) return ZB_OK;
+    if (*buf) cudaFree(*buf);
+    *buf = NULL; *have = 0;
+    if (cudaMalloc(buf, bytes) != cudaSuccess) { snprintf(ctx->err, sizeof ctx->err, "cudaMalloc of %zu staging bytes failed", bytes); return ZB_ERR_NOMEM; }
+    *have = bytes;
+    return ZB_OK;
+}
+
+// npairs subtractions of one geometry, software-pipelined inside the context: while pair n is computed, the inputs
+// of pair n+1 travel to the other staging set on a copy stream and the products of pair n-1 travel back on a third
+// (SURVEY.md 8(b)'s zb_subtract_batch).  One cudaMemcpyAsync per array.  Per-pair status in rcs[] (may be NULL);
+// returns the first non-OK status after finishing the batch.
+extern "C" int zb_subtract_batch(zb_ctx *ctx, int npairs, const zb_params *params, const zb_host_pair *pairs,
+                                 zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps, int *rcs)
+{
+    if (!ctx || npairs < 0 || (npairs && (!params || !pairs))) { if (ctx) snprintf(ctx->err, sizeof ctx->err, "null argument"); return ZB_ERR_PARAM; }
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return zb_cuda_fail(ctx, cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
+    if (!ctx->batch_ready) {
+        if (cudaStreamCreateWithFlags(&ctx->st_h2d, cudaStreamNonBlocking) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->st_d2h, cudaStreamNonBlocking) != cudaSuccess)
+            return zb_cuda_fail(ctx, cudaGetLastError(), "copy streams", __FILE__, __LINE__);
+        for (int i = 0; i < 2; i++) {
+            cudaEventCreateWithFlags(&ctx->ev_h2d[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&ctx->ev_d2h[i], cudaEventDisableTiming);
+            cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming);
+        }
+        ctx->batch_ready = 1;
+    }
+    cudaStream_t st = ctx->stream;
+    int first_bad = ZB_OK;
+    // upload of pair i into staging set i & 1 (after the set's previous products have left and its previous inputs were consumed)
+    auto upload = [&](int i) -> int {
+        const int set = i & 1;
+        const zb_params *p = &params[i];
+        const zb_host_pair &h = pairs[i];
+        if (!h.sci || !h.ref || !h.diff || !h.noise) { snprintf(ctx->err, sizeof ctx->err, "pair %d: null image pointer", i); return ZB_ERR_PARAM; }
+        const size_t n = (size_t)p->nx * p->ny;
+        const void *src[6] = {h.sci, h.ref, h.sci_rms, h.ref_rms, h.sci_mask, h.ref_mask};
+        const size_t esz[6] = {4, 4, 4, 4, mask_elem(h.sci_mask_dtype), mask_elem(h.ref_mask_dtype)};
+        void **buf = set ? ctx->d_stage_b : ctx->d_stage;
+        for (int k = 0; k < 6; k++) if (src[k]) CHECK_RC(stage_buf_set(ctx, set, k, n * esz[k]));
+        CHECK_RC(stage_buf_set(ctx, set, 6, n * 4)); CHECK_RC(stage_buf_set(ctx, set, 7, n * 4));
+        if (h.out_mask) CHECK_RC(stage_buf_set(ctx, set, 8, n * 4));
+        if (i >= 2) { cudaStreamWaitEvent(ctx->st_h2d, ctx->ev_done[set], 0); cudaStreamWaitEvent(ctx->st_h2d, ctx->ev_d2h[set], 0); }
+        for (int k = 0; k < 6; k++) if (src[k]) cudaMemcpyAsync(buf[k], src[k], n * esz[k], cudaMemcpyHostToDevice, ctx->st_h2d);
+        cudaEventRecord(ctx->ev_h2d[set], ctx->st_h2d);
+        return ZB_OK;
+    };
+    if (npairs > 0) { int rc = upload(0); if (rc != ZB_OK) return rc; }
+    for (int i = 0; i < npairs; i++) {
+        const int set = i & 1;
+        const zb_params *p = &params[i];
+        const zb_host_pair &h = pairs[i];
+        const size_t n = (size_t)p->nx * p->ny;
+        void **buf = set ? ctx->d_stage_b : ctx->d_stage;
+        if (i + 1 < npairs) { int rc = upload(i + 1); if (rc != ZB_OK) { if (rcs) rcs[i + 1] = rc; if (first_bad == ZB_OK) first_bad = rc; } }
+        cudaStreamWaitEvent(st, ctx->ev_h2d[set], 0);
+        zb_sizes sz; zb_sizes_of(p, &sz);
+        int rc = zb_subtract(ctx, p, (const float *)buf[0], (const float *)buf[1],
+                             h.sci_rms ? (const float *)buf[2] : NULL, h.ref_rms ? (const float *)buf[3] : NULL,
+                             h.sci_mask ? buf[4] : NULL, h.sci_mask_dtype, h.ref_mask ? buf[5] : NULL, h.ref_mask_dtype,
+                             (float *)buf[6], (float *)buf[7], h.out_mask ? (int32_t *)buf[8] : NULL,
+                             regions + (size_t)i * sz.n_regions, kernel_sol ? kernel_sol + (size_t)i * sz.n_regions * (sz.n_comp_total + 1) : NULL,
+                             stamps ? stamps + (size_t)i * sz.n_regions * sz.n_stamps : NULL, ZB_STREAM_OWN);
+        if (rcs) rcs[i] = rc;
+        cudaEventRecord(ctx->ev_done[set], st);
+        if (rc != ZB_OK) { if (first_bad == ZB_OK) first_bad = rc; continue; }
+        // zb_subtract returns with the products complete on `st`: send them home on the third stream
+        cudaStreamWaitEvent(ctx->st_d2h, ctx->ev_done[set], 0);
+        cudaMemcpyAsync(h.diff, buf[6], n * 4, cudaMemcpyDeviceToHost, ctx->st_d2h);
+        cudaMemcpyAsync(h.noise, buf[7], n * 4, cudaMemcpyDeviceToHost, ctx->st_d2h);
+        if (h.out_mask) cudaMemcpyAsync(h.out_mask, buf[8], n * 4, cudaMemcpyDeviceToHost, ctx->st_d2h);
+        cudaEventRecord(ctx->ev_d2h[set], ctx->st_d2h);
+    }
+    cudaError_t e = zb_stream_wait(ctx, ctx->st_d2h);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->st_h2d);
+    if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "zb_subtract_batch copies", __FILE__, __LINE__);
+    return first_bad;
+}
+
 // ABI self-check used by the loader tests: sizeof of the public structs as this library was built.
 extern "C" int zb_abi_sizeof(int which) {
     switch (which) {
@@ -715,6 +801,7 @@ extern "C" int zb_abi_sizeof(int which) {
     case 2: return (int)sizeof(zb_region_info);
     case 3: return (int)sizeof(zb_stamp_info);
     case 4: return (int)sizeof(zb_tile_info);
+    case 5: return (int)sizeof(zb_host_pair);
     default: return -1;
     }
 }

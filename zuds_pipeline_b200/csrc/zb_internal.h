@@ -142,9 +142,7 @@ struct zb_ctx {
     double  *d_kern;             // [region][blocks+1][fw*fw]  K per convolution block (+ the region-centre kernel)
     double  *d_kernr;            // the same kernels reversed, rows padded to the convolution's chunk width (what k_convolve stages)
     double  *d_kaks;             // [region][blocks+1]  sum |K| per block in the reference's tap order
-    float2  *d_kern32;           // [region][blocks+1][kstride]  (K, K^2) float pairs, reversed, rows padded: k_convolve's operand
-    double  *d_ksumb;            // [region][blocks+1]  sum K per block (sky term of k_convolve)
-    float   *d_csky;             // [region]  sky level subtracted before the FP32 products
+    void    *d_ktap;             // [region][blocks+1][fw*fwp] 16-byte taps (K double, K^2 float), reversed, rows padded: k_convolve's operand
     int      n_sm;               // multiprocessors of the device (grid of the persistent kernels)
     double  *d_kstat;            // per-region: ksum, aks
     double  *d_stats;  double *h_stats;   // region QA scratch
@@ -154,6 +152,11 @@ struct zb_ctx {
     void *d_bkg; double *h_bkg;  // background-estimate selection state (zb_bkg.cu)
     // staging for zb_subtract_host
     void *d_stage[9]; size_t stage_bytes[9];
+    // zb_subtract_batch: a second staging set, copy streams and events (H2D of pair n+1 and D2H of pair n-1 overlap pair n)
+    void *d_stage_b[9]; size_t stage_b_bytes[9];
+    cudaStream_t st_h2d, st_d2h;
+    cudaEvent_t ev_h2d[2], ev_d2h[2], ev_done[2];
+    int batch_ready;
     ZbTile tile;
     // timings
     cudaEvent_t ev[ZB_NSTAGES + 1];

@@ -45,19 +45,21 @@ def get_my_share_of_work(fname, reader=default_reader, rank=None, size=None):
     return batch.shard(files, rank, size)
 
 
-def do_one(line, subclass=SingleEpochSubtraction, tmpdir='/tmp', **kwargs):
+def do_one(line, subclass=SingleEpochSubtraction, tmpdir='/tmp', quiet=False, **kwargs):
     """One pair: load, refuse to redo, subtract (scripts/dosub.py:26-187 minus catalog/DB steps)."""
     tstart = time.time()
     scipath, refpath = line.split()[:2]
     sci = CalibratableImageBase.from_file(scipath)
     ref = CalibratableImageBase.from_file(refpath)
-    print(f'load: {time.time() - tstart:.2f} sec to load input images', flush=True)
+    if not quiet:
+        print(f'load: {time.time() - tstart:.2f} sec to load input images', flush=True)
     final = sub_name(sci.local_path, ref.local_path)
     if os.path.exists(final):
         raise PredecessorError(f'{os.path.basename(final)} already has a predecessor')
     substart = time.time()
     sub = subclass.from_images(sci, ref, data_product=False, tmpdir=tmpdir, **kwargs)
-    print(f'sub: {time.time() - substart:.2f} sec to make {sub.basename}', flush=True)
+    if not quiet:
+        print(f'sub: {time.time() - substart:.2f} sec to make {sub.basename}', flush=True)
     return sub
 
 

@@ -60,6 +60,14 @@ class ZbStampInfo(C.Structure):
                 ("mode", C.c_double), ("fwhm", C.c_double), ("chi2", C.c_double)]
 
 
+class ZbHostPair(C.Structure):
+    """zb_host_pair (include/zb200.h): the host pointers of one pair for zb_subtract_batch."""
+    _fields_ = [("sci", C.c_void_p), ("ref", C.c_void_p), ("sci_rms", C.c_void_p), ("ref_rms", C.c_void_p),
+                ("sci_mask", C.c_void_p), ("ref_mask", C.c_void_p),
+                ("sci_mask_dtype", C.c_int32), ("ref_mask_dtype", C.c_int32),
+                ("diff", C.c_void_p), ("noise", C.c_void_p), ("out_mask", C.c_void_p)]
+
+
 def default_params(nx=0, ny=0):
     """Defaults of every flag, hotpants/vargs.c:55-128 + defaults.h:27-80."""
     p = ZbParams()

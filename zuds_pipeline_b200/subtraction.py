@@ -1,10 +1,12 @@
 """Drop-in for ``zuds.subtraction``: ``sub_name`` and ``Subtraction.from_images``.
 
-Same call signature, keyword arguments (``subtract_back``, ``nreg_side``, ``hotpants_kws``), file
-products (``sub.<sci>_<ref>.fits``, ``.rms.fits``, ``.mask.fits``), header keywords and mask-bit
-semantics as zuds/subtraction.py:25-226 — with the fork/exec of the ``hotpants`` binary
-(zuds/subtraction.py:162) replaced by the in-process GPU path (``hotpants.run_hotpants``), and without
-the Postgres records and the archive copy (out of scope).
+Same call signature, keyword arguments (``subtract_back``, ``nreg_side``, ``hotpants_kws``), file products
+(``sub.<sci>_<ref>.fits``, ``.rms.fits``, ``.mask.fits``), header keywords and mask-bit semantics as
+zuds/subtraction.py:25-226.  What differs is everything in between: the reference writes its inputs to a scratch
+directory, fork/execs ``hotpants`` on them (zuds/subtraction.py:162) and reads the products back; here the images
+are uploaded ONCE, every step runs on tensors resident in HBM (``subtract_on_device``: mask OR / boolean, rms from
+weight, background estimates, the subtraction itself, the bit-17 flag), and the products come back ONCE to be
+written as FITS.  No Postgres records, no archive copy (out of scope).
 """
 from __future__ import annotations
 
@@ -15,12 +17,15 @@ from pathlib import Path
 
 import numpy as np
 
-from . import fitsio
+from . import fitsio, params as P
 from .image import CalibratableImageBase, FITSImage, MaskImageBase
+from .synth import BAD_SUM, BIG_RMS, BKG_VAL
 
-__all__ = ['sub_name', 'Subtraction', 'SingleEpochSubtraction', 'MultiEpochSubtraction']
+__all__ = ['sub_name', 'subtract_on_device', 'Subtraction', 'SingleEpochSubtraction', 'MultiEpochSubtraction']
 
 APER_KEY = 'APCOR4'           # zuds/constants.py
+HOTPANTS_BIT = 17             # zuds/subtraction.py:170-176
+SENTINEL = np.float32(1e-30)  # what hotpants writes into masked difference pixels (-fi default)
 
 
 def sub_name(frame, template):
@@ -32,6 +37,87 @@ def sub_name(frame, template):
     outdir = os.path.dirname(frame)
     subp = '_'.join([newp, refp])
     return os.path.join(outdir, 'sub.%s.fits' % subp)
+
+
+# ------------------------------------------------------------------------------------------ device path
+
+class DeviceProducts:
+    """What ``subtract_on_device`` leaves in HBM: ``diff``, ``noise`` (float32), ``mask`` (int32: refmask | scimask |
+    bit 17 where hotpants masked the difference), ``boolean`` (uint8, the -imi image); plus ``command`` (the hotpants
+    command line zuds would have run), ``args`` (it parsed) and ``result`` (per-region QA, kernel table, stamps)."""
+
+
+def subtract_on_device(ctx, sci, ref, sci_rms, ref_rms, sci_mask, ref_mask, seeing, nreg_side=3, hotpants_kws=None,
+                       names=None, stream=None):
+    """The arithmetic of ``Subtraction.from_images`` on torch CUDA tensors, nothing returning to the host in between.
+
+    zuds/subtraction.py:135 (mask OR), zuds/mask.py:42-72 (boolean), zuds/hotpants.py:65-73 (background levels ->
+    -il/-tl), :75-93 (command line), zuds/subtraction.py:162 (hotpants), :167-177 (bit 17).  ``names``: the file
+    names that go into the command line (and so into the DIFFCMD keyword); placeholders when None."""
+    hotpants_kws = hotpants_kws or {}
+    ny, nx = sci.shape
+    badpix, boolean = ctx.mask_combine(sci_mask, ref_mask, BAD_SUM, stream=stream)
+    scibkg, scistd = ctx.background_estimate(sci, sci_mask)
+    refbkg, refstd = ctx.background_estimate(ref, ref_mask)
+    il, tl = scibkg - 10 * scistd, refbkg - 10 * refstd
+    n = names or {}
+    command = P.hotpants_command(n.get('sci', 'sci.fits'), n.get('ref', 'ref.fits'), n.get('out', 'sub.fits'),
+                                 n.get('sci_rms', 'sci.rms.fits'), n.get('ref_rms', 'ref.rms.fits'), n.get('bpm', 'sub.mask.bpm.fits'),
+                                 seeing, nx, ny, il, tl, nreg_side=nreg_side, hotpants_kws=hotpants_kws)
+    args = P.parse_hotpants_args(command.split()[1:])
+    args.params.nx, args.params.ny = nx, ny
+    res = ctx.subtract(args.params, sci, ref, sci_rms, ref_rms, boolean, None, want_mask=False, stream=stream)
+    ctx.mask_flag_sentinel(badpix, res.diff, SENTINEL, 2 ** HOTPANTS_BIT, stream=stream)
+    out = DeviceProducts()
+    out.diff, out.noise, out.mask, out.boolean = res.diff, res.noise, badpix, boolean
+    out.command, out.args, out.result = command, args, res
+    return out
+
+
+class _Scratch:
+    """Per-call private directory, removed on exit whatever happens (zuds/subtraction.py:68,224)."""
+
+    def __init__(self, tmpdir):
+        self.path = Path(tmpdir) / uuid.uuid4().hex
+
+    def __enter__(self):
+        self.path.mkdir(exist_ok=True, parents=True)
+        return self
+
+    def __exit__(self, *exc):
+        shutil.rmtree(self.path, ignore_errors=True)
+        return False
+
+    def adopt(self, image, need_noise_map):
+        """A private copy of ``image`` and its companions, reloaded from the copies: nothing another process does to
+        the originals while this subtraction runs can reach it (zuds/subtraction.py:68-99)."""
+        files = [image.local_path, image.mask_image.local_path]
+        maps = [getattr(image, a) for a in ('_rmsimg', '_weightimg') if hasattr(image, a)]
+        if need_noise_map and not maps:
+            raise ValueError('Science image must have a weight map or rms map defined prior to subtraction.')
+        files += [m.local_path for m in maps]
+        for f in files:
+            shutil.copy(f, self.path)
+        mine = CalibratableImageBase.from_file(os.path.join(self.path, image.basename), load_others=False)
+        mine.mask_image = MaskImageBase.from_file(os.path.join(self.path, image.mask_image.basename))
+        for attr in ('_rmsimg', '_weightimg'):
+            if hasattr(image, attr):
+                setattr(mine, attr, FITSImage.from_file(os.path.join(self.path, getattr(image, attr).basename)))
+        return mine
+
+
+def _noise_map_on_device(ctx, image, data_dev, up):
+    """``image.rms_image`` as a device tensor + the file name zuds would have given it: the rms map itself when the
+    image has one, else 1/sqrt(weight) with BIG_RMS on bad / near-saturated pixels (zuds/image.py:179-190)."""
+    name = image.local_path.replace('.fits', '.rms.fits')
+    if hasattr(image, '_rmsimg'):
+        return up(np.asarray(image._rmsimg.data, np.float32)), image._rmsimg.local_path
+    if not hasattr(image, '_weightimg'):
+        raise ValueError("image %s has neither an rms map nor a weight map" % image.basename)
+    _, own_bad = ctx.mask_combine(up(np.asarray(image.mask_image.data)), None, BAD_SUM, want_or=False)
+    rms = ctx.rms_from_weight(up(np.asarray(image._weightimg.data, np.float32)), bad=own_bad, data=data_dev,
+                              saturate=image.header.get('SATURATE'), big_rms=BIG_RMS)
+    return rms, name
 
 
 class Subtraction(CalibratableImageBase):
@@ -48,114 +134,100 @@ class Subtraction(CalibratableImageBase):
 
     @classmethod
     def from_images(cls, sci, ref, data_product=False, tmpdir='/tmp', **kwargs):
-        from .hotpants import prepare_hotpants, run_hotpants
+        import torch
+        from . import hotpants
 
-        subtract_new_back = kwargs.get('subtract_back', True)
+        subtract_back = kwargs.get('subtract_back', True)
         nreg_side = kwargs.get('nreg_side', 3)
         hotpants_kws = kwargs.get('hotpants_kws', {})
+        if data_product:
+            raise NotImplementedError("archive() (HTTP/tape copy, zuds/archive.py) is outside this path")
+        if 'SEEING' not in sci.header:
+            raise KeyError("SEEING (FWHM in pixels) must be in the science header; zuds.seeing.estimate_seeing "
+                           "queries external catalogues and is outside this path")
 
-        directory = Path(tmpdir) / uuid.uuid4().hex
-        directory.mkdir(exist_ok=True, parents=True)
-        try:
-            # copy the inputs into the directory and reload them: transactional isolation (:68-99)
-            shutil.copy(sci.local_path, directory)
-            shutil.copy(sci.mask_image.local_path, directory)
-            if hasattr(sci, '_rmsimg'):
-                shutil.copy(sci.rms_image.local_path, directory)
-            elif hasattr(sci, '_weightimg'):
-                shutil.copy(sci.weight_image.local_path, directory)
-            else:
-                raise ValueError('Science image must have a weight map or '
-                                 'rms map defined prior to subtraction.')
-            shutil.copy(ref.local_path, directory)
-            shutil.copy(ref.mask_image.local_path, directory)
-            shutil.copy(ref.weight_image.local_path, directory)
+        ctx = hotpants._context(cls.device)
+        dev = torch.device('cuda', cls.device)
 
-            sciname = os.path.join(directory, sci.basename)
-            scimaskn = os.path.join(directory, sci.mask_image.basename)
-            refname = os.path.join(directory, ref.basename)
-            refmaskn = os.path.join(directory, ref.mask_image.basename)
+        def up(a):
+            a = np.ascontiguousarray(a)
+            if a.dtype == np.bool_:
+                a = a.view(np.uint8)
+            elif a.dtype == np.uint16:
+                a = a.astype(np.int32)
+            elif a.dtype.kind == 'f' and a.dtype != np.float32:
+                a = a.astype(np.float32)
+            elif a.dtype.kind in 'iu' and a.dtype.name not in ('uint8', 'int16', 'int32'):
+                a = a.astype(np.int32)
+            return torch.from_numpy(a).to(dev)
 
-            transact_sci = CalibratableImageBase.from_file(sciname)
-            transact_scimask = MaskImageBase.from_file(scimaskn)
-            transact_ref = CalibratableImageBase.from_file(refname)
-            transact_refmask = MaskImageBase.from_file(refmaskn)
-            transact_sci.mask_image = transact_scimask
-            transact_ref.mask_image = transact_refmask
+        with _Scratch(tmpdir) as ws:
+            my_sci = ws.adopt(sci, need_noise_map=True)
+            my_ref = ws.adopt(ref, need_noise_map=False)
+            aligned = my_ref.aligned_to(my_sci, tmpdir=tmpdir)          # SWarp in the reference (:109)
+            aligned.parent_image = my_ref
+            outname = sub_name(my_sci.local_path, my_ref.local_path)
 
-            outname = sub_name(transact_sci.local_path, transact_ref.local_path)
-            outmask = outname.replace('.fits', '.mask.fits')
+            # SExtractor background subtraction of the science image (zuds/hotpants.py:31-40), a hook upstream of the path
+            target = my_sci
+            if subtract_back:
+                if hotpants.background_subtractor is None:
+                    raise NotImplementedError(
+                        "subtract_back=True needs SExtractor's background map, which is upstream of the subtraction "
+                        "path: set zuds_pipeline_b200.hotpants.background_subtractor or pass subtract_back=False")
+                bkg = hotpants.background_subtractor(my_sci)
+                target = FITSImage(np.asarray(my_sci.data, np.float32) - np.asarray(bkg, np.float32) + np.float32(BKG_VAL),
+                                   my_sci.header.copy(), my_sci.basename.replace('.fits', '.bkgsub.fits'))
+                target.map_to_local_file(os.path.join(ws.path, target.basename))
 
-            # the reference resamples with SWarp here (:109); aligned inputs pass through
-            remapped_ref = transact_ref.aligned_to(transact_sci, tmpdir=tmpdir)
-            remapped_refmask = remapped_ref.mask_image
-            remapped_ref.parent_image = transact_ref
+            # one upload, every step on the device, one download
+            d_sci, d_ref = up(np.asarray(target.data, np.float32)), up(np.asarray(aligned.data, np.float32))
+            d_scimask, d_refmask = up(np.asarray(sci.mask_image.data)), up(np.asarray(aligned.mask_image.data))
+            d_scirms, scirms_name = _noise_map_on_device(ctx, my_sci, d_sci, up)
+            d_refrms, refrms_name = _noise_map_on_device(ctx, getattr(aligned, 'parent_image', None) or aligned, d_ref, up)
+            bpm_name = outname.replace('.fits', '.mask.bpm.fits')
+            names = {'sci': target.local_path, 'ref': aligned.local_path, 'out': outname, 'sci_rms': scirms_name,
+                     'ref_rms': refrms_name, 'bpm': os.path.join(ws.path, os.path.basename(bpm_name))}
+            prod = subtract_on_device(ctx, d_sci, d_ref, d_scirms, d_refrms, d_scimask, d_refmask, sci.header['SEEING'],
+                                      nreg_side=nreg_side, hotpants_kws=hotpants_kws, names=names)
+            torch.cuda.synchronize(dev)
+            result = prod.result
+            result.diff, result.noise, result.mask = prod.diff.cpu().numpy(), prod.noise.cpu().numpy(), None
+            submask_data = prod.mask.cpu().numpy()
 
-            submask = MaskImageBase()
-            submask.basename = os.path.basename(outmask)
-            submask.map_to_local_file(outmask)
-            badpix = np.asarray(remapped_refmask.data).astype(np.int32) | np.asarray(sci.mask_image.data).astype(np.int32)
-            submask.header = sci.mask_image.header.copy()
+            # the three products, written where hotpants would have written them, then published next to the science image
+            hotpants.write_outputs(prod.args, my_sci.header, result, argv0='hotpants')
+            submask = MaskImageBase(submask_data, sci.mask_image.header.copy(), os.path.basename(outname.replace('.fits', '.mask.fits')))
             submask.header_comments = dict(sci.mask_image.header_comments)
-            submask.data = badpix
+            submask.header['BIT%d' % HOTPANTS_BIT] = HOTPANTS_BIT
+            submask.header_comments['BIT%d' % HOTPANTS_BIT] = 'MASKED BY HOTPANTS (1e-30) / DG'
+            submask.map_to_local_file(outname.replace('.fits', '.mask.fits'))
             submask.save()
-            submask.boolean.map_to_local_file(directory / submask.boolean.basename)
-            submask.boolean.save()
+            final_out = os.path.join(os.path.dirname(sci.local_path), os.path.basename(outname))
+            for suffix in ('.fits', '.rms.fits', '.mask.fits'):
+                shutil.copy(outname.replace('.fits', suffix), final_out.replace('.fits', suffix))
 
-            command = prepare_hotpants(transact_sci, remapped_ref, outname, submask.boolean, directory,
-                                       tmpdir=tmpdir, nreg_side=nreg_side,
-                                       subtract_new_back=subtract_new_back, hotpants_kws=hotpants_kws)
-
-            final_dir = os.path.dirname(sci.local_path)
-            final_out = os.path.join(final_dir, os.path.basename(outname))
-            product_map = {
-                outname: final_out,
-                outname.replace('.fits', '.rms.fits'): final_out.replace('.fits', '.rms.fits'),
-                outname.replace('.fits', '.mask.fits'): final_out.replace('.fits', '.mask.fits')
-            }
-
-            # run HOTPANTS (in process, on the GPU) -- zuds/subtraction.py:162
-            result = run_hotpants(command, device=cls.device)
-
-            # bit 17 where hotpants masked the difference (:167-177)
-            sd = result.diff
-            hotbad = np.zeros_like(submask.data, dtype=int)
-            hotbad[sd == np.float32(1e-30)] = 2 ** 17
-            submask.data = np.asarray(submask.data) | hotbad
-            submask.header['BIT17'] = 17
-            submask.header_comments['BIT17'] = 'MASKED BY HOTPANTS (1e-30) / DG'
-            submask.save()
-
-            for f in product_map:
-                shutil.copy(f, product_map[f])
-
-            sub = cls.from_file(final_out, load_others=False)
-            finalsubmask = MaskImageBase.from_file(final_out.replace('.fits', '.mask.fits'))
-            sub._rmsimg = FITSImage.from_file(final_out.replace('.fits', '.rms.fits'))
-
-            for key in ('FIELD', 'CCDID', 'QID', 'FID'):
-                v = sci.header.get(key)
-                if v is not None:
-                    sub.header[key] = v
-                    finalsubmask.header[key] = v
-            sub.mask_image = finalsubmask
-            finalsubmask.parent_image = sub
-            sub.reference_image = ref
-            sub.target_image = sci
-            sub.header['SEEING'] = sci.header['SEEING']
-            if 'SEEING' in sci.header_comments:
-                sub.header_comments['SEEING'] = sci.header_comments['SEEING']
-            if issubclass(cls, SingleEpochSubtraction) and 'MAGZP' in sci.header:
-                sub.header['MAGZP'] = sci.header['MAGZP']
-                if APER_KEY in sci.header:
-                    sub.header[APER_KEY] = sci.header[APER_KEY]
-            sub.last_result = result
-            sub.save()
-            sub.mask_image.save()
-            if data_product:
-                raise NotImplementedError("archive() (HTTP/tape copy, zuds/archive.py) is outside this path")
-        finally:
-            shutil.rmtree(directory, ignore_errors=True)
+        sub = cls.from_file(final_out, load_others=False)
+        sub.mask_image = MaskImageBase.from_file(final_out.replace('.fits', '.mask.fits'))
+        sub.mask_image.parent_image = sub
+        sub._rmsimg = FITSImage.from_file(final_out.replace('.fits', '.rms.fits'))
+        for key in ('FIELD', 'CCDID', 'QID', 'FID'):                    # zuds/subtraction.py:193-201
+            v = sci.header.get(key)
+            if v is not None:
+                sub.header[key] = v
+                sub.mask_image.header[key] = v
+        sub.reference_image, sub.target_image = ref, sci
+        sub.header['SEEING'] = sci.header['SEEING']
+        if 'SEEING' in sci.header_comments:
+            sub.header_comments['SEEING'] = sci.header_comments['SEEING']
+        if issubclass(cls, SingleEpochSubtraction) and 'MAGZP' in sci.header:
+            sub.header['MAGZP'] = sci.header['MAGZP']
+            if APER_KEY in sci.header:
+                sub.header[APER_KEY] = sci.header[APER_KEY]
+        sub.last_result = result
+        sub.last_command = prod.command
+        sub.save()
+        sub.mask_image.save()
         return sub
 
     def save(self):
@@ -178,5 +250,11 @@ class SingleEpochSubtraction(Subtraction):
 
 
 class MultiEpochSubtraction(Subtraction):
-    """zuds/subtraction.py:261-319.  The reference builds these by SWarp-coadding single-epoch
-    subtractions; only the pairwise ``from_images`` inherited above is on this path."""
+    """zuds/subtraction.py:261-319.  The reference builds these by SWarp-coadding single-epoch subtractions
+    (:283-319); that coadd is not built here, and a pairwise ``from_images`` under this name
+    would pose as it, so the class refuses."""
+
+    @classmethod
+    def from_images(cls, *a, **kw):
+        raise NotImplementedError("MultiEpochSubtraction is a SWarp coadd of single-epoch subtractions in the reference "
+                                  "(zuds/subtraction.py:283-319); only SingleEpochSubtraction.from_images is built")
