@@ -244,6 +244,27 @@ int zb_weight_from_rms(zb_ctx *ctx, const float *rms, const uint8_t *bad, const 
                        long long n, float *weight, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Alignment of the reference onto the science grid, the step before the subtraction: what zuds runs
+ * SWarp for, once per image and once per mask (zuds/swarp.py:107-204, zuds/fitsfile.py:290-314, configuration
+ * astromatic/makecoadd/default.swarp: LANCZOS3, no oversampling, fixed flux scale, one input image).
+ *   zb_align_lanczos3  out[j*dnx+i] = 6x6 Lanczos-3 interpolation of `src` at the position of target pixel (i, j),
+ *                      weights of each axis normalised to unit sum, times |det CD_dst| / |det CD_src|;
+ *                      value 0 and weight 0 where the 6x6 footprint leaves the source frame, weight 1 elsewhere
+ *                      (out_weight may be NULL).  Device pointers.
+ *   zb_align_mask      nearest-neighbour transport of an integer mask (flag bits cannot be interpolated), with
+ *                      `nodata_bit` OR-ed in where the image's weight is 0 (zuds/mask.py:26-33: 2**16).
+ * World coordinates: gnomonic (TAN) projection, FITS conventions (CRPIX 1-based, CRVAL / CD in degrees).  Distortion
+ * polynomials (TPV PVi_j) are not built. */
+typedef struct zb_wcs {
+    double crpix1, crpix2, crval1, crval2;
+    double cd11, cd12, cd21, cd22;
+} zb_wcs;
+int zb_align_lanczos3(zb_ctx *ctx, const float *src, int snx, int sny, const zb_wcs *src_wcs,
+                      int dnx, int dny, const zb_wcs *dst_wcs, float *out, float *out_weight, void *stream);
+int zb_align_mask(zb_ctx *ctx, const void *src_mask, int dtype, int snx, int sny, const zb_wcs *src_wcs,
+                  int dnx, int dny, const zb_wcs *dst_wcs, int32_t *out, int nodata_bit, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Row-tile sessions: ONE oversized frame fitted by a single region (nreg_x == nreg_y == 1,
  * BASELINE.json configs[4]) split over `world` GPUs by image rows, one process (rank) per GPU.
  * The reference has no counterpart (one single-threaded process per frame, zuds/mpi.py:36-64);

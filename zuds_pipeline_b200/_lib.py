@@ -30,7 +30,9 @@ EXPORTS = ("zb_version", "zb_params_default", "zb_params_check", "zb_sizes_of", 
            "zb_tile_convolve", "zb_tile_finish",
            # wrapper pre/post steps (zuds.utils.quick_background_estimate, mask OR / boolean / bit 17, rms <-> weight)
            "zb_background_estimate", "zb_background_estimate_host",
-           "zb_mask_combine", "zb_mask_flag_sentinel", "zb_rms_from_weight", "zb_weight_from_rms")
+           "zb_mask_combine", "zb_mask_flag_sentinel", "zb_rms_from_weight", "zb_weight_from_rms",
+           # alignment of the reference onto the science grid (what zuds runs SWarp for)
+           "zb_align_lanczos3", "zb_align_mask")
 
 
 class ZbError(RuntimeError):
@@ -77,6 +79,9 @@ def load():
     lib.zb_mask_flag_sentinel.argtypes = [vp, vp, vp, C.c_longlong, C.c_float, C.c_int, vp]
     lib.zb_rms_from_weight.argtypes = [vp, vp, vp, vp, C.c_float, C.c_float, C.c_longlong, vp, vp]
     lib.zb_weight_from_rms.argtypes = [vp, vp, vp, vp, C.c_float, C.c_longlong, vp, vp]
+    wp = C.POINTER(P.ZbWcs)
+    lib.zb_align_lanczos3.argtypes = [vp, vp, C.c_int, C.c_int, wp, C.c_int, C.c_int, wp, vp, vp, vp]
+    lib.zb_align_mask.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, wp, C.c_int, C.c_int, wp, vp, C.c_int, vp]
     _lib = lib
     return lib
 
@@ -246,6 +251,32 @@ class Context:
                                          None if bad is None else self._dev(bad, (torch.uint8, torch.bool)),
                                          None if (data is None or saturate is None) else self._dev(data, (torch.float32,)), sat,
                                          rms.numel(), self._dev(out), self._stream(rms, stream))
+        if rc != 0:
+            self._err(rc)
+        return out
+
+    def align_lanczos3(self, src, src_wcs, dst_shape, dst_wcs, stream=None):
+        """Resample ``src`` (float32 CUDA tensor) onto the grid ``dst_shape`` = (ny, nx) with world coordinates
+        ``dst_wcs``: (aligned image, weight map).  What zuds runs SWarp for (zuds/swarp.py:157-204)."""
+        import torch
+        sny, snx = src.shape
+        dny, dnx = dst_shape
+        out = torch.empty((dny, dnx), dtype=torch.float32, device=src.device)
+        wgt = torch.empty((dny, dnx), dtype=torch.float32, device=src.device)
+        rc = self.lib.zb_align_lanczos3(self.h, self._dev(src, (torch.float32,)), snx, sny, C.byref(src_wcs), dnx, dny, C.byref(dst_wcs),
+                                        self._dev(out), self._dev(wgt), self._stream(src, stream))
+        if rc != 0:
+            self._err(rc)
+        return out, wgt
+
+    def align_mask(self, mask, src_wcs, dst_shape, dst_wcs, nodata_bit=2 ** 16, stream=None):
+        """Nearest-neighbour transport of an integer mask onto the target grid, ``nodata_bit`` where the image's weight is 0."""
+        import torch
+        sny, snx = mask.shape
+        dny, dnx = dst_shape
+        out = torch.empty((dny, dnx), dtype=torch.int32, device=mask.device)
+        rc = self.lib.zb_align_mask(self.h, self._dev(mask), self._mask_dt(mask), snx, sny, C.byref(src_wcs), dnx, dny, C.byref(dst_wcs),
+                                    self._dev(out), int(nodata_bit), self._stream(mask, stream))
         if rc != 0:
             self._err(rc)
         return out

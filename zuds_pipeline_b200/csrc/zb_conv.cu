@@ -31,8 +31,7 @@
 struct __align__(16) KTap { double k; float k2; float pad; };   // one kernel tap as k_convolve reads it (one LDS.128)
 __global__ void __launch_bounds__(256)
 k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, const double *__restrict__ kvec,
-               double *__restrict__ kern, double *__restrict__ kernr, int fwp,
-               double *__restrict__ ksum_out, double *__restrict__ kaks, int nbx_max, int nby_max,
+               int fwp, double *__restrict__ ksum_out, double *__restrict__ kaks, int nbx_max, int nby_max,
                KTap *__restrict__ ktap, int kstride)
 {
     __shared__ double coef[MK_NB][ZB_MAX_BASIS];
@@ -83,12 +82,8 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
         for (int lb = 0; lb < MK_NB; lb++) {
             int b = b0 + lb;
             if (b > nb) continue;
-            kern[((long long)r * per_region + b) * fw2 + t] = acc[lb];
-            // the same kernel reversed (image coordinates ascending) with rows padded to fwp: what k_convolve
-            // copies straight into shared memory
-            kernr[((long long)r * per_region + b) * fw * fwp + roff] = acc[lb];
-            // k_convolve's operand, same reversed / row-padded layout: K for the image term (double) and K^2
-            // for the variance term (float), one 16-byte record per tap
+            // k_convolve's operand: the kernel reversed (image coordinates ascending), rows padded to fwp, K for the
+            // image term (double) and K^2 for the variance term (float) in one 16-byte record per tap
             KTap kt; kt.k = acc[lb]; kt.k2 = (float)(acc[lb] * acc[lb]); kt.pad = 0.f;
             ktap[((long long)r * per_region + b) * kstride + roff] = kt;
         }
@@ -97,7 +92,6 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
         const int b = b0 + lb, npad = fwp - fw;
         if (b > nb || npad <= 0) continue;
         for (int t = tid; t < fw * npad; t += blockDim.x) {
-            kernr[((long long)r * per_region + b) * fw * fwp + (t / npad) * fwp + fw + t % npad] = 0.0;
             KTap z; z.k = 0.0; z.k2 = 0.f; z.pad = 0.f;
             ktap[((long long)r * per_region + b) * kstride + (t / npad) * fwp + fw + t % npad] = z;
         }
@@ -107,16 +101,16 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
     // aks = sum |K| in spatial_convolve's tap order (image coordinates ascending = kernel index descending,
     // alard.c:1289-1304): one dependent chain per block, needed only where a bad pixel lies under a footprint
     if (tid < MK_NB && b0 + tid < nb) {
-        const double *o = kern + ((long long)r * per_region + b0 + tid) * fw2;
+        const KTap *o = ktap + ((long long)r * per_region + b0 + tid) * kstride;        // reversed copy, ascending = that order
         double s = 0.0;
-        for (int i = fw2 - 1; i >= 0; i--) s = __dadd_rn(s, fabs(o[i]));
+        for (int dy = 0; dy < fw; dy++) for (int dx = 0; dx < fw; dx++) s = __dadd_rn(s, fabs(o[dy * fwp + dx].k));
         kaks[(long long)r * per_region + b0 + tid] = s;
     }
-    if (b0 <= nb && nb < b0 + MK_NB) {                             // this CTA made the centre kernel
+    if (b0 <= nb && nb < b0 + MK_NB) {                             // this CTA made the centre kernel: KSUM, kernel index ascending (main.c:1136)
         if (tid == MK_NB) {
-            const double *o = kern + ((long long)r * per_region + nb) * fw2;
+            const KTap *o = ktap + ((long long)r * per_region + nb) * kstride;
             double s = 0.0;
-            for (int i = 0; i < fw2; i++) s = __dadd_rn(s, o[i]);
+            for (int dy = fw - 1; dy >= 0; dy--) for (int dx = fw - 1; dx >= 0; dx--) s = __dadd_rn(s, o[dy * fwp + dx].k);
             ksum_out[(size_t)r * 4] = s;
         }
     }
@@ -249,8 +243,8 @@ typedef unsigned long long u64;
 #define CONV_EPI_WARPS 3
 #define CONV_MAX_KS 4
 #define CONV_MAX_NB 64
-#define CONV_REGS_LIGHT 128          // setmaxnreg of warp group 0
-#define CONV_REGS_FMA 184           // setmaxnreg of the FMA warp groups: 128*LIGHT + 256*FMA <= 65536
+#define CONV_REGS_LIGHT 120          // setmaxnreg of warp group 0
+#define CONV_REGS_FMA 192           // setmaxnreg of the FMA warp groups: 128*LIGHT + 256*FMA = 64512 = 384 * 168, what the launch allocates
 
 struct ConvGeom {
     int NBX, NBY, KS, GX, GY;       // blocks per tile, kernel-row split, thread grid per block
@@ -348,14 +342,47 @@ __device__ __forceinline__ bool conv_tile(const ZbDev *D, const ConvGeom &G, int
 
 // One chunk of CH kernel columns for the TY output rows of a thread.  VAR64 (-convvar): the variance is convolved
 // with K itself, in double.
+template <int TX, int CH, typename AV>
+__device__ __forceinline__ void conv_window(const double *__restrict__ trd, const float *__restrict__ trv, int ch,
+                                            double (&wd)[TX + CH - 1], AV (&wv)[TX + CH - 1])
+{
+#pragma unroll
+    for (int q = 0; q < TX + CH - 1; q++) { wd[q] = trd[ch + q]; wv[q] = (AV)trv[ch + q]; }
+}
+
 template <int TX, int TY, int CH, bool EXACT, bool VAR64, typename AV>
-__device__ __forceinline__ void conv_chunk(const double *__restrict__ trd, const float *__restrict__ trv, const KTap *__restrict__ Kb,
+__device__ __forceinline__ void conv_chunk(const double (&wd)[TX + CH - 1], const AV (&wv)[TX + CH - 1], const KTap *__restrict__ Kb,
                                            int ch, int s, int fw, int fwp, int dy0, int dy1, bool steady,
                                            double (&aq)[TY][TX], AV (&av)[TY][TX])
 {
-    double wd[TX + CH - 1]; AV wv[TX + CH - 1];
+    if (steady && (EXACT || ch + CH <= fw)) {
+        // every output row of the thread takes this tile row: the taps of output row oy+1 are requested before the
+        // multiply-adds of output row oy are issued, so their shared-memory latency hides behind ~100 instructions
+        double2 kk[2][CH];                                       // one LDS.128 per tap: (K, [K^2 float | pad])
+        const double2 *k0 = reinterpret_cast<const double2 *>(Kb + s * fwp + ch);
 #pragma unroll
-    for (int q = 0; q < TX + CH - 1; q++) { wd[q] = trd[ch + q]; wv[q] = (AV)trv[ch + q]; }
+        for (int dx = 0; dx < CH; dx++) kk[0][dx] = k0[dx];
+#pragma unroll
+        for (int oy = 0; oy < TY; oy++) {
+            if (oy + 1 < TY) {
+                const double2 *kn = reinterpret_cast<const double2 *>(Kb + (s - oy - 1) * fwp + ch);
+#pragma unroll
+                for (int dx = 0; dx < CH; dx++) kk[(oy + 1) & 1][dx] = kn[dx];
+            }
+#pragma unroll
+            for (int dx = 0; dx < CH; dx++) {
+                const double k = kk[oy & 1][dx].x;
+                const float k2 = __int_as_float(__double2loint(kk[oy & 1][dx].y));
+#pragma unroll
+                for (int t = 0; t < TX; t++) {
+                    aq[oy][t] = fma(wd[t + dx], k, aq[oy][t]);
+                    if (VAR64) av[oy][t] = (AV)fma((double)wv[t + dx], k, (double)av[oy][t]);
+                    else av[oy][t] = (AV)fmaf((float)wv[t + dx], k2, (float)av[oy][t]);
+                }
+            }
+        }
+        return;
+    }
 #pragma unroll
     for (int oy = 0; oy < TY; oy++) {
         const int dy = s - oy;
@@ -396,8 +423,8 @@ template <int TX, int TY, int CH, bool EXACT, bool VAR64>
 __global__ void __launch_bounds__(CONV_THREADS, 1)
 k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ CUtensorMap tm_rms,
            const ZbDev *__restrict__ D, const PixCtx P, const __grid_constant__ ConvGeom G,
-           const double *__restrict__ sols, const KTap *__restrict__ ktap, const double *__restrict__ kernr,
-           const double *__restrict__ ksums, const double *__restrict__ kaks,
+           const double *__restrict__ sols, const KTap *__restrict__ ktap,
+           const double *__restrict__ ksums, const double *__restrict__ kaks, int *__restrict__ tile_counter,
            float *__restrict__ rdiff, float *__restrict__ rnoise, int32_t *__restrict__ omask,
            float *__restrict__ diff, float *__restrict__ noise, int32_t *__restrict__ out_mask)
 {
@@ -416,6 +443,7 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
     double *s_pre = (double *)(dyn + G.o_pre);                 // [NB][fw][fwp+1]  prefix sums of |K| along each kernel row (uks/aks test)
     unsigned short *resm = (unsigned short *)(dyn + G.o_resm); // [OH][OW]  mask bits the convolution contributes (alard.c:1312-1332)
     unsigned *s_rowbad = (unsigned *)(bars + 8);               // [2 parity][16]  bit per tile row: the row holds a bad pixel
+    int *s_tile = (int *)(s_rowbad + 32);                      // [4] ring of tile indices handed out by the producer; -1: no more work
     uint64_t *raw_full = bars, *raw_empty = bars + 1, *k_full = bars + 2, *k_empty = bars + 3, *res_full = bars + 4, *res_empty = bars + 5;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -444,16 +472,28 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
 #endif
         if (warp == 0) {
             // ================================================================== producer
+            // Tiles are handed out dynamically (an atomic counter): their cost varies with what lies under them
+            // (flagged pixels, partial blocks at region edges), and a static split left SMs idle for 17 % of the launch.
+            // The tile of iteration `it` travels to the other roles in s_tile[it & 3], published by the raw_full barrier.
             int it = 0;
-            for (int t = blockIdx.x; t < G.n_tiles; t += gridDim.x) {
+            for (;;) {
+                int t = 0;
+                if (lane == 0) t = atomicAdd(tile_counter, 1);
+                t = __shfl_sync(0xffffffffu, t, 0);
                 TileRef T; ZbRegion R;
-                if (!conv_tile(D, G, t, T, R)) continue;
-                const unsigned par = it & 1; it++;
+                if (t < G.n_tiles && !conv_tile(D, G, t, T, R)) continue;
+                const unsigned par = it & 1;
+                if (lane == 0) mbar_wait(raw_empty, par ^ 1);
+                __syncwarp();
+                if (t >= G.n_tiles) {                                              // no more work: tell the other roles and leave
+                    if (lane == 0) { s_tile[it & 3] = -1; mbar_arrive(raw_full); }
+                    break;
+                }
+                if (lane == 0) s_tile[it & 3] = t;
+                it++;
                 // tile origin, image coordinates; the box starts at the 16-byte aligned column at or before it: a tensor
                 // load whose innermost start is not 16-byte aligned raises an illegal-instruction trap (tools/tma_probe.cu)
                 const int gx0 = (R.bx0 + T.bx0 * B) & ~3, gy0 = R.by0 + T.by0 * B;
-                if (lane == 0) mbar_wait(raw_empty, par ^ 1);
-                __syncwarp();
                 if (G.use_tma) {
                     if (lane == 0) {
                         const unsigned bytes = (unsigned)(WR * TH * 4) * (G.have_rms ? 2u : 1u);
@@ -494,7 +534,7 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
             // A warp owns output rows ew, ew+3, ...; lanes own columns.  The global loads of a row (other image, its
             // rms, its user mask: up to EPC column chunks of 32) are issued one row ahead of their use.
             const int ew = warp - 1;
-            constexpr int EPC = 3;                                                 // column chunks handled per pass over a row
+            constexpr int EPC = 2;                                                 // column chunks handled per pass over a row
             const bool conv_t = D->conv_template != 0;
             const bool do_scale = conv_t ? (D->p.phot_normalize == 't') : (D->p.phot_normalize == 'i');
             const bool bg_const = D->p.bg_order == 0;
@@ -502,11 +542,13 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
             const double o_qq = __fmul_rn(P.o_quad, P.o_quad);
             const float fill_noise = D->p.fill_val_noise;
             const bool mask_out = D->p.kf_spread_mask2 >= 0;
-            int it = 0;
-            for (int t = blockIdx.x; t < G.n_tiles; t += gridDim.x) {
+            for (int it = 0;; it++) {
+                const unsigned par = it & 1;
+                mbar_wait(res_full, par);
+                const int t = s_tile[it & 3];
+                if (t < 0) break;
                 TileRef T; ZbRegion R;
-                if (!conv_tile(D, G, t, T, R)) continue;
-                const unsigned par = it & 1; it++;
+                conv_tile(D, G, t, T, R);
                 const int r = T.r;
                 const int i00 = T.bx0 * B + hw, j00 = T.by0 * B + hw;              // first output pixel, region coordinates
                 const double *sol = sols + (long long)r * (D->sz.n_comp_total + 1);
@@ -517,7 +559,6 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                 const int own_y0 = R.ry0 - R.by0 - j00, own_y1 = R.own_y1 - R.by0 - j00;
                 const long long gout = (long long)(R.by0 + j00) * nxi + (R.bx0 + i00);
                 const long long lout = R.off + (long long)j00 * R.rpx + i00;
-                mbar_wait(res_full, par);
                 const int any = s_any[par];
                 const int nchunk = (ox_lim + 31) >> 5;
                 for (int c0 = 0; c0 < nchunk; c0 += EPC) {
@@ -597,16 +638,22 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
         const int dy0 = (g * fw) / KS, dy1 = ((g + 1) * fw) / KS;                  // this band's kernel rows (ascending image rows)
         const bool have_rms = G.have_rms != 0;
         const double c_qq = __fmul_rn(P.c_quad, P.c_quad);
-        int it = 0;
-        for (int t = blockIdx.x; t < G.n_tiles; t += gridDim.x) {
+        for (int it = 0;; it++) {
+            const unsigned par = it & 1;
+            mbar_wait(raw_full, par);
+            const int t = s_tile[it & 3];
+            if (t < 0) {                                                           // pass the end of work on to the epilogue warps
+                mbar_wait(res_empty, par ^ 1);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(res_full);
+                break;
+            }
             TileRef T; ZbRegion R;
-            if (!conv_tile(D, G, t, T, R)) continue;
-            const unsigned par = it & 1; it++;
+            conv_tile(D, G, t, T, R);
             const int gx0 = R.bx0 + T.bx0 * B, gy0 = R.by0 + T.by0 * B;
             const int sh = gx0 & 3;                                                // the raw box starts at the aligned column gx0 - sh
             unsigned *Rany = rmask + (size_t)(par * 2 + 0) * TH * NW, *Rbad = rmask + (size_t)(par * 2 + 1) * TH * NW;
             unsigned *Vany = vmask + (size_t)(par * 2 + 0) * OH * NW, *Vbad = vmask + (size_t)(par * 2 + 1) * OH * NW;
-            mbar_wait(raw_full, par);
             if (ft == 0) s_any[par] = 0;
             if (ft < 16) s_rowbad[par * 16 + ft] = 0u;
             named_bar_sync(1, CONV_FMA_THREADS);                                   // every FMA warp is done with the previous comp tile
@@ -623,16 +670,16 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                     float *cv = compv + (size_t)ty * Wv;
                     for (int txb = 0; txb < Wt; txb += 32) {
                         const int tx = txb + lane;
-                        int cm = 0;
+                        bool bad = false;                                          // every value flag carries INPUT_ISBAD (makeInputMask)
                         if (tx < Wt) {
                             const float pv = ri[tx], rv = rr[tx];
                             cd[tx] = (double)pv;
                             cv[tx] = __fmul_rn(rv, rv);
-                            if (yin && tx < x_in) cm = value_bits(pv, fill, P.cU, P.cL);
+                            bad = yin && tx < x_in && (pv == fill || pv >= P.cU || pv <= P.cL);
                         }
-                        const unsigned ba = __ballot_sync(0xffffffffu, cm != 0), bb = __ballot_sync(0xffffffffu, (cm & ZB_FLAG_INPUT_ISBAD) != 0);
-                        if (lane == 0) { Rany[ty * NW + (txb >> 5)] = ba; Rbad[ty * NW + (txb >> 5)] = bb; if (bb) atomicOr(&s_rowbad[par * 16 + (ty >> 5)], 1u << (ty & 31)); }
-                        anyf |= (ba != 0u);
+                        const unsigned bb = __ballot_sync(0xffffffffu, bad);
+                        if (lane == 0) { Rany[ty * NW + (txb >> 5)] = bb; Rbad[ty * NW + (txb >> 5)] = bb; if (bb) atomicOr(&s_rowbad[par * 16 + (ty >> 5)], 1u << (ty & 31)); }
+                        anyf |= (bb != 0u);
                     }
                 }
             } else {
@@ -662,6 +709,18 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
             if (lane == 0 && anyf) s_any[par] = 1;
             __syncwarp();
             if (lane == 0) mbar_arrive(raw_empty);                                 // the producer may fetch the next tile's boxes
+            // prefix sums of |K| along every kernel row of the tile's blocks, one thread per row (the uks/aks test below);
+            // the kernels were requested when the previous tile's multiply ended and have normally landed by now
+            mbar_wait(k_full, par);
+            // (taken by the threads of the last band first: band 0 also owns the mask work after the multiply)
+            for (int k = CONV_FMA_THREADS - 1 - ft; k < NB * fw; k += CONV_FMA_THREADS) {
+                const int b = k / fw, dy = k - b * fw;
+                const KTap *kr = kbuf + (size_t)b * G.kstride + dy * fwp;
+                double *pr = s_pre + (size_t)k * (fwp + 1);
+                double acc = 0.0;
+                pr[0] = 0.0;
+                for (int dx = 0; dx < fw; dx++) { acc += fabs(kr[dx].k); pr[dx + 1] = acc; }
+            }
             named_bar_sync(1, CONV_FMA_THREADS);
             if (s_any[par]) {                                                      // OR of the flag rows over each footprint's 2hw+1 rows
                 for (int k = ft; k < 2 * OH * NW; k += CONV_FMA_THREADS) {
@@ -681,23 +740,10 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
             for (int oy = 0; oy < TY; oy++)
 #pragma unroll
                 for (int tt = 0; tt < TX; tt++) { aq[oy][tt] = 0.0; av[oy][tt] = (AV)0; }
-            mbar_wait(k_full, par);
             const bool any_bad = (s_rowbad[par * 16 + 0] | s_rowbad[par * 16 + 1] | s_rowbad[par * 16 + 2] | s_rowbad[par * 16 + 3] |
                                   s_rowbad[par * 16 + 4] | s_rowbad[par * 16 + 5] | s_rowbad[par * 16 + 6] | s_rowbad[par * 16 + 7] |
                                   s_rowbad[par * 16 + 8] | s_rowbad[par * 16 + 9] | s_rowbad[par * 16 + 10] | s_rowbad[par * 16 + 11] |
                                   s_rowbad[par * 16 + 12] | s_rowbad[par * 16 + 13]) != 0u;
-            if (any_bad) {
-                // prefix sums of |K| along every kernel row of the tile's blocks: one thread per row
-                for (int k = ft; k < NB * fw; k += CONV_FMA_THREADS) {
-                    const int b = k / fw, dy = k - b * fw;
-                    const KTap *kr = kbuf + (size_t)b * G.kstride + dy * fwp;
-                    double *pr = s_pre + (size_t)k * (fwp + 1);
-                    double acc = 0.0;
-                    pr[0] = 0.0;
-                    for (int dx = 0; dx < fw; dx++) { acc += fabs(kr[dx].k); pr[dx + 1] = acc; }
-                }
-                named_bar_sync(1, CONV_FMA_THREADS);
-            }
             if (active) {
                 const KTap *Kb = kbuf + (size_t)lb * G.kstride;
                 const double *tbd = compd + (size_t)y0 * Wc + x0;
@@ -706,7 +752,11 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                     const double *trd = tbd + (size_t)s * Wc;
                     const float *trv = tbv + (size_t)s * Wv;
                     const bool steady = (s - (TY - 1) >= dy0) && (s < dy1);        // every output row of the thread sees this tile row
-                    for (int ch = 0; ch < fwp; ch += CH) conv_chunk<TX, TY, CH, EXACT, VAR64, AV>(trd, trv, Kb, ch, s, fw, fwp, dy0, dy1, steady, aq, av);
+                    for (int ch = 0; ch < fwp; ch += CH) {
+                        double wd[TX + CH - 1]; AV wv[TX + CH - 1];
+                        conv_window<TX, CH, AV>(trd, trv, ch, wd, wv);
+                        conv_chunk<TX, TY, CH, EXACT, VAR64, AV>(wd, wv, Kb, ch, s, fw, fwp, dy0, dy1, steady, aq, av);
+                    }
                 }
             }
             // ---- what the convolution contributes to the mask (alard.c:1304-1332), by the band-0 owner of each output: the
@@ -870,7 +920,7 @@ static size_t conv_plan(ConvGeom &G, int B, int fw, int TX, int TY, int CH, bool
     G.o_vmask = up128(o);   o = G.o_vmask + (size_t)4 * OH * G.NW * 4;
     G.o_pre = up128(o);     o = G.o_pre + (size_t)NB * fw * (G.fwp + 1) * 8;
     G.o_resm = up128(o);    o = G.o_resm + (size_t)OH * OW * 2;
-    G.o_misc = up128(o);    o = G.o_misc + 64 + 2 * 16 * 4;
+    G.o_misc = up128(o);    o = G.o_misc + 64 + 2 * 16 * 4 + 4 * 4;
     return o;
 }
 
@@ -903,34 +953,44 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
     else if (B <= 24) { TXr = 7; TYr = 3; CHr = 7; }
     else              { TXr = 8; TYr = 3; CHr = 8; }
     const bool have_rms = P.conv_rms != nullptr;
-    ConvGeom G; memset(&G, 0, sizeof G);
-    G.GX = (B + TXr - 1) / TXr; G.GY = (B + TYr - 1) / TYr;
-    const int tpb = G.GX * G.GY;
-    if (tpb > CONV_FMA_THREADS) { snprintf(ctx->err, sizeof ctx->err, "kc_step %d too large for the convolution kernel", B); return ZB_ERR_UNSUPPORTED; }
-    // Tile shape: NBX x NBY blocks and KS bands of kernel rows.  256 FMA threads, one band per 256/KS of them.
-    // Score = busy lanes x a mild preference for little halo; limited by shared memory and the TMA box (256).
-    {
-        static int env_nbx = -1, env_nby = 0, env_ks = 0;
-        if (env_nbx < 0) { const char *e = getenv("ZB_CONV_TILE"); env_nbx = 0; if (e) sscanf(e, "%dx%dx%d", &env_nbx, &env_nby, &env_ks); }
-        double best = -1; ConvGeom Gb = G;
-        for (int ks = 1; ks <= CONV_MAX_KS; ks *= 2)
-            for (int by = 1; by <= 8; by++)
-                for (int bx = 1; bx <= 8; bx++) {
-                    if (env_nbx > 0 && !(bx == env_nbx && by == env_nby && ks == env_ks)) continue;
-                    const int nb = bx * by;
-                    if (nb * tpb > CONV_FMA_THREADS / ks || nb > CONV_MAX_NB || ks > fw) continue;
-                    if (p.convolve_variance && ks > 1) continue;               // -convvar: the double variance sum is not split into bands
-                    ConvGeom T = G; T.NBX = bx; T.NBY = by; T.KS = ks;
-                    const size_t sm = conv_plan(T, B, fw, TXr, TYr, CHr, have_rms);
-                    if (sm > (size_t)ZB_SMEM_CONV || T.WR > 256 || T.TH > 256 || T.TH > 16 * 32 - 64) continue;
-                    const double util = (double)(nb * tpb * ks) / CONV_FMA_THREADS;
-                    const double halo = (double)(nb * B * B) / ((double)T.Wt * T.TH);
-                    const int lo = fw / ks, hi = (fw + ks - 1) / ks;               // band imbalance: the tile waits for the widest band
-                    const double score = util * ((double)lo / hi * 0.5 + 0.5) * (0.85 + 0.15 * halo) * (1.0 - 0.02 * (ks - 1));
-                    if (score > best) { best = score; Gb = T; }
-                }
-        if (best < 0) { snprintf(ctx->err, sizeof ctx->err, "no convolution tile fits shared memory (kc_step %d, kernel width %d)", B, fw); return ZB_ERR_UNSUPPORTED; }
-        G = Gb;
+    // The tile shape depends on the configuration only (kernel block size and width, rms map or not, -convvar):
+    // searched once per context and configuration, not per pair (the search costs the host ~2 ms)
+    ConvGeom G;
+    const int gkey[6] = {B, fw, have_rms ? 1 : 0, p.convolve_variance ? 1 : 0, TXr, TYr};
+    if (ctx->conv_geom_bytes == (int)sizeof(ConvGeom) && memcmp(ctx->conv_geom_key, gkey, sizeof gkey) == 0) {
+        memcpy(&G, ctx->conv_geom, sizeof G);
+    } else {
+        memset(&G, 0, sizeof G);
+        G.GX = (B + TXr - 1) / TXr; G.GY = (B + TYr - 1) / TYr;
+        const int tpb = G.GX * G.GY;
+        if (tpb > CONV_FMA_THREADS) { snprintf(ctx->err, sizeof ctx->err, "kc_step %d too large for the convolution kernel", B); return ZB_ERR_UNSUPPORTED; }
+        // Tile shape: NBX x NBY blocks and KS bands of kernel rows.  256 FMA threads, one band per 256/KS of them.
+        // Score = busy lanes x a mild preference for little halo; limited by shared memory and the TMA box (256).
+        {
+            static int env_nbx = -1, env_nby = 0, env_ks = 0;
+            if (env_nbx < 0) { const char *e = getenv("ZB_CONV_TILE"); env_nbx = 0; if (e) sscanf(e, "%dx%dx%d", &env_nbx, &env_nby, &env_ks); }
+            double best = -1; ConvGeom Gb = G;
+            for (int ks = 1; ks <= CONV_MAX_KS; ks *= 2)
+                for (int by = 1; by <= 8; by++)
+                    for (int bx = 1; bx <= 8; bx++) {
+                        if (env_nbx > 0 && !(bx == env_nbx && by == env_nby && ks == env_ks)) continue;
+                        const int nb = bx * by;
+                        if (nb * tpb > CONV_FMA_THREADS / ks || nb > CONV_MAX_NB || ks > fw) continue;
+                        if (p.convolve_variance && ks > 1) continue;               // -convvar: the double variance sum is not split into bands
+                        ConvGeom T = G; T.NBX = bx; T.NBY = by; T.KS = ks;
+                        const size_t sm = conv_plan(T, B, fw, TXr, TYr, CHr, have_rms);
+                        if (sm > (size_t)ZB_SMEM_CONV || T.WR > 256 || T.TH > 256 || T.TH > 16 * 32 - 64) continue;
+                        const double util = (double)(nb * tpb * ks) / CONV_FMA_THREADS;
+                        const double halo = (double)(nb * B * B) / ((double)T.Wt * T.TH);
+                        const int lo = fw / ks, hi = (fw + ks - 1) / ks;               // band imbalance: the tile waits for the widest band
+                        const double score = util * ((double)lo / hi * 0.5 + 0.5) * (0.85 + 0.15 * halo) * (1.0 - 0.02 * (ks - 1));
+                        if (score > best) { best = score; Gb = T; }
+                    }
+            if (best < 0) { snprintf(ctx->err, sizeof ctx->err, "no convolution tile fits shared memory (kc_step %d, kernel width %d)", B, fw); return ZB_ERR_UNSUPPORTED; }
+            G = Gb;
+        }
+        static_assert(sizeof(ConvGeom) <= sizeof(ctx->conv_geom), "conv_geom cache too small");
+        memcpy(ctx->conv_geom, &G, sizeof G); memcpy(ctx->conv_geom_key, gkey, sizeof gkey); ctx->conv_geom_bytes = (int)sizeof(ConvGeom);
     }
     const size_t smem = conv_plan(G, B, fw, TXr, TYr, CHr, have_rms);
     G.nbx_max = nbx_max; G.nby_max = nby_max;
@@ -951,7 +1011,7 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
     G.n_tiles = nt;
 
     dim3 gk((nbx_max * nby_max + 1 + MK_NB - 1) / MK_NB + 1, nR);
-    k_make_kernels<<<gk, 256, 0, st>>>(ctx->d_dev, ctx->d_sol, ctx->d_kvec, ctx->d_kern, ctx->d_kernr, G.fwp, ctx->d_kstat, ctx->d_kaks, nbx_max, nby_max,
+    k_make_kernels<<<gk, 256, 0, st>>>(ctx->d_dev, ctx->d_sol, ctx->d_kvec, G.fwp, ctx->d_kstat, ctx->d_kaks, nbx_max, nby_max,
                                        (KTap *)ctx->d_ktap, G.kstride); ZB_DBG("k_make_kernels");
     CUtensorMap tm_img, tm_rms;
     memset(&tm_img, 0, sizeof tm_img); memset(&tm_rms, 0, sizeof tm_rms);
@@ -961,12 +1021,13 @@ int zb_launch_convolve(zb_ctx *ctx, const float *sci, const float *ref, const fl
                 (!have_rms || conv_tensor_map(&tm_rms, P.conv_rms, p.nx, p.ny, G.WR, G.TH));
     int grid = ctx->n_sm > 0 ? ctx->n_sm : 148;
     if (grid > nt) grid = nt;
+    zb_zero_small(ctx, ctx->d_tilectr, sizeof(int), st);
     cudaEventRecord(ctx->ev[10], st);          // k_convolve alone: the kernel bench.py's roofline is quoted on
     if (grid > 0) {
 #define ZB_CONV_LAUNCH2(TX_, TY_, CH_, EX_, V64_) do { \
         cudaFuncSetAttribute(k_convolve<TX_, TY_, CH_, EX_, V64_>, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_CONV); \
-        k_convolve<TX_, TY_, CH_, EX_, V64_><<<grid, CONV_THREADS, smem, st>>>(tm_img, tm_rms, ctx->d_dev, P, G, ctx->d_sol, (const KTap *)ctx->d_ktap, ctx->d_kernr, \
-            ctx->d_kstat, ctx->d_kaks, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask); } while (0)
+        k_convolve<TX_, TY_, CH_, EX_, V64_><<<grid, CONV_THREADS, smem, st>>>(tm_img, tm_rms, ctx->d_dev, P, G, ctx->d_sol, (const KTap *)ctx->d_ktap, \
+            ctx->d_kstat, ctx->d_kaks, ctx->d_tilectr, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, diff, noise, out_mask); } while (0)
 #define ZB_CONV_LAUNCH(TX_, TY_, CH_) do { \
         if (p.convolve_variance) ZB_CONV_LAUNCH2(TX_, TY_, CH_, false, true); \
         else if ((fw % CH_) == 0) ZB_CONV_LAUNCH2(TX_, TY_, CH_, true, false); \

@@ -257,8 +257,8 @@ static void free_workspace(zb_ctx *ctx) {
                       (void **)&ctx->d_ran, (void **)&ctx->d_fx, (void **)&ctx->d_fy, (void **)&ctx->d_kvec, (void **)&ctx->d_ren,
                       (void **)&ctx->d_cells, (void **)&ctx->d_stamps, (void **)&ctx->d_vec, (void **)&ctx->d_kref, (void **)&ctx->d_gram,
                       (void **)&ctx->d_rhs, (void **)&ctx->d_wxy, (void **)&ctx->d_mat, (void **)&ctx->d_sol, (void **)&ctx->d_vv,
-                      (void **)&ctx->d_indx, (void **)&ctx->d_fit, (void **)&ctx->d_jobs, (void **)&ctx->d_njobs, (void **)&ctx->d_kern, (void **)&ctx->d_kernr, (void **)&ctx->d_kaks,
-                      (void **)&ctx->d_ktap,
+                      (void **)&ctx->d_indx, (void **)&ctx->d_fit, (void **)&ctx->d_jobs, (void **)&ctx->d_njobs, (void **)&ctx->d_kaks,
+                      (void **)&ctx->d_ktap, (void **)&ctx->d_tilectr,
                       (void **)&ctx->d_kstat, (void **)&ctx->d_stats, (void **)&ctx->d_qa, (void **)&ctx->d_qpart};
     for (size_t i = 0; i < sizeof dptrs / sizeof dptrs[0]; i++) { if (*dptrs[i]) cudaFree(*dptrs[i]); *dptrs[i] = NULL; }
     void **hptrs[] = {(void **)&ctx->h_dev, (void **)&ctx->h_cells, (void **)&ctx->h_stamps, (void **)&ctx->h_fit, (void **)&ctx->h_njobs, (void **)&ctx->h_stats};
@@ -402,9 +402,8 @@ int zb_configure(zb_ctx *ctx, const zb_params *p) {
     DMALLOC(ctx->d_jobs, ns * sizeof(int));
     DMALLOC(ctx->d_njobs, sizeof(int));   HMALLOC(ctx->h_njobs, (4 + ns) * sizeof(int));     // [0]: job count; [4..]: job list scratch (zb_tile.cu)
     const int B = sz.kc_step, nbx = (sz.max_rpix_x + B - 1) / B, nby = (sz.max_rpix_y + B - 1) / B;
-    DMALLOC(ctx->d_kern, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * fw * fw * sizeof(double));
-    DMALLOC(ctx->d_kernr, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * fw * (fw + 8) * sizeof(double));
     DMALLOC(ctx->d_kaks, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * sizeof(double));
+    DMALLOC(ctx->d_tilectr, 16);
     DMALLOC(ctx->d_ktap, (size_t)sz.n_regions * ((size_t)nbx * nby + 1) * fw * (fw + 8) * 16);
     DMALLOC(ctx->d_kstat, (size_t)sz.n_regions * 4 * sizeof(double));
     const size_t stat_bytes = (size_t)sz.n_regions * ((size_t)sz.n_comp_total + 512) * sizeof(double) + ns * 8;

@@ -139,10 +139,10 @@ struct zb_ctx {
     double  *d_vv; int *d_indx;  // LU scratch
     ZbFit   *d_fit, *h_fit;
     int     *d_jobs, *d_njobs, *h_njobs;
-    double  *d_kern;             // [region][blocks+1][fw*fw]  K per convolution block (+ the region-centre kernel)
-    double  *d_kernr;            // the same kernels reversed, rows padded to the convolution's chunk width (what k_convolve stages)
     double  *d_kaks;             // [region][blocks+1]  sum |K| per block in the reference's tap order
     void    *d_ktap;             // [region][blocks+1][fw*fwp] 16-byte taps (K double, K^2 float), reversed, rows padded: k_convolve's operand
+    int     *d_tilectr;          // tile counter of k_convolve's dynamic schedule
+    unsigned char conv_geom[512]; int conv_geom_key[6]; int conv_geom_bytes;   // cached tile shape of k_convolve (zb_conv.cu)
     int      n_sm;               // multiprocessors of the device (grid of the persistent kernels)
     double  *d_kstat;            // per-region: ksum, aks
     double  *d_stats;  double *h_stats;   // region QA scratch

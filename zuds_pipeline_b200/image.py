@@ -108,13 +108,52 @@ class FITSImage:
         ny, nx = np.shape(value)
         self.header["NAXIS1"], self.header["NAXIS2"] = int(nx), int(ny)
 
-    def aligned_to(self, other, tmpdir='/tmp'):
-        """zuds/fitsfile.py:290-314 resamples with SWarp (an external binary upstream of this path).
-        Images already on the target grid are returned as they are; anything else is refused."""
-        if np.shape(self.data) != np.shape(other.data):
-            raise NotImplementedError("SWarp alignment is upstream of the subtraction path: supply a "
-                                      "reference already resampled to the science grid")
-        return self
+    def aligned_to(self, other, tmpdir='/tmp', device=None):
+        """This image on the pixel grid of ``other`` (zuds/fitsfile.py:290-314, where SWarp does it: LANCZOS3
+        resampling of the image, zuds/swarp.py:107-204; the mask follows with bit 16 where nothing was covered,
+        zuds/mask.py:26-33).  Runs on the GPU (``zb_align_lanczos3`` / ``zb_align_mask``) from the two headers' world
+        coordinates (TAN projection).  Images without world coordinates that already share the grid pass through."""
+        from . import params as P
+        have_wcs = all(k in self.header and k in other.header for k in ("CRPIX1", "CRPIX2", "CRVAL1", "CRVAL2"))
+        if not have_wcs:
+            if np.shape(self.data) != np.shape(other.data):
+                raise ValueError("images %s and %s have different shapes and no world coordinates to align them with"
+                                 % (self.basename, other.basename))
+            return self
+        src_wcs, dst_wcs = P.ZbWcs.from_header(self.header), P.ZbWcs.from_header(other.header)
+        same = np.shape(self.data) == np.shape(other.data) and all(
+            getattr(src_wcs, f) == getattr(dst_wcs, f) for f, _ in P.ZbWcs._fields_)
+        if same:
+            return self                                       # already on the target grid: SWarp would copy it
+        import torch
+        from . import hotpants
+        ctx = hotpants._context(hotpants.DEVICE if device is None else device)
+        dev = torch.device("cuda", ctx.device)
+        dst_shape = tuple(np.shape(other.data))
+        out, wgt = ctx.align_lanczos3(torch.from_numpy(np.ascontiguousarray(self.data, np.float32)).to(dev), src_wcs, dst_shape, dst_wcs)
+        new = type(self)() if not isinstance(self, MaskImageBase) else FITSImage()
+        new.header = self.header.copy()
+        for k in ("CRPIX1", "CRPIX2", "CRVAL1", "CRVAL2", "CD1_1", "CD1_2", "CD2_1", "CD2_2", "CDELT1", "CDELT2",
+                  "PC1_1", "PC1_2", "PC2_1", "PC2_2", "CTYPE1", "CTYPE2"):
+            new.header.remove(k)
+            if k in other.header:
+                new.header[k] = other.header[k]
+        new.header_comments = dict(self.header_comments)
+        new.data = out.cpu().numpy()
+        new.basename = self.basename.replace(".fits", "_aligned_to_%s.remap.fits" % other.basename[:-5])
+        new.parent_image = self
+        new.weight_map = wgt.cpu().numpy()
+        mask = getattr(self, "mask_image", None)
+        if mask is not None:
+            m = np.ascontiguousarray(mask.data)
+            if m.dtype.name not in ("uint8", "int16", "int32"):
+                m = m.astype(np.int32)
+            md = ctx.align_mask(torch.from_numpy(m).to(dev), src_wcs, dst_shape, dst_wcs, nodata_bit=2 ** 16)
+            nm = MaskImageBase(md.cpu().numpy(), mask.header.copy(), mask.basename.replace(".fits", "_aligned_to_%s.remap.fits" % other.basename[:-5]))
+            nm.header_comments = dict(mask.header_comments)
+            nm.parent_image = mask
+            new.mask_image = nm
+        return new
 
 
 class MaskImageBase(FITSImage):

@@ -60,6 +60,33 @@ class ZbStampInfo(C.Structure):
                 ("mode", C.c_double), ("fwhm", C.c_double), ("chi2", C.c_double)]
 
 
+class ZbWcs(C.Structure):
+    """zb_wcs (include/zb200.h): TAN projection, FITS conventions."""
+    _fields_ = [(n, C.c_double) for n in ("crpix1", "crpix2", "crval1", "crval2", "cd11", "cd12", "cd21", "cd22")]
+
+    @classmethod
+    def from_header(cls, hdr):
+        """CRPIXi / CRVALi and the CD matrix (CDi_j, or CDELTi with an optional PCi_j) of a FITS header; raises KeyError
+        without them and NotImplementedError for anything but a plain gnomonic projection."""
+        for ax in ("1", "2"):
+            ctype = str(hdr.get("CTYPE" + ax, ""))
+            if ctype and not (ctype.endswith("TAN") or ctype.endswith("TPV")):
+                raise NotImplementedError("projection %r: only gnomonic (TAN) world coordinates are built" % ctype)
+        if any(k.startswith("PV1_") or k.startswith("PV2_") for k in hdr.keys()):
+            raise NotImplementedError("TPV distortion polynomials (PVi_j) are not built")
+        w = cls()
+        w.crpix1, w.crpix2 = float(hdr["CRPIX1"]), float(hdr["CRPIX2"])
+        w.crval1, w.crval2 = float(hdr["CRVAL1"]), float(hdr["CRVAL2"])
+        if "CD1_1" in hdr:
+            w.cd11, w.cd12 = float(hdr["CD1_1"]), float(hdr.get("CD1_2", 0.0))
+            w.cd21, w.cd22 = float(hdr.get("CD2_1", 0.0)), float(hdr["CD2_2"])
+        else:
+            d1, d2 = float(hdr["CDELT1"]), float(hdr["CDELT2"])
+            w.cd11, w.cd12 = d1 * float(hdr.get("PC1_1", 1.0)), d1 * float(hdr.get("PC1_2", 0.0))
+            w.cd21, w.cd22 = d2 * float(hdr.get("PC2_1", 0.0)), d2 * float(hdr.get("PC2_2", 1.0))
+        return w
+
+
 class ZbHostPair(C.Structure):
     """zb_host_pair (include/zb200.h): the host pointers of one pair for zb_subtract_batch."""
     _fields_ = [("sci", C.c_void_p), ("ref", C.c_void_p), ("sci_rms", C.c_void_p), ("ref_rms", C.c_void_p),
