@@ -449,7 +449,32 @@ def bench_pairs(args):
                 b.synchronize()
                 best = max(best, hb.numel() / (a.elapsed_time(b) * 1e-3) / 1e9)
             link[name] = round(best, 2)
-        del hb, db
+        # every rank at once, both directions at once, in the proportions of the e2e leg (one pair's inputs up, one
+        # pair's products down, nothing computed): what the host side (DRAM, PCIe roots) gives N GPUs together
+        barrier()
+        in_b = min(hb.numel(), sum(t.numel() * t.element_size() for t in pin_in[0] if t is not None))
+        out_b = sum(t.numel() * t.element_size() for t in pin_out[0][0])
+        sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
+        hb2 = torch.empty(out_b, dtype=torch.uint8).pin_memory()
+        db2 = torch.empty(out_b, dtype=torch.uint8, device="cuda")
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a.record()
+        sa.wait_event(a)
+        sb.wait_event(a)
+        nrep = 8
+        for _ in range(nrep):
+            with torch.cuda.stream(sa):
+                db[:in_b].copy_(hb[:in_b], non_blocking=True)
+            with torch.cuda.stream(sb):
+                hb2.copy_(db2, non_blocking=True)
+        torch.cuda.current_stream().wait_stream(sa)
+        torch.cuda.current_stream().wait_stream(sb)
+        b.record()
+        b.synchronize()
+        link["copy_only_replay_pairs_per_s_per_gpu"] = round(nrep / (a.elapsed_time(b) * 1e-3), 1)
+        link["copy_only_replay_gbs_both_ways_per_gpu"] = round(nrep * (in_b + out_b) / (a.elapsed_time(b) * 1e-3) / 1e9, 2)
+        del hb, db, hb2, db2
     except RuntimeError as e:          # pinned allocation refused: report, do not fail the bench
         link = {"error": str(e)[:120]}
     # ---- the convolution kernel alone, one context, nothing else on the GPU (roofline)
@@ -488,8 +513,10 @@ def bench_pairs(args):
         "e2e": {"value": pairs_total / host_s, "unit": UNIT, "h2d_bytes_per_step": in_bytes * B, "d2h_bytes_per_step": out_bytes * B,
                 "call": "zb_subtract_batch (one call per context and step: H2D of pair n+1 and D2H of pair n-1 overlap pair n), out_mask NULL as in the zuds command line (no -omi)",
                 "host_link": link,
-                "link_bound_pairs_per_s": (round(min(link["h2d_gbs"] * 1e9 / in_bytes, link["d2h_gbs"] * 1e9 / out_bytes), 1)
-                                           if "h2d_gbs" in link else None)},
+                "link_bound_pairs_per_s": (round(world * min(link["h2d_gbs"] * 1e9 / in_bytes, link["d2h_gbs"] * 1e9 / out_bytes), 1)
+                                           if "h2d_gbs" in link else None),
+                "copy_only_replay_pairs_per_s": (round(world * link["copy_only_replay_pairs_per_s_per_gpu"], 1)
+                                                 if "copy_only_replay_pairs_per_s_per_gpu" in link else None)},
         "gpu_launches": launches,
         "clocks": clk,
         "roofline": {"kernel": "k_convolve", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",

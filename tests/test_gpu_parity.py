@@ -167,6 +167,44 @@ def test_nan_and_constant_inputs(oracle, gpu_ctx):
     assert (np.abs(o.diff.astype(np.float64) - g.diff)[fin] / sig[fin]).max() <= TOL_SIGMA
 
 
+QA_FIELDS = ("dmean", "dsige", "dsig", "dmeano", "dsigeo", "dsigo", "x2norm", "nx2norm", "nscalo")
+
+
+def _qa_numbers(g):
+    return [[float(getattr(g.regions[i], f)) for f in QA_FIELDS] for i in range(g.sizes.n_regions)]
+
+
+@pytest.mark.parametrize("nan_pixels", [False, True])
+def test_region_statistics_routes_agree(nan_pixels, oracle, gpu_ctx, monkeypatch):
+    """The region statistics by their three routes: clip iterations >= 2 on the shell lists (default), full passes
+    only (ZB_QA_NOTAIL=1), and getStampStats3 with its histogram phase (ZB_QA_HIST=1).  The two full-pass routes add
+    the same terms in the same order: identical numbers; the shell route forms each iteration's sums as a
+    difference, so it may differ in the last bits.  All of them are the oracle's keywords."""
+    case = CS.SMALL[0]
+    pair = CS.make_pair(case)
+    if nan_pixels:                     # a NaN under a clean mask enters the OK-pixel runs: the shell lists must be given up
+        pair.sci[100:104, 200:203] = np.nan
+        pair.ref[300, 310] = np.inf
+    p = CS.params_of(case, pair)
+    ins = CS.inputs_of(case, pair)
+    o = H.run_oracle(oracle, p, *ins)
+    base = gpu_ctx.subtract_host(p, *ins)
+    monkeypatch.setenv("ZB_QA_NOTAIL", "1")
+    full = gpu_ctx.subtract_host(p, *ins)
+    monkeypatch.delenv("ZB_QA_NOTAIL")
+    monkeypatch.setenv("ZB_QA_HIST", "1")
+    hist = gpu_ctx.subtract_host(p, *ins)
+    monkeypatch.delenv("ZB_QA_HIST")
+    assert _qa_numbers(full) == _qa_numbers(hist)
+    for a, b in zip(_qa_numbers(base), _qa_numbers(full)):
+        for x, y in zip(a, b):
+            assert x == y or abs(x - y) <= 1e-10 * max(abs(x), abs(y)), (a, b)
+    for g in (base, full, hist):
+        assert np.array_equal(g.mask, o.mask)
+        bad = keywords_mismatch(region_keywords(g), region_keywords(o), exact=False)
+        assert not bad, bad
+
+
 @pytest.mark.parametrize("name", ["c1", "c1b", "c4"])
 def test_full_size_quadrant(name, oracle, gpu_ctx):
     """BASELINE.json configs[0]/[1] (and the zuds-actual variant) and configs[3] (hw 15, order 4,

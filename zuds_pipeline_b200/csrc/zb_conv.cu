@@ -68,6 +68,9 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
         coef[lb][i1] = c;
     }
     __syncthreads();
+    double ak[MK_NB];                                                      // this thread's share of sum |K| per block
+#pragma unroll
+    for (int lb = 0; lb < MK_NB; lb++) ak[lb] = 0.0;
     for (int t = tid; t < fw2; t += blockDim.x) {
         const int roff = (fw - 1 - t / fw) * fwp + (fw - 1 - t % fw);      // position in the reversed, row-padded copy
         double acc[MK_NB];
@@ -84,6 +87,7 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
             if (b > nb) continue;
             // k_convolve's operand: the kernel reversed (image coordinates ascending), rows padded to fwp, K for the
             // image term (double) and K^2 for the variance term (float) in one 16-byte record per tap
+            ak[lb] += fabs(acc[lb]);
             KTap kt; kt.k = acc[lb]; kt.k2 = (float)(acc[lb] * acc[lb]); kt.pad = 0.f;
             ktap[((long long)r * per_region + b) * kstride + roff] = kt;
         }
@@ -97,14 +101,21 @@ k_make_kernels(const ZbDev *__restrict__ D, const double *__restrict__ sols, con
         }
     }
 
+    // aks = sum |K| of every block: k_convolve decides uks/aks < kerFracMask from it with a 1e-9 margin and re-sums both
+    // in the reference's tap order when the ratio is that close to the threshold (conv_kernel_fraction_low), so any
+    // summation order does here: per-thread shares, warp shuffles, then the eight warps in order (deterministic)
+    __shared__ double ak_w[8][MK_NB];
+#pragma unroll
+    for (int lb = 0; lb < MK_NB; lb++) {
+        double v = ak[lb];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((tid & 31) == 0) ak_w[tid >> 5][lb] = v;
+    }
     __syncthreads();
-    // aks = sum |K| in spatial_convolve's tap order (image coordinates ascending = kernel index descending,
-    // alard.c:1289-1304): one dependent chain per block, needed only where a bad pixel lies under a footprint
     if (tid < MK_NB && b0 + tid < nb) {
-        const KTap *o = ktap + ((long long)r * per_region + b0 + tid) * kstride;        // reversed copy, ascending = that order
-        double s = 0.0;
-        for (int dy = 0; dy < fw; dy++) for (int dx = 0; dx < fw; dx++) s = __dadd_rn(s, fabs(o[dy * fwp + dx].k));
-        kaks[(long long)r * per_region + b0 + tid] = s;
+        double sum = 0.0;
+        for (int w = 0; w < 8; w++) sum += ak_w[w][tid];
+        kaks[(long long)r * per_region + b0 + tid] = sum;
     }
     if (b0 <= nb && nb < b0 + MK_NB) {                             // this CTA made the centre kernel: KSUM, kernel index ascending (main.c:1136)
         if (tid == MK_NB) {

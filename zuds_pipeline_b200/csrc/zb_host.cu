@@ -259,7 +259,8 @@ static void free_workspace(zb_ctx *ctx) {
                       (void **)&ctx->d_rhs, (void **)&ctx->d_wxy, (void **)&ctx->d_mat, (void **)&ctx->d_sol, (void **)&ctx->d_vv,
                       (void **)&ctx->d_indx, (void **)&ctx->d_fit, (void **)&ctx->d_jobs, (void **)&ctx->d_njobs, (void **)&ctx->d_kaks,
                       (void **)&ctx->d_ktap, (void **)&ctx->d_tilectr,
-                      (void **)&ctx->d_kstat, (void **)&ctx->d_stats, (void **)&ctx->d_qa, (void **)&ctx->d_qpart};
+                      (void **)&ctx->d_kstat, (void **)&ctx->d_stats, (void **)&ctx->d_qa, (void **)&ctx->d_qpart,
+                      (void **)&ctx->d_qshell, (void **)&ctx->d_qshell_n};
     for (size_t i = 0; i < sizeof dptrs / sizeof dptrs[0]; i++) { if (*dptrs[i]) cudaFree(*dptrs[i]); *dptrs[i] = NULL; }
     void **hptrs[] = {(void **)&ctx->h_dev, (void **)&ctx->h_cells, (void **)&ctx->h_stamps, (void **)&ctx->h_fit, (void **)&ctx->h_njobs, (void **)&ctx->h_stats};
     for (size_t i = 0; i < sizeof hptrs / sizeof hptrs[0]; i++) { if (*hptrs[i]) cudaFreeHost(*hptrs[i]); *hptrs[i] = NULL; }
@@ -411,6 +412,13 @@ int zb_configure(zb_ctx *ctx, const zb_params *p) {
     cudaMemsetAsync(ctx->d_stats, 0, stat_bytes, ctx->stream);
     DMALLOC(ctx->d_qa, (size_t)sz.n_regions * 4 * sizeof(ZbQaStat));
     DMALLOC(ctx->d_qpart, (size_t)sz.n_regions * 5 * ZB_QA_NBLK * sizeof(ZbQaPart));
+    {   // clip-shell lists (zb_stats.cu): one segment per warp of every k_qa_pass CTA and statistic
+        const int nblk = zb_qa_nblk(sz.n_regions);
+        const long long per_warp = ((long long)sz.max_rpix_x * sz.max_rpix_y + (long long)nblk * 8 - 1) / ((long long)nblk * 8);
+        ctx->qshell_cap = (int)(per_warp / ZB_QA_SHELL_DIV) + 32;
+        DMALLOC(ctx->d_qshell, (size_t)sz.n_regions * 4 * nblk * 8 * ctx->qshell_cap * sizeof(float));
+        DMALLOC(ctx->d_qshell_n, (size_t)sz.n_regions * 4 * nblk * 8 * sizeof(int));
+    }
     zb_copy_small(ctx, ctx->d_dev, H, sizeof(ZbDev), ctx->stream);
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
     if (e == cudaSuccess) e = cudaGetLastError();

@@ -87,9 +87,20 @@ struct ZbQaStat {
     double crit_mean[8], crit_istd[8];
     double mean, sd, bin1, binsize, samp_med;
     double sum, median, mode, fwhm, lfwhm;
+    // clip iterations >= 2 from the shell list (zb_stats.cu): sums over the first criterion's interval, and the
+    // float interval every later criterion must still contain for the list to hold all later rejections
+    double base_s1, base_s2;
+    int base_n, shell_bad;
+    float core_lo, core_hi;
     int bins[256];
 };
+#define ZB_QA_SHELL_DIV 8       // a warp's shell segment holds 1/8 of the pixels it reads in a pass
 struct ZbQaPart { double s1, s2; int n, pad; };
+// CTAs per region of a k_qa_pass launch: enough to put ~4 CTAs on every SM whatever the number of regions
+static inline int zb_qa_nblk(int n_regions) {
+    int nblk = n_regions >= 5 ? ZB_QA_NBLK_MIN : (4 * 148 + n_regions - 1) / n_regions;
+    return nblk < ZB_QA_NBLK_MIN ? ZB_QA_NBLK_MIN : (nblk > ZB_QA_NBLK ? ZB_QA_NBLK : nblk);
+}
 
 #define ZB_CUDA_OK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return zb_cuda_fail(ctx, e_, #call, __FILE__, __LINE__); } while (0)
 
@@ -148,6 +159,7 @@ struct zb_ctx {
     double  *d_stats;  double *h_stats;   // region QA scratch
     ZbQaStat *d_qa;              // [region][4]
     ZbQaPart *d_qpart;           // [region][5][ZB_QA_NBLK]  (4 stats + getNoiseStats3)
+    float *d_qshell; int *d_qshell_n; int qshell_cap;   // [region][4][ZB_QA_NBLK * 8 warps][cap] clip-shell values and their counts
     cudaEvent_t ev_sync;         // blocking-sync event (zb_stream_wait)
     void *d_bkg; double *h_bkg;  // background-estimate selection state (zb_bkg.cu)
     // staging for zb_subtract_host

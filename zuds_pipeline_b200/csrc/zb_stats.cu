@@ -1,8 +1,9 @@
 // zb_stats.cu — per-region QA numbers that hotpants writes as FITS keywords.
 //   k_final_sig / k_final_clip   alard.c:1027-1060 getFinalStampSig + main.c:1417-1435 (FSIGnn / FSCATnn)
-//   k_qa_sample / k_qa_pass / k_qa_decide
+//   k_qa_sample / k_qa_pass / k_qa_tail
 //                                main.c:1479-1554: getStampStats3 (functions.c:763-1035) on the difference
-//                                and noise images for GOOD and OK pixels, getNoiseStats3 (functions.c:719-761)
+//                                and noise images for GOOD and OK pixels, getNoiseStats3 (functions.c:719-761).
+//                                Two passes over the frame, then the remaining clip iterations on short lists.
 //   k_rescale_ok                 main.c:1557-1579 (-okn)
 //
 // The four getStampStats3 runs of a region read the same three arrays (difference, noise, mask),
@@ -110,10 +111,18 @@ __device__ static inline void qa_masks(int s, int &um, int &sm) {
     if (s < 2) { um = 0x0; sm = 0xffff; } else { um = 0xff; sm = ZB_FLAG_OUTPUT_ISBAD; }
 }
 
+__device__ static void qa_reset(ZbQaStat &Q, int s, int um, int sm) {
+    Q.phase = 0; Q.status = 0; Q.maxiter = 5; Q.umask = um; Q.smask = sm; Q.use_noise = s & 1;
+    Q.ncrit = 0; Q.cnt_prev = 0; Q.tries = 0; Q.imax = 0; Q.ticket = 0; Q.exact = 0;
+    Q.clo = Q.llo = -3.402823466e38f; Q.chi = Q.lhi = 3.402823466e38f;
+    Q.mean = Q.sd = Q.mode = Q.median = Q.fwhm = Q.lfwhm = Q.sum = 0;
+    Q.base_s1 = Q.base_s2 = 0; Q.base_n = 0; Q.shell_bad = 0; Q.core_lo = 1.f; Q.core_hi = -1.f;
+}
+
 // The first 100 accepted random samples (functions.c:811-833), accepted in attempt order.
 __global__ void __launch_bounds__(256)
 k_qa_sample(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const float *__restrict__ rnoise,
-            const int32_t *__restrict__ omask, ZbQaStat *__restrict__ qa, const double *__restrict__ ran, int n_ran)
+            const int32_t *__restrict__ omask, ZbQaStat *__restrict__ qa, const double *__restrict__ ran, int n_ran, int hist)
 {
     const int s = blockIdx.x, r = blockIdx.y, tid = threadIdx.x;
     const ZbRegion R = D->reg[r];
@@ -132,6 +141,13 @@ k_qa_sample(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const 
     __syncthreads();
     if (npts < 100) {
         if (tid == 0) { Q.phase = 2; Q.status = 4; Q.mean = Q.sd = Q.mode = Q.median = Q.fwhm = Q.lfwhm = Q.sum = 0; }
+        return;
+    }
+    if (!hist) {            // the sample only sizes the histogram (functions.c:811-838): nothing to draw without it
+        if (tid == 0) {
+            Q.npts_s = 0; Q.samp_med = Q.binsize = Q.bin1 = 0.;
+            qa_reset(Q, s, um, sm);
+        }
         return;
     }
     for (int base = 0; base < npts; base += 256) {
@@ -165,10 +181,7 @@ k_qa_sample(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const 
         Q.samp_med = work[(int)(0.5f * n)];
         Q.binsize = (work[(int)(0.9f * n)] - work[(int)(0.5f * n)]) / (float)100;
         Q.bin1 = work[(int)(0.5f * n)] - 128. * Q.binsize;
-        Q.phase = 0; Q.status = 0; Q.maxiter = 5; Q.umask = um; Q.smask = sm; Q.use_noise = s & 1;
-        Q.ncrit = 0; Q.cnt_prev = 0; Q.tries = 0; Q.imax = 0; Q.ticket = 0; Q.exact = 0;
-        Q.clo = Q.llo = -3.402823466e38f; Q.chi = Q.lhi = 3.402823466e38f;
-        Q.mean = Q.sd = Q.mode = Q.median = Q.fwhm = Q.lfwhm = Q.sum = 0;
+        qa_reset(Q, s, um, sm);
     }
 }
 
@@ -176,6 +189,7 @@ struct QaShared {
     int phase[4], ncrit[4], exact[4];
     float flo[4], fhi[4];
     double cm[4][8], ci[4][8], mean[4], isd[4], bin1[4], binsize[4], ibin[4];
+    float core_lo[4], core_hi[4];
     int bins[4][256];
     double ra[8], rb[8]; int rc[8];
 };
@@ -224,9 +238,9 @@ __device__ static bool qa_interval(double mean, double istd, float sig, float &l
 // The sequential decisions of sigma_clip (functions.c:1037-1107) and of the re-binning loop
 // (functions.c:879-1031) for one (region, stat); s == 4 finishes getNoiseStats3 on the first pass.
 // Runs in the last CTA of a pass to finish (see k_qa_pass).
-__device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *part /* [5][ZB_QA_NBLK] */, int nblk, double *q, int r, int s, int first, const int *bins)
+__device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *P /* this statistic's nblk partial sums */, int nblk, double *q, int r, int s, int first, const int *bins,
+                                 int pass, int hist)
 {
-    const ZbQaPart *P = part + s * ZB_QA_NBLK;          // this region's partial sums, staged in shared memory
     double s1 = 0, s2 = 0; long long n = 0;
     if (s == 4) {
         if (!first) return;
@@ -242,6 +256,8 @@ __device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *p
     const float sig = D->p.stat_sig;
     if (Q.phase == 0) {
         const int k = Q.ncrit;                          // passes done so far == iterations started
+        const int after = hist ? 1 : 2;                 // the histogram outputs reach no product (see zb_launch_region_stats)
+        if (pass == 1) { Q.base_s1 = s1; Q.base_s2 = s2; Q.base_n = ncnt; }       // sums over the first criterion's interval
         if (k == 0 && ncnt == 0) { Q.mean = 0; Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
         if (ncnt != Q.cnt_prev && k < Q.maxiter) {
             Q.cnt_prev = ncnt;
@@ -250,13 +266,17 @@ __device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *p
             if (ncnt > 1) { double sd = s2 - ncnt * Q.mean * Q.mean; Q.sd = sqrt(sd / (double)(ncnt - 1)); }
             else { Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
             Q.crit_mean[k] = Q.mean; Q.crit_istd[k] = 1. / Q.sd; Q.ncrit = k + 1;
+            if (k == 0) {                               // pixels outside this core go to the shell list in pass 1
+                const double w = 0.75 * (double)sig * Q.sd;
+                Q.core_lo = (float)(Q.mean - w); Q.core_hi = (float)(Q.mean + w);
+            }
             float lo, hi;
             if (!Q.exact && qa_interval(Q.mean, 1. / Q.sd, sig, lo, hi)) {
                 Q.llo = lo; Q.lhi = hi;
                 Q.clo = fmaxf(Q.clo, lo); Q.chi = fminf(Q.chi, hi);
             } else Q.exact = 1;
-            if (k + 1 >= Q.maxiter) Q.phase = 1;        // iter == maxiter ends the loop whatever the next count is
-        } else Q.phase = 1;
+            if (k + 1 >= Q.maxiter) Q.phase = after;    // iter == maxiter ends the loop whatever the next count is
+        } else Q.phase = after;
         return;
     }
     // histogram phase: this pass filled the bins with the current bin1/binsize
@@ -274,11 +294,15 @@ __device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *p
     if (Q.tries >= 5) { Q.status = 1; Q.phase = 2; }
 }
 
-template <int MINB, int ROT>
+// SHELL (the pass after the first criterion): every kept value outside the criterion's core interval is also
+// appended to the shell list of its (statistic, warp) — in pixel order, positions from warp ballots, so the
+// lists and every sum formed from them are deterministic.  k_qa_tail runs the remaining clip iterations on them.
+template <int MINB, int ROT, bool SHELL>
 __global__ void __launch_bounds__(256, MINB)
 k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const float *__restrict__ rnoise,
           int32_t *__restrict__ omask, int32_t *__restrict__ out_mask, ZbQaStat *qa,
-          ZbQaPart *part, double *__restrict__ q, int first, int use_div)
+          ZbQaPart *part, double *__restrict__ q, int first, int use_div, int pass, int hist,
+          float *__restrict__ shell, int *__restrict__ shell_n, int shell_cap)
 {
     __shared__ QaShared S;
     __shared__ int s_last;
@@ -291,12 +315,14 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
         for (int c = 0; c < 8; c++) { S.cm[tid][c] = Q.crit_mean[c]; S.ci[tid][c] = Q.crit_istd[c]; }
         S.mean[tid] = Q.mean; S.isd[tid] = 1. / Q.sd; S.bin1[tid] = Q.bin1; S.binsize[tid] = Q.binsize; S.ibin[tid] = use_div ? __longlong_as_double(0x7ff8000000000000ll) : 1. / Q.binsize;
         S.flo[tid] = Q.phase == 0 ? Q.clo : Q.llo; S.fhi[tid] = Q.phase == 0 ? Q.chi : Q.lhi;
+        S.core_lo[tid] = Q.core_lo; S.core_hi[tid] = Q.core_hi;
     }
     for (int k = tid; k < 4 * 256; k += 256) (&S.bins[0][0])[k] = 0;
     __syncthreads();
     if (!first && S.phase[0] == 2 && S.phase[1] == 2 && S.phase[2] == 2 && S.phase[3] == 2) return;
     const float statSig = D->p.stat_sig;
     const int npix = R.rpx * R.rpy;
+    const int nblk = gridDim.x;                     // CTAs per region: ZB_QA_NBLK_MIN .. ZB_QA_NBLK (zb_qa_nblk)
     double a1[4] = {0, 0, 0, 0}, a2[4] = {0, 0, 0, 0}; int an[4] = {0, 0, 0, 0};
     double nsum = 0; int nn = 0;
     // one statistic's share of a pixel; `s` is a compile-time constant at every call site
@@ -322,7 +348,6 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
                         const unsigned peers = __match_any_sync(__activemask(), index); \
                         if ((int)(__ffs(peers) - 1) == (threadIdx.x & 31)) atomicAdd(&S.bins[s][index], __popc(peers)); \
                         a1[s] += fabs((double)(xv)); an[s]++; } } } } } while (0)
-    const int nblk = gridDim.x;                     // CTAs per region: ZB_QA_NBLK_MIN .. ZB_QA_NBLK (zb_launch_region_stats)
     const int stride = nblk * 256;
     // every statistic either finished (empty interval: nothing is kept, its sums are not used) or in a clip pass
     bool fast = true;
@@ -333,7 +358,14 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
         f_lo[q] = S.phase[q] == 2 ? __int_as_float(0x7f800000) : S.flo[q];
         f_hi[q] = S.phase[q] == 2 ? __int_as_float(0xff800000) : S.fhi[q];
     }
-    for (int kb = blockIdx.x * 256 + tid; kb < npix; kb += 4 * stride) {
+    const int lane = tid & 31;
+    int scnt[4] = {0, 0, 0, 0};                     // SHELL: values appended so far to this warp's four segments
+    float c_lo[4], c_hi[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) { c_lo[q] = S.core_lo[q]; c_hi[q] = S.core_hi[q]; }
+    // warp-uniform trip count (lanes past the end carry excluded dummy pixels): the shell ballots need whole warps
+    for (int kb0 = blockIdx.x * 256 + (tid & ~31); kb0 < npix; kb0 += 4 * stride) {
+        const int kb = kb0 + lane;
         float dv[4], nv[4]; int mv[4];
 #pragma unroll
         for (int u = 0; u < 4; u++) {                   // 12 independent loads in flight per thread
@@ -345,10 +377,52 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
         // value of the batch finite: branch-light code with the interval ends in registers.  It adds the
         // same terms to the same per-thread sums in the same order as the generic code below (a rejected
         // pixel adds 0.0), so the two paths are interchangeable bit for bit.
+        // (a NaN/Inf only matters under a mask value that lets the pixel into one of the four runs)
         bool nonfinite = false;
 #pragma unroll
-        for (int u = 0; u < 4; u++) nonfinite |= (dv[u] * 0.0f != 0.0f) || (nv[u] * 0.0f != 0.0f);
-        if (fast && !nonfinite) {
+        for (int u = 0; u < 4; u++)
+            nonfinite |= ((dv[u] * 0.0f != 0.0f) || (nv[u] * 0.0f != 0.0f))
+                         && ((mv[u] & 0xffff) == 0 || ((mv[u] & 0xff) && !(mv[u] & ZB_FLAG_OUTPUT_ISBAD)));
+        if (SHELL) {
+            const bool plain = fast && !__any_sync(0xffffffffu, nonfinite);
+            if (plain) {
+                const unsigned lt = (1u << lane) - 1u;
+                const size_t seg0 = ((size_t)(r * 4) * nblk + blockIdx.x) * 8 + (tid >> 5);     // statistic 0's segment
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const float d = dv[u], nz = nv[u];
+                    const int m0 = mv[u];
+                    const bool good = (m0 & 0xffff) == 0;
+                    const bool okp = !good && (m0 & 0xff) && !(m0 & ZB_FLAG_OUTPUT_ISBAD);
+                    const double dd = (double)d, dn = (double)nz;
+                    const double d2 = (double)(d * d), n2 = (double)(nz * nz);
+                    const bool usable_d = !(fabs(dd) <= ZB_ZEROVAL), usable_n = !(fabs(dn) <= ZB_ZEROVAL);
+                    bool keep[4];
+                    keep[0] = good && usable_d && !(d < f_lo[0] || d > f_hi[0]);
+                    keep[1] = good && usable_n && !(nz < f_lo[1] || nz > f_hi[1]);
+                    keep[2] = okp && usable_d && !(d < f_lo[2] || d > f_hi[2]);
+                    keep[3] = okp && usable_n && !(nz < f_lo[3] || nz > f_hi[3]);
+#pragma unroll
+                    for (int s = 0; s < 4; s++) {
+                        const float v = (s & 1) ? nz : d;
+                        if ((s < 2) ? good : okp) {                     // the same terms, in the same order, as the plain form below
+                            a1[s] += keep[s] ? ((s & 1) ? dn : dd) : 0.0; a2[s] += keep[s] ? ((s & 1) ? n2 : d2) : 0.0; an[s] += keep[s];
+                        }
+                        const bool sh = keep[s] && (v < c_lo[s] || v > c_hi[s]);
+                        const unsigned b = __ballot_sync(0xffffffffu, sh);
+                        if (b) {
+                            const int pos = scnt[s] + __popc(b & lt);
+                            if (sh && pos < shell_cap) shell[(seg0 + (size_t)s * nblk * 8) * shell_cap + pos] = v;
+                            scnt[s] += __popc(b);
+                        }
+                    }
+                }
+                continue;
+            }
+            // a statistic clipping with the exact criteria, or a NaN/Inf in the batch: the lists are not complete
+            if (lane == 0) for (int s = 0; s < 4; s++) atomicOr(&qa[r * 4 + s].shell_bad, 1);
+        }
+        if (!SHELL && fast && !nonfinite) {
 #pragma unroll
             for (int u = 0; u < 4; u++) {
                 const float d = dv[u], nz = nv[u];
@@ -428,6 +502,10 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
         }
     }
 #undef QA_ACC
+    if (SHELL && lane == 0) {
+#pragma unroll
+        for (int s = 0; s < 4; s++) shell_n[((size_t)(r * 4 + s) * nblk + blockIdx.x) * 8 + (tid >> 5)] = scnt[s];
+    }
 #pragma unroll                                   // static indices keep a1/a2/an in registers
     for (int s = 0; s < 4; s++) {
         if (S.phase[s] == 2) continue;
@@ -458,8 +536,59 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
         s_part[k].s1 = __ldcg(&g->s1); s_part[k].s2 = __ldcg(&g->s2); s_part[k].n = __ldcg(&g->n);
     }
     __syncthreads();
-    if (tid < 5) qa_decide(D, qa, s_part, nblk, q, r, tid, first, tid < 4 ? S.bins[tid] : S.bins[0]);
+    if (tid < 5) qa_decide(D, qa, s_part + tid * ZB_QA_NBLK, nblk, q, r, tid, first, tid < 4 ? S.bins[tid] : S.bins[0], pass, hist);
     if (tid == 0) qa[r * 4].ticket = 0;
+}
+
+// Clip iterations 2.. of one (region, statistic) without another pass over the frame.  After pass 1 the kept
+// set is the first criterion's interval I1 and every later criterion only removes values near its ends: as long
+// as the accepted interval still contains the core [mean0 -+ 0.75 sig sd0], every value it rejects is on the shell
+// list, and the iteration's sums are the sums over I1 minus the sums over the rejected shell values.  The same
+// decisions as a full pass (qa_decide); if the containment ever fails, or the lists are incomplete, the state is
+// left where it is and the full passes that follow carry on from it.
+__global__ void __launch_bounds__(256)
+k_qa_tail(const ZbDev *__restrict__ D, ZbQaStat *qa, double *__restrict__ q,
+          const float *__restrict__ shell, const int *__restrict__ shell_n, int shell_cap, int nblk)
+{
+    const int s = blockIdx.x, r = blockIdx.y, tid = threadIdx.x;
+    if (D->reg[r].skip) return;
+    ZbQaStat &Q = qa[r * 4 + s];
+    __shared__ QaShared S;
+    __shared__ int s_go;
+    __shared__ float s_lo, s_hi;
+    __shared__ ZbQaPart s_one;
+    const int nseg = nblk * 8;
+    const size_t seg0 = (size_t)(r * 4 + s) * nseg;
+    if (Q.phase != 0 || Q.shell_bad || Q.exact || Q.ncrit != 2) return;          // uniform over the CTA (nobody has written yet)
+    // overflow of any segment: the list is incomplete
+    int over = 0;
+    for (int g = tid; g < nseg; g += 256) over |= shell_n[seg0 + g] > shell_cap;
+    if (__syncthreads_or(over)) return;
+    for (int it = 0; it < 8; it++) {
+        if (tid == 0) {
+            s_go = Q.phase == 0 && !Q.exact && Q.clo <= Q.core_lo && Q.chi >= Q.core_hi;
+            s_lo = Q.clo; s_hi = Q.chi;
+        }
+        __syncthreads();
+        if (!s_go) return;
+        const float lo = s_lo, hi = s_hi;
+        double r1 = 0, r2 = 0; int rn = 0;
+        // fixed assignment: warp w takes segments w, w+8, ...; lanes stride the segment
+        for (int g = tid >> 5; g < nseg; g += 8) {
+            const int n = shell_n[seg0 + g];
+            const float *v = shell + (seg0 + g) * shell_cap;
+            for (int k = tid & 31; k < n; k += 32) {
+                const float x = v[k];
+                if (x < lo || x > hi) { r1 += (double)x; r2 += (double)(x * x); rn++; }
+            }
+        }
+        qa_block_sum(S, r1, r2, rn);
+        if (tid == 0) {
+            s_one.s1 = Q.base_s1 - r1; s_one.s2 = Q.base_s2 - r2; s_one.n = Q.base_n - rn;
+            qa_decide(D, qa, &s_one, 1, q, r, s, 0, S.bins[0], 2 + it, 0);
+        }
+        __syncthreads();
+    }
 }
 
 __global__ void k_qa_finish(const ZbDev *__restrict__ D, const ZbQaStat *__restrict__ qa, double *__restrict__ q)
@@ -499,29 +628,44 @@ __global__ void k_rescale_ok(const ZbDev *__restrict__ D, const int32_t *__restr
 int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStream_t st)
 {
     const int nR = ctx->sz.n_regions;
-    k_qa_sample<<<dim3(4, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, ctx->d_qa, ctx->d_ran, ctx->n_ran); ZB_DBG("k_qa_sample");
-    ctx->launches++;
-    // at most maxiter (5) clip passes + 5 histogram passes; finished regions fall through at once.
-    // CTAs per region: enough to put ~4 CTAs on every SM whatever the number of regions (a single-region
-    // coadd-scale frame would otherwise stream 38 Mpx through 64 CTAs)
+    // The keywords hotpants writes (DMEAN, DSIGE, DSIG and their OK-pixel twins, X2NRM, NX2NRM) come from the
+    // sigma-clip phase of getStampStats3 and from getNoiseStats3.  Its histogram phase (functions.c:879-1031: mode,
+    // median, FWHM) only feeds fprintf(stderr) lines of main.c:1479-1554 and has no side effect on any product, so
+    // it — and the 100-value sample that sizes its bins — is left out unless ZB_QA_HIST=1 asks for the whole routine.
     static int minb = 0, use_div = 0, rot = -1;
+    int hist, notail;               // read per call: the tests switch them (ZB_QA_NOTAIL=1: full passes only)
+    { const char *e = getenv("ZB_QA_HIST"); hist = (e && e[0] == '1') ? 1 : 0; }
+    { const char *e = getenv("ZB_QA_NOTAIL"); notail = (e && e[0] == '1') ? 1 : 0; }
     if (rot < 0) { const char *e = getenv("ZB_QA_ROT"); rot = e ? atoi(e) : 1; }
     { const char *e = getenv("ZB_QA_DIV"); use_div = (e && e[0] == '1') ? 1 : 0; }
     // 4 CTAs/SM: 9 regions x 64 CTAs = one resident wave (A/B on B200: 1.47 ms vs 1.65 at 3)
     if (!minb) { const char *e = getenv("ZB_QA_MINB"); minb = e ? atoi(e) : 4; }
-    int nblk = nR >= 5 ? ZB_QA_NBLK_MIN : (4 * 148 + nR - 1) / nR;
-    nblk = nblk < ZB_QA_NBLK_MIN ? ZB_QA_NBLK_MIN : (nblk > ZB_QA_NBLK ? ZB_QA_NBLK : nblk);
-    for (int pass = 0; pass < 10; pass++) {
-#define QA_LAUNCH(M, R) k_qa_pass<M, R><<<dim3(nblk, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask, \
-                                                                  ctx->d_qa, ctx->d_qpart, ctx->d_stats, pass == 0, use_div)
-        if (!rot) QA_LAUNCH(4, 0);                  // ZB_QA_ROT=0: the generic form unrolled four times (A/B)
-        else if (minb == 3) QA_LAUNCH(3, 1);
-        else if (minb == 4) QA_LAUNCH(4, 1);
-        else QA_LAUNCH(2, 1);
-#undef QA_LAUNCH
+    k_qa_sample<<<dim3(4, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, ctx->d_qa, ctx->d_ran, ctx->n_ran, hist); ZB_DBG("k_qa_sample");
+    ctx->launches++;
+    const int nblk = zb_qa_nblk(nR);
+#define QA_ARGS(pass) ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask, ctx->d_qa, ctx->d_qpart, ctx->d_stats, (pass) == 0, use_div, \
+                      (pass), hist, ctx->d_qshell, ctx->d_qshell_n, ctx->qshell_cap
+    // sigma clip: at most maxiter (5) iterations.  Passes 0 and 1 read the frame; iterations 2.. run on the shell
+    // lists pass 1 leaves behind (k_qa_tail); passes 2-4 only do work for a statistic the tail had to hand back
+    // (finished regions fall through at once).  With the histogram: up to 5 more passes, no shell lists.
+    const int npass = hist ? 10 : 5;
+    for (int pass = 0; pass < npass; pass++) {
+        if (pass == 1 && !hist) {
+            k_qa_pass<3, 1, true><<<dim3(nblk, nR), 256, 0, st>>>(QA_ARGS(pass)); ZB_DBG("k_qa_pass shell");
+            ctx->launches++;
+            if (notail) continue;
+            k_qa_tail<<<dim3(4, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_qa, ctx->d_stats, ctx->d_qshell, ctx->d_qshell_n, ctx->qshell_cap, nblk); ZB_DBG("k_qa_tail");
+            ctx->launches++;
+            continue;
+        }
+        if (!rot) k_qa_pass<4, 0, false><<<dim3(nblk, nR), 256, 0, st>>>(QA_ARGS(pass));       // ZB_QA_ROT=0: the generic form unrolled four times (A/B)
+        else if (minb == 3) k_qa_pass<3, 1, false><<<dim3(nblk, nR), 256, 0, st>>>(QA_ARGS(pass));
+        else if (minb == 4) k_qa_pass<4, 1, false><<<dim3(nblk, nR), 256, 0, st>>>(QA_ARGS(pass));
+        else k_qa_pass<2, 1, false><<<dim3(nblk, nR), 256, 0, st>>>(QA_ARGS(pass));
         ZB_DBG("k_qa_pass");
         ctx->launches++;
     }
+#undef QA_ARGS
     k_qa_finish<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_qa, ctx->d_stats); ZB_DBG("k_qa_finish");
     ctx->launches++;
     if (ctx->p.rescale_ok) {
