@@ -162,6 +162,13 @@ __device__ __forceinline__ static double background_at(const ZbDev *D, const ZbR
     return bg;
 }
 
+// the same, kept out of line: k_convolve's epilogue calls it per pixel only for -bgo > 0, and inlined there the compiler
+// hoists its coordinate normalisation (two double divisions) into the per-row code of the common -bgo 0 case too
+__device__ __noinline__ static double background_at_call(const ZbDev *D, int rpx, int rpy, const double *sol, int xi, int yi) {
+    ZbRegion R; R.rpx = rpx; R.rpy = rpy;
+    return background_at(D, R, sol, xi, yi);
+}
+
 // everything after the convolution sum for one region pixel; the other image's value `oth`, its rms
 // value `orv` (ignored without an rms map) and its user-mask bits `ub` are passed in so that callers
 // can issue those global loads in batches
@@ -300,9 +307,9 @@ __device__ __forceinline__ u64 bits_at(const unsigned *row, int x, int n) {
 
 // alard.c:1304-1308,1327: sum |K| over all taps (aks) and over the taps whose pixel is not INPUT_ISBAD (uks), both in
 // the reference's tap order; true when uks/aks < kerFracMask.  Fast decision: uks = aks - (the bad taps), the bad taps
-// of a footprint row summed run by run from the row's prefix sums of |K| (a dead column or the frame border is one
-// run per row), accurate to ~1e-13 relative; the reference's sequentially rounded sums are only reproduced when the
-// ratio is within 1e-9 of the threshold.
+// of a footprint row summed run by run from the row's prefix sums of |K| (a saturated core, a dead column or the frame
+// border is one run per row: summing such runs tap by tap made the launch 70 % slower), accurate to ~1e-13 relative;
+// the reference's sequentially rounded sums are only reproduced when the ratio is within 1e-9 of the threshold.
 //   pre   [fw][fwp+1] prefix sums of |K| along each (reversed) kernel row of the output's block
 //   Kb    the block's taps (reversed, rows padded to fwp)
 //   rbad  R_bad row of the footprint's first row; rows: bit dy set when tile row (first row + dy) holds any bad pixel
@@ -456,6 +463,7 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
     unsigned *s_rowbad = (unsigned *)(bars + 8);               // [2 parity][16]  bit per tile row: the row holds a bad pixel
     int *s_tile = (int *)(s_rowbad + 32);                      // [4] ring of tile indices handed out by the producer; -1: no more work
     uint64_t *raw_full = bars, *raw_empty = bars + 1, *k_full = bars + 2, *k_empty = bars + 3, *res_full = bars + 4, *res_empty = bars + 5;
+    uint64_t *v_full = bars + 7;                               // the V flag rows of the tile are complete (FMA warps, tiles with flagged pixels)
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int hw = D->p.hw_kernel, fw = D->sz.fw_kernel, B = D->sz.kc_step;
@@ -469,7 +477,7 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
 
     if (tid == 0) {
         mbar_init(raw_full, 1); mbar_init(raw_empty, NFW); mbar_init(k_full, 1); mbar_init(k_empty, NFW);
-        mbar_init(res_full, NFW); mbar_init(res_empty, CONV_EPI_WARPS);
+        mbar_init(res_full, NFW); mbar_init(res_empty, CONV_EPI_WARPS); mbar_init(v_full, NFW);
         s_any[0] = s_any[1] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -613,7 +621,11 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                             else ovar = (float)__dadd_rn(__dmul_rn(fabs((double)ov), (double)P.o_invgain), o_qq);
                             // (float)sqrt((double)x) == sqrtf(x) correctly rounded: 53 >= 2*24+2 makes the double rounding innocuous
                             float nz = __fsqrt_rn(__fadd_rn(ovar, var));
+                            #ifdef CONV_BG_INLINE
                             const double bg = bg_const ? bg0 : background_at(D, R, sol, i00 + ox, j00 + oy);
+#else
+                            const double bg = bg_const ? bg0 : background_at_call(D, R.rpx, R.rpy, sol, i00 + ox, j00 + oy);
+#endif
                             float d = __fsub_rn((float)__dadd_rn((double)conv_out, bg), ov);
                             if (do_scale) { d = (float)__dmul_rn((double)d, inv1); nz = (float)__dmul_rn((double)nz, inv1); }
                             if (conv_t) d = -d;
@@ -649,6 +661,7 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
         const int dy0 = (g * fw) / KS, dy1 = ((g + 1) * fw) / KS;                  // this band's kernel rows (ascending image rows)
         const bool have_rms = G.have_rms != 0;
         const double c_qq = __fmul_rn(P.c_quad, P.c_quad);
+        int vit = 0;                                                               // tiles that had flagged pixels so far (phase of v_full)
         for (int it = 0;; it++) {
             const unsigned par = it & 1;
             mbar_wait(raw_full, par);
@@ -676,12 +689,13 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
             if (have_rms && !P.cmask_src) {
                 for (int ty = fwarp; ty < TH; ty += NFW) {
                     const bool yin = gy0 + ty < nyi;
-                    const float *ri = raw_img + ty * WR + sh, *rr = raw_rms + ty * WR + sh;
-                    double *cd = compd + (size_t)ty * Wc;
-                    float *cv = compv + (size_t)ty * Wv;
+                    const float *__restrict__ ri = raw_img + ty * WR + sh, *__restrict__ rr = raw_rms + ty * WR + sh;
+                    double *__restrict__ cd = compd + (size_t)ty * Wc;
+                    float *__restrict__ cv = compv + (size_t)ty * Wv;
+#ifdef CONV_CONVERT_SIMPLE
                     for (int txb = 0; txb < Wt; txb += 32) {
                         const int tx = txb + lane;
-                        bool bad = false;                                          // every value flag carries INPUT_ISBAD (makeInputMask)
+                        bool bad = false;
                         if (tx < Wt) {
                             const float pv = ri[tx], rv = rr[tx];
                             cd[tx] = (double)pv;
@@ -692,6 +706,32 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                         if (lane == 0) { Rany[ty * NW + (txb >> 5)] = bb; Rbad[ty * NW + (txb >> 5)] = bb; if (bb) atomicOr(&s_rowbad[par * 16 + (ty >> 5)], 1u << (ty & 31)); }
                         anyf |= (bb != 0u);
                     }
+#else
+                    for (int txb = 0; txb < Wt; txb += 128) {                      // four 32-column segments in flight
+                        float pv[4], rv[4];
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            const int tx = txb + 32 * q + lane;
+                            pv[q] = tx < Wt ? ri[tx] : 0.f; rv[q] = tx < Wt ? rr[tx] : 0.f;
+                        }
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            const int tx = txb + 32 * q + lane;
+                            bool bad = false;                                      // every value flag carries INPUT_ISBAD (makeInputMask)
+                            if (tx < Wt) {
+                                cd[tx] = (double)pv[q];
+                                cv[tx] = __fmul_rn(rv[q], rv[q]);
+                                bad = yin && tx < x_in && (pv[q] == fill || pv[q] >= P.cU || pv[q] <= P.cL);
+                            }
+                            const unsigned bb = __ballot_sync(0xffffffffu, bad);
+                            if (lane == 0 && txb + 32 * q < Wt) {
+                                Rany[ty * NW + ((txb >> 5) + q)] = bb; Rbad[ty * NW + ((txb >> 5) + q)] = bb;
+                                if (bb) atomicOr(&s_rowbad[par * 16 + (ty >> 5)], 1u << (ty & 31));
+                            }
+                            anyf |= (bb != 0u);
+                        }
+                    }
+#endif
                 }
             } else {
                 for (int ty = fwarp; ty < TH; ty += NFW) {
@@ -723,7 +763,6 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
             // prefix sums of |K| along every kernel row of the tile's blocks, one thread per row (the uks/aks test below);
             // the kernels were requested when the previous tile's multiply ended and have normally landed by now
             mbar_wait(k_full, par);
-            // (taken by the threads of the last band first: band 0 also owns the mask work after the multiply)
             for (int k = CONV_FMA_THREADS - 1 - ft; k < NB * fw; k += CONV_FMA_THREADS) {
                 const int b = k / fw, dy = k - b * fw;
                 const KTap *kr = kbuf + (size_t)b * G.kstride + dy * fwp;
@@ -741,7 +780,12 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                     for (int dy = 0; dy < fw; dy++) v |= src[(size_t)dy * NW];
                     (pl ? Vbad : Vany)[(size_t)oy * NW + w] = v;
                 }
-                named_bar_sync(1, CONV_FMA_THREADS);                               // the band-0 owners read them after the multiply
+#ifdef CONV_V_BARSYNC
+                named_bar_sync(1, CONV_FMA_THREADS);
+#else
+                __syncwarp();
+                if (lane == 0) mbar_arrive(v_full);                                // read after the multiply: nobody waits here
+#endif
             }
             // ---- multiply
             const bool active = lb < NB && T.bx0 + lbx < T.nbx && T.by0 + lby < T.nby;
@@ -770,11 +814,18 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                     }
                 }
             }
-            // ---- what the convolution contributes to the mask (alard.c:1304-1332), by the band-0 owner of each output: the
+            // ---- what the convolution contributes to the mask (alard.c:1304-1332), by the owners of each output: the
             // pixel's own bits with OUTPUT_ISBAD when it is bad; OK_CONV when a flagged pixel lies under the footprint, or
             // BAD_CONV | OUTPUT_ISBAD when too much of the kernel sits on bad pixels
             mbar_wait(res_empty, par ^ 1);
+#ifndef CONV_V_BARSYNC
+            if (s_any[par]) { mbar_wait(v_full, vit & 1); vit++; }                 // every warp's share of the V rows is written
+#endif
+#ifdef CONV_MASK_BAND0
             if (active && g == 0 && s_any[par]) {
+#else
+            if (active && s_any[par]) {                                            // the KS band owners of an output tile share its columns
+#endif
                 const float kfm = D->p.ker_frac_mask;
                 const u64 fmask = (1ull << fw) - 1ull;
                 const double aks_blk = any_bad ? kaks[(long long)T.r * per_region + (long long)(T.by0 + lby) * T.nbx + (T.bx0 + lbx)] : 1.0;
@@ -788,7 +839,11 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                     const u64 wc = bits_at(Rany + (size_t)(yy + hw) * NW, x0 + hw, TX);
                     const u64 rows = any_bad ? bits_at(s_rowbad + par * 16, yy, fw) : 0ull;
 #pragma unroll 1
+#ifdef CONV_MASK_BAND0
                     for (int tt = 0; tt < TX; tt++) {
+#else
+                    for (int tt = g; tt < TX; tt += KS) {
+#endif
                         if (gxi * TX + tt >= B) break;
                         int m = 0;
                         if ((wc >> tt) & 1ull) {

@@ -612,8 +612,19 @@ k_lu_subst(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, const dou
         if (tid == 0) {
             double sum = b[i];
             if (i + 1 < n) sum -= sd1[i] * b[i + 1];
-#pragma unroll 8
-            for (int j = i + 2; j < n; j++) sum -= p[j];
+            // the chain of dependent subtractions is the critical path of the whole solve: the next eight products are
+            // in registers before the current eight are subtracted, so only the adder's latency is paid per term
+            int j = i + 2;
+            if (j + 8 <= n) {
+                double q0 = p[j], q1 = p[j + 1], q2 = p[j + 2], q3 = p[j + 3], q4 = p[j + 4], q5 = p[j + 5], q6 = p[j + 6], q7 = p[j + 7];
+                for (j += 8; j + 8 <= n; j += 8) {
+                    const double r0 = p[j], r1 = p[j + 1], r2 = p[j + 2], r3 = p[j + 3], r4 = p[j + 4], r5 = p[j + 5], r6 = p[j + 6], r7 = p[j + 7];
+                    sum -= q0; sum -= q1; sum -= q2; sum -= q3; sum -= q4; sum -= q5; sum -= q6; sum -= q7;
+                    q0 = r0; q1 = r1; q2 = r2; q3 = r3; q4 = r4; q5 = r5; q6 = r6; q7 = r7;
+                }
+                sum -= q0; sum -= q1; sum -= q2; sum -= q3; sum -= q4; sum -= q5; sum -= q6; sum -= q7;
+            }
+            for (; j < n; j++) sum -= p[j];
             b[i] = sum / dg[i];
         } else if (i >= 1) {
             // prepare row i-1: products with x_j, j >= i+1 (all known while thread 0 works on row i)

@@ -91,10 +91,11 @@ struct ZbQaStat {
     // float interval every later criterion must still contain for the list to hold all later rejections
     double base_s1, base_s2;
     int base_n, shell_bad;
-    float core_lo, core_hi;
+    float core_lo, core_hi;        // core of the shell lists as collected by the last shell pass
+    float ncore_lo, ncore_hi;      // core the next frame pass collects with (from the latest mean / sd)
     int bins[256];
 };
-#define ZB_QA_SHELL_DIV 8       // a warp's shell segment holds 1/8 of the pixels it reads in a pass
+#define ZB_QA_SHELL_DIV 4       // a warp's shell segment holds 1/4 of the pixels it reads in a pass
 struct ZbQaPart { double s1, s2; int n, pad; };
 // CTAs per region of a k_qa_pass launch: enough to put ~4 CTAs on every SM whatever the number of regions
 static inline int zb_qa_nblk(int n_regions) {

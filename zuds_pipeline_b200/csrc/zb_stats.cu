@@ -116,7 +116,7 @@ __device__ static void qa_reset(ZbQaStat &Q, int s, int um, int sm) {
     Q.ncrit = 0; Q.cnt_prev = 0; Q.tries = 0; Q.imax = 0; Q.ticket = 0; Q.exact = 0;
     Q.clo = Q.llo = -3.402823466e38f; Q.chi = Q.lhi = 3.402823466e38f;
     Q.mean = Q.sd = Q.mode = Q.median = Q.fwhm = Q.lfwhm = Q.sum = 0;
-    Q.base_s1 = Q.base_s2 = 0; Q.base_n = 0; Q.shell_bad = 0; Q.core_lo = 1.f; Q.core_hi = -1.f;
+    Q.base_s1 = Q.base_s2 = 0; Q.base_n = 0; Q.shell_bad = 0; Q.core_lo = Q.ncore_lo = 1.f; Q.core_hi = Q.ncore_hi = -1.f;
 }
 
 // The first 100 accepted random samples (functions.c:811-833), accepted in attempt order.
@@ -143,10 +143,46 @@ k_qa_sample(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const 
         if (tid == 0) { Q.phase = 2; Q.status = 4; Q.mean = Q.sd = Q.mode = Q.median = Q.fwhm = Q.lfwhm = Q.sum = 0; }
         return;
     }
-    if (!hist) {            // the sample only sizes the histogram (functions.c:811-838): nothing to draw without it
+    if (!hist) {
+        // The reference's sample only sizes the histogram (functions.c:811-838).  Without the histogram a sample serves one
+        // purpose: a robust guess of where the bulk of the values lies, the *core* whose complement pass 0 appends to the
+        // shell lists (k_qa_pass<SHELL>).  It affects which values are listed, never a result.  GOOD-pixel statistics:
+        // the first 256 draws of the same random sequence, median +- 2 x half the 16..84 % range.  OK-pixel statistics
+        // (a percent of the pixels): no core at all, every value is listed.
+        __shared__ float sv[256], so[256];
+        float c_lo = 3.402823466e38f, c_hi = -3.402823466e38f;       // empty core
+        if (s < 2) {
+            int flag = 0; float rdat = 0.f;
+            if (2 * tid + 1 < n_ran) {
+                const int xr = (int)floor(ran[2 * tid] * R.rpx), yr = (int)floor(ran[2 * tid + 1] * R.rpy);
+                rdat = data[xr + yr * R.rpx];
+                flag = !zb_excluded(m[xr + yr * R.rpx], rdat, um, sm) && !(rdat * 0.0f != 0.0f);
+            }
+            const unsigned bal = __ballot_sync(0xffffffffu, flag);
+            if ((tid & 31) == 0) wsum[tid >> 5] = __popc(bal);
+            __syncthreads();
+            int before = 0, n = 0;
+            for (int w = 0; w < 8; w++) { if (w < (tid >> 5)) before += wsum[w]; n += wsum[w]; }
+            const int pos = before + __popc(bal & ((1u << (tid & 31)) - 1u));
+            if (flag) sv[pos] = rdat;
+            __syncthreads();
+            if (n >= 32) {
+                if (tid < n) {                                          // rank sort: ties broken by position
+                    const float v = sv[tid]; int rank = 0;
+                    for (int j = 0; j < n; j++) { const float u = sv[j]; rank += (u < v) || (u == v && j < tid); }
+                    so[rank] = v;
+                }
+                __syncthreads();
+                if (tid == 0) {
+                    const float med = so[n / 2], half = 0.5f * (so[(int)(0.84f * n)] - so[(int)(0.16f * n)]);
+                    c_lo = med - 2.f * half; c_hi = med + 2.f * half;
+                }
+            }
+        }
         if (tid == 0) {
             Q.npts_s = 0; Q.samp_med = Q.binsize = Q.bin1 = 0.;
             qa_reset(Q, s, um, sm);
+            Q.ncore_lo = c_lo; Q.ncore_hi = c_hi;
         }
         return;
     }
@@ -257,7 +293,10 @@ __device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *P
     if (Q.phase == 0) {
         const int k = Q.ncrit;                          // passes done so far == iterations started
         const int after = hist ? 1 : 2;                 // the histogram outputs reach no product (see zb_launch_region_stats)
-        if (pass == 1) { Q.base_s1 = s1; Q.base_s2 = s2; Q.base_n = ncnt; }       // sums over the first criterion's interval
+        if (pass >= 0) {                                // sums over the interval this pass kept, and the core its shell lists were cut at
+            Q.base_s1 = s1; Q.base_s2 = s2; Q.base_n = ncnt;
+            Q.core_lo = Q.ncore_lo; Q.core_hi = Q.ncore_hi;
+        }
         if (k == 0 && ncnt == 0) { Q.mean = 0; Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
         if (ncnt != Q.cnt_prev && k < Q.maxiter) {
             Q.cnt_prev = ncnt;
@@ -266,9 +305,9 @@ __device__ static void qa_decide(const ZbDev *D, ZbQaStat *qa, const ZbQaPart *P
             if (ncnt > 1) { double sd = s2 - ncnt * Q.mean * Q.mean; Q.sd = sqrt(sd / (double)(ncnt - 1)); }
             else { Q.sd = ZB_MAXVAL; Q.status = 5; Q.phase = 2; return; }
             Q.crit_mean[k] = Q.mean; Q.crit_istd[k] = 1. / Q.sd; Q.ncrit = k + 1;
-            if (k == 0) {                               // pixels outside this core go to the shell list in pass 1
+            if (pass >= 0) {                            // a frame pass: values outside this core go to the shell list of the next one
                 const double w = 0.75 * (double)sig * Q.sd;
-                Q.core_lo = (float)(Q.mean - w); Q.core_hi = (float)(Q.mean + w);
+                Q.ncore_lo = (float)(Q.mean - w); Q.ncore_hi = (float)(Q.mean + w);
             }
             float lo, hi;
             if (!Q.exact && qa_interval(Q.mean, 1. / Q.sd, sig, lo, hi)) {
@@ -315,7 +354,7 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
         for (int c = 0; c < 8; c++) { S.cm[tid][c] = Q.crit_mean[c]; S.ci[tid][c] = Q.crit_istd[c]; }
         S.mean[tid] = Q.mean; S.isd[tid] = 1. / Q.sd; S.bin1[tid] = Q.bin1; S.binsize[tid] = Q.binsize; S.ibin[tid] = use_div ? __longlong_as_double(0x7ff8000000000000ll) : 1. / Q.binsize;
         S.flo[tid] = Q.phase == 0 ? Q.clo : Q.llo; S.fhi[tid] = Q.phase == 0 ? Q.chi : Q.lhi;
-        S.core_lo[tid] = Q.core_lo; S.core_hi[tid] = Q.core_hi;
+        S.core_lo[tid] = Q.ncore_lo; S.core_hi[tid] = Q.ncore_hi;
     }
     for (int k = tid; k < 4 * 256; k += 256) (&S.bins[0][0])[k] = 0;
     __syncthreads();
@@ -397,6 +436,10 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
                     const double dd = (double)d, dn = (double)nz;
                     const double d2 = (double)(d * d), n2 = (double)(nz * nz);
                     const bool usable_d = !(fabs(dd) <= ZB_ZEROVAL), usable_n = !(fabs(dn) <= ZB_ZEROVAL);
+                    if (first && good && !(fabsf(d) < 1e-10f)) {        // getNoiseStats3, functions.c:719-761
+                        const float ndat = (float)(1. / nz);
+                        nn++; nsum += (double)(d * d * ndat * ndat);
+                    }
                     bool keep[4];
                     keep[0] = good && usable_d && !(d < f_lo[0] || d > f_hi[0]);
                     keep[1] = good && usable_n && !(nz < f_lo[1] || nz > f_hi[1]);
@@ -540,29 +583,35 @@ k_qa_pass(const ZbDev *__restrict__ D, const float *__restrict__ rdiff, const fl
     if (tid == 0) qa[r * 4].ticket = 0;
 }
 
-// Clip iterations 2.. of one (region, statistic) without another pass over the frame.  After pass 1 the kept
-// set is the first criterion's interval I1 and every later criterion only removes values near its ends: as long
-// as the accepted interval still contains the core [mean0 -+ 0.75 sig sd0], every value it rejects is on the shell
-// list, and the iteration's sums are the sums over I1 minus the sums over the rejected shell values.  The same
-// decisions as a full pass (qa_decide); if the containment ever fails, or the lists are incomplete, the state is
-// left where it is and the full passes that follow carry on from it.
-__global__ void __launch_bounds__(256)
+// The clip iterations of one (region, statistic) that follow a shell pass, without another pass over the frame.  The
+// pass left the sums over the values it kept (base) and, on the shell lists, every kept value outside its core.  As
+// long as the accepted interval still contains the core, every value a later criterion rejects is on the lists, and the
+// iteration's sums are the base sums minus the sums over the rejected list values.  The same decisions as a full pass
+// (qa_decide); if the containment ever fails, or the lists are incomplete, the state is left where it is and the frame
+// passes that follow carry on from it.
+#define QA_TAIL_NT 1024
+__global__ void __launch_bounds__(QA_TAIL_NT)
 k_qa_tail(const ZbDev *__restrict__ D, ZbQaStat *qa, double *__restrict__ q,
-          const float *__restrict__ shell, const int *__restrict__ shell_n, int shell_cap, int nblk)
+          const float *__restrict__ shell, const int *__restrict__ shell_n, int shell_cap, int nblk, int pass)
 {
     const int s = blockIdx.x, r = blockIdx.y, tid = threadIdx.x;
     if (D->reg[r].skip) return;
     ZbQaStat &Q = qa[r * 4 + s];
-    __shared__ QaShared S;
-    __shared__ int s_go;
+    __shared__ double w1[QA_TAIL_NT / 32], w2[QA_TAIL_NT / 32];
+    __shared__ int wn[QA_TAIL_NT / 32];
+    __shared__ int s_go, s_dummy_bins[1];
     __shared__ float s_lo, s_hi;
     __shared__ ZbQaPart s_one;
     const int nseg = nblk * 8;
     const size_t seg0 = (size_t)(r * 4 + s) * nseg;
-    if (Q.phase != 0 || Q.shell_bad || Q.exact || Q.ncrit != 2) return;          // uniform over the CTA (nobody has written yet)
+    // uniform over the CTA (nobody has written yet); base sums, core and lists are those of the shell pass that has just run
+    const int usable = Q.phase == 0 && !Q.shell_bad && !Q.exact;
+    __syncthreads();
+    if (tid == 0) Q.shell_bad = 0;                                               // for the next shell pass, if there is one
+    if (!usable) return;
     // overflow of any segment: the list is incomplete
     int over = 0;
-    for (int g = tid; g < nseg; g += 256) over |= shell_n[seg0 + g] > shell_cap;
+    for (int g = tid; g < nseg; g += QA_TAIL_NT) over |= shell_n[seg0 + g] > shell_cap;
     if (__syncthreads_or(over)) return;
     for (int it = 0; it < 8; it++) {
         if (tid == 0) {
@@ -573,19 +622,36 @@ k_qa_tail(const ZbDev *__restrict__ D, ZbQaStat *qa, double *__restrict__ q,
         if (!s_go) return;
         const float lo = s_lo, hi = s_hi;
         double r1 = 0, r2 = 0; int rn = 0;
-        // fixed assignment: warp w takes segments w, w+8, ...; lanes stride the segment
-        for (int g = tid >> 5; g < nseg; g += 8) {
+        // fixed assignment: thread t takes segments t, t + QA_TAIL_NT, ... and walks each in order: the sums do not depend on timing
+        for (int g = tid; g < nseg; g += QA_TAIL_NT) {
             const int n = shell_n[seg0 + g];
             const float *v = shell + (seg0 + g) * shell_cap;
-            for (int k = tid & 31; k < n; k += 32) {
+            int k = 0;
+            for (; k + 8 <= n; k += 8) {
+                float x[8];
+#pragma unroll
+                for (int e = 0; e < 8; e++) x[e] = v[k + e];
+#pragma unroll
+                for (int e = 0; e < 8; e++)
+                    if (x[e] < lo || x[e] > hi) { r1 += (double)x[e]; r2 += (double)(x[e] * x[e]); rn++; }
+            }
+            for (; k < n; k++) {
                 const float x = v[k];
                 if (x < lo || x > hi) { r1 += (double)x; r2 += (double)(x * x); rn++; }
             }
         }
-        qa_block_sum(S, r1, r2, rn);
+        for (int o = 16; o > 0; o >>= 1) {
+            r1 += __shfl_xor_sync(0xffffffffu, r1, o);
+            r2 += __shfl_xor_sync(0xffffffffu, r2, o);
+            rn += __shfl_xor_sync(0xffffffffu, rn, o);
+        }
+        if ((tid & 31) == 0) { w1[tid >> 5] = r1; w2[tid >> 5] = r2; wn[tid >> 5] = rn; }
+        __syncthreads();
         if (tid == 0) {
-            s_one.s1 = Q.base_s1 - r1; s_one.s2 = Q.base_s2 - r2; s_one.n = Q.base_n - rn;
-            qa_decide(D, qa, &s_one, 1, q, r, s, 0, S.bins[0], 2 + it, 0);
+            double t1 = 0, t2 = 0; int tn = 0;
+            for (int w = 0; w < QA_TAIL_NT / 32; w++) { t1 += w1[w]; t2 += w2[w]; tn += wn[w]; }
+            s_one.s1 = Q.base_s1 - t1; s_one.s2 = Q.base_s2 - t2; s_one.n = Q.base_n - tn;
+            qa_decide(D, qa, &s_one, 1, q, r, s, 0, s_dummy_bins, -1, 0);        // not a frame pass: base sums and core stay
         }
         __syncthreads();
     }
@@ -645,16 +711,18 @@ int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStr
     const int nblk = zb_qa_nblk(nR);
 #define QA_ARGS(pass) ctx->d_dev, ctx->d_rdiff, ctx->d_rnoise, ctx->d_omask, out_mask, ctx->d_qa, ctx->d_qpart, ctx->d_stats, (pass) == 0, use_div, \
                       (pass), hist, ctx->d_qshell, ctx->d_qshell_n, ctx->qshell_cap
-    // sigma clip: at most maxiter (5) iterations.  Passes 0 and 1 read the frame; iterations 2.. run on the shell
-    // lists pass 1 leaves behind (k_qa_tail); passes 2-4 only do work for a statistic the tail had to hand back
-    // (finished regions fall through at once).  With the histogram: up to 5 more passes, no shell lists.
+    // sigma clip: at most maxiter (5) iterations.  Pass 0 reads the frame: sums of everything, and every value outside the
+    // sample's core onto the shell lists; k_qa_tail then runs the clip iterations on the lists.  If it has to hand a
+    // statistic back (the accepted interval no longer contains the core, a list overflowed, NaNs in the region), pass 1
+    // collects again around mean0 +- 0.75 statSig sd0 and the tail retries; passes 2-4 are plain passes that fall
+    // through at once when nothing is left.  With the histogram: 5 + up to 5 plain passes, no shell lists.
     const int npass = hist ? 10 : 5;
     for (int pass = 0; pass < npass; pass++) {
-        if (pass == 1 && !hist) {
+        if (pass <= 1 && !hist) {
             k_qa_pass<3, 1, true><<<dim3(nblk, nR), 256, 0, st>>>(QA_ARGS(pass)); ZB_DBG("k_qa_pass shell");
             ctx->launches++;
             if (notail) continue;
-            k_qa_tail<<<dim3(4, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_qa, ctx->d_stats, ctx->d_qshell, ctx->d_qshell_n, ctx->qshell_cap, nblk); ZB_DBG("k_qa_tail");
+            k_qa_tail<<<dim3(4, nR), QA_TAIL_NT, 0, st>>>(ctx->d_dev, ctx->d_qa, ctx->d_stats, ctx->d_qshell, ctx->d_qshell_n, ctx->qshell_cap, nblk, pass); ZB_DBG("k_qa_tail");
             ctx->launches++;
             continue;
         }
