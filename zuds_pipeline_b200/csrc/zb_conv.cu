@@ -948,27 +948,33 @@ static size_t conv_plan(ConvGeom &G, int B, int fw, int TX, int TY, int CH, bool
     G.TH = (G.NBY - 1) * B + G.GY * TY + fw - 1;
     G.WR = (G.Wt + 3 + 3) & ~3;      // + up to 3 columns: the box starts at a 16-byte aligned column (TMA traps otherwise)
     G.NW = (G.Wt + 31) / 32 + 2;
-    // row pitches of the two planes: fewest shared-memory conflicts of the window loads for the thread layout of the
-    // first four half-warps (double plane: 8-byte elements, 16 lanes per wavefront) / two warps (float plane: 32 lanes)
+    // row pitches of the two planes: fewest shared-memory wavefronts of a window load, summed over every warp of a band
+    // of kernel rows (double plane: 8-byte elements, a wavefront serves 16 lanes; float plane: 32 lanes).  Judged on the
+    // first two warps only, the pitch left every window load with a 2-way conflict (ncu: 3.8 wavefronts per LDS.64).
     {
-        const int tpb = G.GX * G.GY;
+        const int tpb = G.GX * G.GY, Tg = CONV_FMA_THREADS / (G.KS > 0 ? G.KS : 1);
         for (int plane = 0; plane < 2; plane++) {
-            const int lanes = plane == 0 ? 16 : 32, groups = plane == 0 ? 4 : 2;
+            const int lanes = plane == 0 ? 16 : 32;
             int best = -1, bestw = G.Wt;
             for (int wc = G.Wt; wc < G.Wt + 2 * lanes; wc++) {
-                int worst = 0;
-                for (int h = 0; h < groups; h++) {
-                    int cnt[32] = {0};
+                int total = 0;
+                for (int u0 = 0; u0 < Tg; u0 += lanes) {
+                    int cnt[32] = {0}, worst = 0;
+                    long seen[32][8]; int nseen[32] = {0};
                     for (int l = 0; l < lanes; l++) {
-                        const int u = h * lanes + l, lb = u / tpb, lt = u - lb * tpb;
+                        const int u = u0 + l, lb = u / tpb, lt = u - lb * tpb;
+                        if (u >= Tg || lb >= G.NBX * G.NBY) continue;
                         const int gx = lt / G.GY, gy = lt - gx * G.GY, lby = lb / G.NBX, lbx = lb - lby * G.NBX;
-                        if (lb >= G.NBX * G.NBY) continue;
                         const long a = (long)(lby * B + gy * TY) * wc + lbx * B + gx * TX;
-                        cnt[a & (lanes - 1)]++;
+                        const int bank = (int)(a & (lanes - 1));
+                        bool dup = false;                                  // lanes reading the same word share a wavefront
+                        for (int k = 0; k < nseen[bank]; k++) dup |= seen[bank][k] == a;
+                        if (!dup) { if (nseen[bank] < 8) seen[bank][nseen[bank]++] = a; cnt[bank]++; }
                     }
                     for (int k = 0; k < lanes; k++) worst = cnt[k] > worst ? cnt[k] : worst;
+                    total += worst;
                 }
-                if (best < 0 || worst < best) { best = worst; bestw = wc; }
+                if (best < 0 || total < best) { best = total; bestw = wc; }
             }
             if (plane == 0) G.Wc = bestw; else G.Wv = bestw;
         }
