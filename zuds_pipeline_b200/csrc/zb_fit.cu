@@ -811,23 +811,47 @@ int zb_launch_fit_solve(zb_ctx *ctx, cudaStream_t st)
     const size_t smp = ((size_t)n * (LU_NB + 1) + n) * sizeof(double);
     if (smp > ZB_SMEM_OPTIN) { snprintf(ctx->err, sizeof ctx->err, "normal matrix of %d rows too large for the LU panel kernel", n); return ZB_ERR_UNSUPPORTED; }
     cudaFuncSetAttribute(k_lu_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
-    for (int k0 = 0; k0 < n; k0 += LU_NB) {
-        const int nb = n - k0 < LU_NB ? n - k0 : LU_NB, rest = n - k0 - nb;
-        k_lu_panel<<<nR, LU_PT, ((size_t)(n - k0) * (LU_NB + 1) + (n - k0)) * sizeof(double), st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv, ctx->d_indx, k0); ZB_DBG("k_lu_panel");
-        ctx->launches++;
-        if (n - nb > 0) {
-            k_lu_swap_u<<<dim3((n - nb + 127) / 128, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, k0); ZB_DBG("k_lu_swap_u");
-            ctx->launches++;
-        }
-        if (rest > 0) {
-            k_lu_trail<<<dim3((rest + 31) / 32, (rest + 31) / 32, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, k0); ZB_DBG("k_lu_trail");
-            ctx->launches++;
-        }
-    }
-    const size_t sms = (size_t)5 * n * sizeof(double);
     cudaFuncSetAttribute(k_lu_subst, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
-    k_lu_subst<<<nR, LU_ST, sms, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, ctx->d_sol); ZB_DBG("k_lu_subst");
-    ctx->launches += 4;
+    // The factorisation is 3 launches per 32 columns (70 per solve at n = 735, one solve per clip iteration, 38 iterations
+    // at configs[3]): with 32 contexts the host's launch rate, not the GPU, set the pace.  The sequence depends only on
+    // (n, regions) and on workspace pointers that live as long as the configuration, so it is captured once into a
+    // graph and replayed with one launch.  ZB_LU_GRAPH=0: plain launches.
+    static int use_graph = -1;
+    if (use_graph < 0) { const char *e = getenv("ZB_LU_GRAPH"); use_graph = (e && e[0] == '0') ? 0 : 1; }
+    int nlaunch = 0;
+    auto enqueue = [&](cudaStream_t s) {
+        for (int k0 = 0; k0 < n; k0 += LU_NB) {
+            const int nb = n - k0 < LU_NB ? n - k0 : LU_NB, rest = n - k0 - nb;
+            k_lu_panel<<<nR, LU_PT, ((size_t)(n - k0) * (LU_NB + 1) + (n - k0)) * sizeof(double), s>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv, ctx->d_indx, k0);
+            nlaunch++;
+            if (n - nb > 0) { k_lu_swap_u<<<dim3((n - nb + 127) / 128, nR), 128, 0, s>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, k0); nlaunch++; }
+            if (rest > 0) { k_lu_trail<<<dim3((rest + 31) / 32, (rest + 31) / 32, nR), 256, 0, s>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, k0); nlaunch++; }
+        }
+        k_lu_subst<<<nR, LU_ST, (size_t)5 * n * sizeof(double), s>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, ctx->d_sol);
+        nlaunch++;
+    };
+    if (use_graph && !(ctx->lu_exec && ctx->lu_key[0] == n && ctx->lu_key[1] == nR)) {
+        if (ctx->lu_exec) { cudaGraphExecDestroy(ctx->lu_exec); ctx->lu_exec = NULL; }
+        // captured on the context's own stream (a legacy default stream cannot be captured); nothing runs during capture
+        cudaGraph_t g = NULL;
+        if (cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+            enqueue(ctx->stream);
+            if (cudaStreamEndCapture(ctx->stream, &g) == cudaSuccess && g) {
+                if (cudaGraphInstantiate(&ctx->lu_exec, g, 0) != cudaSuccess) ctx->lu_exec = NULL;
+                cudaGraphDestroy(g);
+            }
+        }
+        (void)cudaGetLastError();
+        ctx->lu_key[0] = n; ctx->lu_key[1] = nR;
+        nlaunch = 0;
+    }
+    if (use_graph && ctx->lu_exec) {
+        if (cudaGraphLaunch(ctx->lu_exec, st) != cudaSuccess) return zb_cuda_fail(ctx, cudaGetLastError(), "LU graph launch", __FILE__, __LINE__);
+        for (int k0 = 0; k0 < n; k0 += LU_NB) { const int nb = n - k0 < LU_NB ? n - k0 : LU_NB; nlaunch += 1 + (n - nb > 0) + (n - k0 - nb > 0); }
+        nlaunch++;                                   // kernels launched (by one graph launch)
+    } else enqueue(st);
+    ZB_DBG("LU");
+    ctx->launches += nlaunch + 3;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "fit solve", __FILE__, __LINE__);
     return ZB_OK;

@@ -253,6 +253,7 @@ extern "C" int zb_create(int device, zb_ctx **out) {
 }
 
 static void free_workspace(zb_ctx *ctx) {
+    if (ctx->lu_exec) { cudaGraphExecDestroy(ctx->lu_exec); ctx->lu_exec = NULL; }      // its nodes hold workspace pointers
     void **dptrs[] = {(void **)&ctx->d_dev, (void **)&ctx->d_min, (void **)&ctx->d_omask, (void **)&ctx->d_rdiff, (void **)&ctx->d_rnoise,
                       (void **)&ctx->d_ran, (void **)&ctx->d_fx, (void **)&ctx->d_fy, (void **)&ctx->d_kvec, (void **)&ctx->d_ren,
                       (void **)&ctx->d_cells, (void **)&ctx->d_stamps, (void **)&ctx->d_vec, (void **)&ctx->d_kref, (void **)&ctx->d_gram,

@@ -154,6 +154,7 @@ struct zb_ctx {
     double  *d_kaks;             // [region][blocks+1]  sum |K| per block in the reference's tap order
     void    *d_ktap;             // [region][blocks+1][fw*fwp] 16-byte taps (K double, K^2 float), reversed, rows padded: k_convolve's operand
     int     *d_tilectr;          // tile counter of k_convolve's dynamic schedule
+    cudaGraphExec_t lu_exec; int lu_key[2];       // the LU launch sequence of zb_launch_fit_solve as a graph, for (mat_size, n_regions)
     unsigned char conv_geom[512]; int conv_geom_key[6]; int conv_geom_bytes;   // cached tile shape of k_convolve (zb_conv.cu)
     int      n_sm;               // multiprocessors of the device (grid of the persistent kernels)
     double  *d_kstat;            // per-region: ksum, aks
