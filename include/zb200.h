@@ -222,6 +222,26 @@ int zb_background_estimate(zb_ctx *ctx, const float *data /* device */, const vo
 int zb_background_estimate_host(zb_ctx *ctx, const float *data /* host */, const void *mask /* host */, int mask_dtype,
                                 long long n, double *bkg, double *bkgstd);
 
+/* The same estimate for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * It takes no context and calls no cudaMalloc / cudaFree / cudaMallocHost or any allocating library routine: the
+ * selection state (histograms, prefixes, counts) lives in a static device array of ZB_BKG_STATIC_SCRATCH_BYTES that
+ * every GPU loading the library holds until exit.  Runs on the calling thread's CURRENT device; does not synchronise.
+ *   data, mask   device pointers as for zb_background_estimate (mask may be NULL)
+ *   n            number of pixels, at most ZB_BKG_STATIC_MAX_PIXELS (the scratch's histogram counters are 32-bit);
+ *                a larger n is refused with ZB_ERR_PARAM and a message, before anything is launched
+ *   out          DEVICE buffer of two doubles: out[0] = bkg, out[1] = bkgstd, complete when `stream` reaches this point
+ *   stream       a cudaStream_t, or NULL for the legacy default stream (ZB_STREAM_OWN is refused: there is no context)
+ *   msg, msglen  optional buffer for the error text (what zb_last_error is for the context calls)
+ * All calls on a device share the one array, and a call finds the previous call's contents in it: every call clears
+ * the state on `stream` first, and calls that OVERLAP on the GPU (streams not ordered with each other) race — order
+ * them.  The first call on a device resolves the array's device address and loads the kernels; make it outside
+ * graph capture. */
+#define ZB_BKG_STATIC_SCRATCH_BYTES 17408
+#define ZB_BKG_STATIC_MAX_PIXELS    (1LL << 31)
+int zb_background_estimate_static(const float *data /* device */, const void *mask /* device */, int mask_dtype, long long n,
+                                  double *out /* device [2] */, void *stream, char *msg, int msglen);
+
 /* ------------------------------------------------------------------------------------------
  * The other elementwise steps zuds does around the hotpants call, on DEVICE pointers so that a
  * caller holding its images in HBM never returns to the host between them, zb_background_estimate and zb_subtract.

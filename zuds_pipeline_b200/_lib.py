@@ -29,7 +29,7 @@ EXPORTS = ("zb_version", "zb_params_default", "zb_params_check", "zb_sizes_of", 
            "zb_tile_normal_import", "zb_tile_solve", "zb_tile_sig_export", "zb_tile_sig_import", "zb_tile_clip",
            "zb_tile_convolve", "zb_tile_finish",
            # wrapper pre/post steps (zuds.utils.quick_background_estimate, mask OR / boolean / bit 17, rms <-> weight)
-           "zb_background_estimate", "zb_background_estimate_host",
+           "zb_background_estimate", "zb_background_estimate_host", "zb_background_estimate_static",
            "zb_mask_combine", "zb_mask_flag_sentinel", "zb_rms_from_weight", "zb_weight_from_rms",
            # alignment of the reference onto the science grid (what zuds runs SWarp for)
            "zb_align_lanczos3", "zb_align_mask")
@@ -75,6 +75,7 @@ def load():
     dp = C.POINTER(C.c_double)
     lib.zb_background_estimate.argtypes = [vp, vp, vp, C.c_int, C.c_longlong, dp, dp, vp]
     lib.zb_background_estimate_host.argtypes = [vp, vp, vp, C.c_int, C.c_longlong, dp, dp]
+    lib.zb_background_estimate_static.argtypes = [vp, vp, C.c_int, C.c_longlong, vp, vp, C.c_char_p, C.c_int]
     lib.zb_mask_combine.argtypes = [vp, vp, C.c_int, vp, C.c_int, C.c_longlong, C.c_int, vp, vp, vp]
     lib.zb_mask_flag_sentinel.argtypes = [vp, vp, vp, C.c_longlong, C.c_float, C.c_int, vp]
     lib.zb_rms_from_weight.argtypes = [vp, vp, vp, vp, C.c_float, C.c_float, C.c_longlong, vp, vp]
@@ -96,6 +97,29 @@ def check_params(p):
     buf = C.create_string_buffer(512)
     rc = load().zb_params_check(C.byref(p), buf, 512)
     return rc, buf.value.decode()
+
+
+BKG_STATIC_MAX_PIXELS = 1 << 31        # ZB_BKG_STATIC_MAX_PIXELS (include/zb200.h)
+
+
+def background_estimate_static(data, mask, out, n=None, stream=None):
+    """zb_background_estimate_static: the background estimate without any allocation and without a context, on the
+    current CUDA device.  ``data`` (float32), ``mask`` (uint8/int16/int32 or None) and ``out`` (float64, two elements)
+    are CUDA tensors; only their data_ptr() crosses the C ABI and nothing is allocated here either.  ``n`` overrides
+    the pixel count (to probe the size limit).  The result lands in ``out`` in stream order; no synchronisation."""
+    import torch
+    assert data.is_cuda and data.is_contiguous() and data.dtype == torch.float32
+    assert out.is_cuda and out.is_contiguous() and out.dtype == torch.float64 and out.numel() >= 2
+    dt = 0
+    if mask is not None:
+        assert mask.is_cuda and mask.is_contiguous() and mask.numel() == data.numel()
+        dt = MASK_DTYPES[str(mask.dtype).replace("torch.", "")]
+    s = torch.cuda.current_stream(data.device).cuda_stream if stream is None else stream.cuda_stream
+    buf = C.create_string_buffer(256)
+    rc = load().zb_background_estimate_static(C.c_void_p(data.data_ptr()), None if mask is None else C.c_void_p(mask.data_ptr()), dt,
+                                              data.numel() if n is None else n, C.c_void_p(out.data_ptr()), C.c_void_p(s), buf, 256)
+    if rc != 0:
+        raise ZbError(rc, buf.value.decode())
 
 
 class Result:

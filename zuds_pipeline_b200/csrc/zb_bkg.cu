@@ -192,3 +192,86 @@ extern "C" int zb_background_estimate_host(zb_ctx *ctx, const float *data, const
     if (mask) cudaMemcpyAsync(ctx->d_stage[4], mask, mb, cudaMemcpyHostToDevice, ctx->stream);
     return bkg_run(ctx, (const float *)ctx->d_stage[0], mask ? ctx->d_stage[4] : NULL, mask_dtype, n, bkg, bkgstd, ctx->stream);
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// zb_background_estimate_static — the same estimate for callers that may not allocate (code under CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The radix-selection state that bkg_run keeps in a lazily cudaMalloc'ed BkState lives here in a
+// file-scope device array that every GPU loading the library holds until exit; no context, no pinned host buffer, no
+// synchronisation: the two results are written to a device buffer of the caller, ordered on the caller's stream.
+// In host code the array's NAME is only a host-side stand-in for the symbol, not a device address (a kernel handed it
+// faults, or silently uses the wrong memory where the GPU can reach host memory): the device address is obtained once
+// per device with cudaGetSymbolAddress, with that device current, and that pointer is what the kernels get.
+// Every call on a device shares the array and finds the previous call's contents in it: the whole state is cleared on
+// the stream at the start of each call, and two calls that overlap on the GPU (different streams without an ordering
+// between them) race.
+#include <mutex>
+
+static __device__ __align__(256) unsigned char g_bkg_static[ZB_BKG_STATIC_SCRATCH_BYTES];
+static_assert(sizeof(BkState) <= ZB_BKG_STATIC_SCRATCH_BYTES, "the static scratch array is smaller than the selection state");
+
+#define BK_MAX_DEVICES 64
+static std::mutex g_bkg_static_mu;
+static BkState *g_bkg_static_ptr[BK_MAX_DEVICES];      // device address of g_bkg_static on each device, NULL until resolved
+
+__global__ void k_bkg_emit(const BkState *__restrict__ st, double *__restrict__ out)
+{
+    out[0] = st->bkg;
+    out[1] = 1.4826 * st->mad;          // the one double operation of zuds/utils.py:52 (this file is built with -fmad=false)
+}
+
+static int bkg_static_fail(char *msg, int msglen, int rc, const char *what, cudaError_t e)
+{
+    if (msg && msglen > 0) {
+        if (e != cudaSuccess) snprintf(msg, (size_t)msglen, "%s: %s", what, cudaGetErrorString(e));
+        else snprintf(msg, (size_t)msglen, "%s", what);
+    }
+    return rc;
+}
+
+extern "C" int zb_background_estimate_static(const float *data, const void *mask, int mask_dtype, long long n,
+                                             double *out, void *stream, char *msg, int msglen)
+{
+    if (msg && msglen > 0) msg[0] = 0;
+    if (!data || !out || n < 0) return bkg_static_fail(msg, msglen, ZB_ERR_PARAM, "zb_background_estimate_static: null data/out pointer or negative n", cudaSuccess);
+    if (n > ZB_BKG_STATIC_MAX_PIXELS) {
+        char buf[192];
+        snprintf(buf, sizeof buf, "zb_background_estimate_static: %lld pixels exceed the maximum of %lld the static scratch's 32-bit counters are sized for",
+                 n, (long long)ZB_BKG_STATIC_MAX_PIXELS);
+        return bkg_static_fail(msg, msglen, ZB_ERR_PARAM, buf, cudaSuccess);
+    }
+    if (mask && !(mask_dtype == ZB_MASK_U8 || mask_dtype == ZB_MASK_I16 || mask_dtype == ZB_MASK_I32))
+        return bkg_static_fail(msg, msglen, ZB_ERR_PARAM, "zb_background_estimate_static: bad mask dtype", cudaSuccess);
+    if (stream == ZB_STREAM_OWN) return bkg_static_fail(msg, msglen, ZB_ERR_PARAM, "zb_background_estimate_static: ZB_STREAM_OWN needs a context; pass a stream (NULL = legacy default stream)", cudaSuccess);
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return bkg_static_fail(msg, msglen, ZB_ERR_CUDA, "cudaGetDevice", e);
+    if (dev < 0 || dev >= BK_MAX_DEVICES) return bkg_static_fail(msg, msglen, ZB_ERR_UNSUPPORTED, "zb_background_estimate_static: device ordinal out of range", cudaSuccess);
+    BkState *S;
+    {
+        // set-up, once per device, with that device current (it is: the calling thread's current device)
+        std::lock_guard<std::mutex> lk(g_bkg_static_mu);
+        if (!g_bkg_static_ptr[dev]) {
+            void *p = NULL;
+            e = cudaGetSymbolAddress(&p, g_bkg_static);
+            if (e != cudaSuccess || !p) return bkg_static_fail(msg, msglen, ZB_ERR_CUDA, "cudaGetSymbolAddress(g_bkg_static)", e);
+            g_bkg_static_ptr[dev] = (BkState *)p;
+        }
+        S = g_bkg_static_ptr[dev];
+    }
+    cudaStream_t st = stream ? (cudaStream_t)stream : cudaStreamLegacy;
+    e = cudaMemsetAsync(S, 0, sizeof(BkState), st);            // prefixes, ranks, counts, ticket and histograms start at zero
+    if (e != cudaSuccess) return bkg_static_fail(msg, msglen, ZB_ERR_CUDA, "cudaMemsetAsync of the static scratch", e);
+    long long want = (n + BK_NT * 16 - 1) / (BK_NT * 16);
+    const int grid = (int)(want < 1 ? 1 : (want > 148 * 8 ? 148 * 8 : want));
+    k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mask_dtype, n, S, 0, 53, 11, 1, 0);
+    k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mask_dtype, n, S, 0, 42, 11, 0, 0);
+    k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mask_dtype, n, S, 0, 32, 10, 0, 1);
+    k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mask_dtype, n, S, 1, 53, 11, 1, 0);
+    k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mask_dtype, n, S, 1, 42, 11, 0, 0);
+    k_bkg_pass<<<grid, BK_NT, 0, st>>>(data, mask, mask_dtype, n, S, 1, 32, 10, 0, 1);
+    k_bkg_emit<<<1, 1, 0, st>>>(S, out);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return bkg_static_fail(msg, msglen, ZB_ERR_CUDA, "zb_background_estimate_static: kernel launch", e);
+    return ZB_OK;
+}
