@@ -287,6 +287,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t *b, unsigned parity) {
     asm volatile("{\n\t.reg .pred P1;\n\tLAB_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t@P1 bra DONE;\n\tbra LAB_WAIT;\n\tDONE:\n\t}"
                  ::"r"(smem_u32(b)), "r"(parity) : "memory");
 }
+// The waits of the roles that run ahead of the multiply (producer) or behind it (epilogue) last tens of microseconds; a
+// tight try_wait loop there was a third of all instructions the CTA issued (ncu: 31 M + 28 M executions of the two
+// loops against 554 M in total), on the schedulers the FMA warps need.  These sleep between polls instead.
+__device__ __forceinline__ void mbar_wait_idle(uint64_t *b, unsigned parity) {
+    for (;;) {
+        unsigned done;
+        asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.u32 %0, 1, 0, P1;\n\t}"
+                     : "=r"(done) : "r"(smem_u32(b)), "r"(parity) : "memory");
+        if (done) return;
+#ifndef CONV_WAIT_SPIN
+        __nanosleep(400);
+#endif
+    }
+}
 __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *tm, int x, int y, uint64_t *bar) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
                  ::"r"(smem_u32(dst)), "l"(tm), "r"(x), "r"(y), "r"(smem_u32(bar)) : "memory");
@@ -502,7 +516,7 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                 TileRef T; ZbRegion R;
                 if (t < G.n_tiles && !conv_tile(D, G, t, T, R)) continue;
                 const unsigned par = it & 1;
-                if (lane == 0) mbar_wait(raw_empty, par ^ 1);
+                if (lane == 0) mbar_wait_idle(raw_empty, par ^ 1);
                 __syncwarp();
                 if (t >= G.n_tiles) {                                              // no more work: tell the other roles and leave
                     if (lane == 0) { s_tile[it & 3] = -1; mbar_arrive(raw_full); }
@@ -535,7 +549,7 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
                     if (lane == 0) mbar_arrive(raw_full);
                 }
                 if (lane == 0) {
-                    mbar_wait(k_empty, par ^ 1);
+                    mbar_wait_idle(k_empty, par ^ 1);
                     int nex = 0;
                     for (int lb = 0; lb < NB; lb++) { const int lby = lb / NBX, lbx = lb - lby * NBX; nex += (T.bx0 + lbx < T.nbx && T.by0 + lby < T.nby); }
                     mbar_expect_tx(k_full, (unsigned)(nex * G.kstride * sizeof(KTap)));
@@ -563,7 +577,7 @@ k_convolve(const __grid_constant__ CUtensorMap tm_img, const __grid_constant__ C
             const bool mask_out = D->p.kf_spread_mask2 >= 0;
             for (int it = 0;; it++) {
                 const unsigned par = it & 1;
-                mbar_wait(res_full, par);
+                mbar_wait_idle(res_full, par);
                 const int t = s_tile[it & 3];
                 if (t < 0) break;
                 TileRef T; ZbRegion R;
