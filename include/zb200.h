@@ -122,6 +122,8 @@ typedef struct zb_region_info {
     double  dmean, dsige, dsig;                       /* DMEANnn DSIGEnn DSIGnn */
     double  dmeano, dsigeo, dsigo;                    /* DMEANOnn DSIGEOnn DSIGOnn */
     double  nscalo;                                   /* NSCALOnn (sd/nmean) */
+    double  t_merit, i_merit;                         /* -c b only: check_stamps' merit of each direction (alard.c:483-724;
+                                                         the "Result : merit" lines of main.c:1037,1053), else 0 */
 } zb_region_info;
 
 /* Per-stamp bookkeeping = hotpants/globals.h:1-24 minus the big arrays (what -savexy dumps). */

@@ -416,11 +416,13 @@ static int psf_centers(reg_t *R, stamp_t *s, const float *img, int xLen, int yLe
 }
 
 /* functions.c:187-361 buildStamps (getCenters = 1 branch) + cutStamp :363-388 */
+/* phase: 1 = the statistics half of buildStamps (functions.c:207-249), 2 = the sub-stamp search half (:251-330),
+   3 = both.  With -c b the reference runs both statistics of a grid cell before either search. */
 static void build_stamp(reg_t *R, stamp_t *s, const float *img, int sXMin, int sXMax, int sYMin, int sYMax,
-                        int rXBMin, int rYBMin, double hiThresh, int bbit1, int bbit2) {
+                        int rXBMin, int rYBMin, double hiThresh, int bbit1, int bbit2, int phase) {
     int sPixX = sXMax - sXMin + 1, sPixY = sYMax - sYMin + 1;
     int xMin = sXMin - rXBMin, yMin = sYMin - rYBMin, xMax = sXMax - rXBMin, yMax = sYMax - rYBMin, i, j;
-    if (s->nss == 0) {
+    if ((phase & 1) && s->nss == 0) {
         float *area = (float *)calloc((size_t)sPixX * sPixY, sizeof(float));
         stats_t st;
         for (j = yMin; j <= yMax; j++)
@@ -434,7 +436,7 @@ static void build_stamp(reg_t *R, stamp_t *s, const float *img, int sXMin, int s
         s->sd = st.sd; s->fwhm = st.fwhm; s->lfwhm = st.lfwhm;
         free(area);
     }
-    psf_centers(R, s, img, sPixX, sPixY, hiThresh, bbit1, bbit2);
+    if (phase & 2) psf_centers(R, s, img, sPixX, sPixY, hiThresh, bbit1, bbit2);
 }
 
 /* ------------------------------------------------------------------- basis */
@@ -825,6 +827,68 @@ static int fit_kernel(reg_t *R, stamp_t *st, int nS, const float *imRef, const f
     return 0;
 }
 
+/* alard.c:483-724 check_stamps (-c b): every stamp is fitted alone with a constant kernel (the leading
+   (nCompKer+1)^2 block of its own normal equations), stamps whose kernel sum lies more than kerSigReject sigma
+   from the clipped mean are left out, the rest get one trial global fit, and the clipped mean of their
+   getStampSig figures divided by the kernel sum at region pixel (0,0) is the merit of this direction.
+   Figure of merit 'v' only (sig2 = sig3 = 0 then, alard.c:1082-1083,1127).  A direction without stamps returns
+   666 (what the reference's fall-through yields for it, after reading unset memory on the way). */
+static double check_stamps(reg_t *R, stamp_t *st, int nS, const float *imRef, const float *imNoise) {
+    int nK = R->sz.n_comp_ker, nC = nK + 2, nComps = nK + 1, n = R->sz.mat_size;
+    int i, im, jm, nks = 0, ntest = 0, mcnt1 = 0, mcnt2 = 0, *indx;
+    double **cm, *cv, kmean = 0, kstdev = 0, merit1 = 0, merit2 = 0, sd1 = 0, sd2 = 0, **M, *tsol, *norm, *dif;
+    float *ks, *m1, *m2; stamp_t *ts;
+    if (nS <= 0) return 666;
+    ks = (float *)calloc((size_t)nS, sizeof(float));
+    norm = (double *)calloc((size_t)nS, sizeof(double)); dif = (double *)calloc((size_t)nS, sizeof(double));
+    cm = (double **)malloc((size_t)nC * sizeof(double *));
+    for (i = 0; i < nC; i++) cm[i] = (double *)calloc((size_t)nC, sizeof(double));
+    cv = (double *)calloc((size_t)nC, sizeof(double));
+    indx = (int *)calloc((size_t)(n > nC ? n : nC) + 2, sizeof(int));
+    for (i = 0; i < nS; i++) {
+        stamp_t *s = &st[i];
+        for (im = 1; im <= nComps; im++) {
+            cv[im] = s->scprod[im];
+            for (jm = 1; jm <= im; jm++) { cm[im][jm] = MAT(s, nC, im, jm); cm[jm][im] = cm[im][jm]; }
+        }
+        lu_decompose(cm, nComps, indx);
+        lu_backsub(cm, nComps, indx, cv);
+        norm[i] = cv[1];
+        ks[nks++] = (float)cv[1];
+    }
+    hp_oracle_sigma_clip(ks, nks, &kmean, &kstdev, 10, R->p->stat_sig);
+    for (i = 0; i < nS; i++) { dif[i] = fabs((norm[i] - kmean) / kstdev); if (dif[i] < R->p->ker_sig_reject) ntest++; }
+    ts = (stamp_t *)calloc((size_t)ntest + 1, sizeof(stamp_t));
+    for (i = 0, ntest = 0; i < nS; i++) if (dif[i] < R->p->ker_sig_reject) ts[ntest++] = st[i];
+    M = (double **)malloc((size_t)(n + 1) * sizeof(double *));
+    for (i = 0; i <= n; i++) M[i] = (double *)calloc((size_t)n + 1, sizeof(double));
+    R->wxy = (double **)malloc((size_t)nS * sizeof(double *));
+    for (i = 0; i < nS; i++) R->wxy[i] = (double *)calloc((size_t)R->sz.n_comp, sizeof(double));
+    tsol = (double *)calloc((size_t)R->sz.n_comp_total + 1, sizeof(double));
+    build_matrix(R, ts, ntest, M);
+    build_scprod(R, ts, ntest, imRef, tsol);
+    lu_decompose(M, n, indx);
+    lu_backsub(M, n, indx, tsol);
+    kmean = make_kernel(R, 0, 0, tsol);
+    m1 = (float *)calloc((size_t)ntest + 1, sizeof(float)); m2 = (float *)calloc((size_t)ntest + 1, sizeof(float));
+    for (i = 0; i < ntest; i++) {
+        double sig1 = stamp_sig(R, &ts[i], tsol, imNoise);
+        if (sig1 != -1 && sig1 <= MAXVAL) m1[mcnt1++] = (float)sig1;
+        m2[mcnt2++] = 0.f;                                 /* sig2 and sig3 stay 0 with -fom v */
+    }
+    hp_oracle_sigma_clip(m1, mcnt1, &merit1, &sd1, 10, R->p->stat_sig);
+    hp_oracle_sigma_clip(m2, mcnt2, &merit2, &sd2, 10, R->p->stat_sig);
+    merit1 /= kmean; merit2 /= kmean;
+    for (i = 0; i <= n; i++) free(M[i]);
+    for (i = 0; i < nS; i++) free(R->wxy[i]);
+    for (i = 0; i < nC; i++) free(cm[i]);
+    free(M); free(R->wxy); R->wxy = NULL; free(cm); free(cv); free(indx); free(ks); free(norm); free(dif);
+    free(ts); free(tsol); free(m1); free(m2);
+    if (mcnt1 > 0) return merit1;
+    if (mcnt2 > 0) return merit2;
+    return 666;
+}
+
 /* ----------------------------------------------------------- convolution */
 
 /* alard.c:1249-1344 spatial_convolve: one kernel per kcStep x kcStep block, realised at
@@ -934,11 +998,12 @@ int hp_oracle_subtract(const zb_params *p,
                        float *diff, float *noise, int32_t *out_mask,
                        zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps_out) {
     zb_sizes sz; reg_t R; int ir, jr, nR = 0, nK, nC, nvec, npix, fw, k, l;
+    const int both = (p->force_convolve == 'b');
     int convTmpl = (p->force_convolve == 't');
     float tU = p->t_uthresh - p->t_pedestal, tUK = p->t_ukthresh - p->t_pedestal, tL = p->t_lthresh - p->t_pedestal;
     float iU = p->i_uthresh - p->i_pedestal, iUK = p->i_ukthresh - p->i_pedestal, iL = p->i_lthresh - p->i_pedestal;
 
-    if (p->force_convolve != 't' && p->force_convolve != 'i') return ZB_ERR_UNSUPPORTED;
+    if (p->force_convolve != 't' && p->force_convolve != 'i' && !both) return ZB_ERR_UNSUPPORTED;
     if (p->fig_merit != 'v' || p->use_full_ss) return ZB_ERR_UNSUPPORTED;
     if (p->n_ksstamps > ZB_MAX_KSS || p->ngauss > ZB_MAX_GAUSS) return ZB_ERR_UNSUPPORTED;
     hp_oracle_sizes(p, &sz);
@@ -970,14 +1035,14 @@ int hp_oracle_subtract(const zb_params *p,
         int xBufLo = rXMin - bx0, yBufLo = rYMin - by0;
         int rpx = bx1 - bx0 + 1, rpy = by1 - by0 + 1, n = rpx * rpy, nS = 0, attempt, is, x, y;
         float *t, *i_, *o, *e, *nz; int *m, *mis, *mts, *cmask, *omask_other;
-        stamp_t *st; double *sol, ksum, inv1, sum; stats_t sd_, sn_, sdm, snm;
+        stamp_t *st, *st2 = NULL; int nS2 = 0; double tMerit = 0, iMerit = 0;   /* -c b: st = template stamps, st2 = image stamps */
+        double *sol, ksum, inv1, sum; stats_t sd_, sn_, sdm, snm;
         const float *imConv, *imRef; float *noiseOut; int iters = 0, singular = 0, nskip = 0;
         double meansig = 0, scatter = 0, meansigF = 0, scatterF = 0, x2norm; int nx2norm;
 
         memset(ri, 0, sizeof *ri);
         ri->rx_min = rXMin; ri->rx_max = rXMax; ri->ry_min = rYMin; ri->ry_max = rYMax;
         ri->bx_min = bx0; ri->bx_max = bx1; ri->by_min = by0; ri->by_max = by1;
-        ri->conv_template = convTmpl;
         R.rpx = rpx; R.rpy = rpy;
         t = (float *)malloc((size_t)n * 4); i_ = (float *)malloc((size_t)n * 4);
         o = (float *)malloc((size_t)n * 4); e = (float *)malloc((size_t)n * 4); nz = (float *)malloc((size_t)n * 4);
@@ -1019,43 +1084,78 @@ int hp_oracle_subtract(const zb_params *p,
 
         /* stamp search with one retry at a lower threshold, main.c:829-998 */
         st = (stamp_t *)calloc((size_t)sz.n_stamps + 1, sizeof(stamp_t));
+        if (both) st2 = (stamp_t *)calloc((size_t)sz.n_stamps + 1, sizeof(stamp_t));
         R.kft = p->ker_fit_thresh;
         for (attempt = 1; attempt <= 2; attempt++) {
             int flag = 0, gk, gl;
-            nS = 0;
+            nS = 0; nS2 = 0;
             for (gl = 0; gl < sz.nstamp_y; gl++)
                 for (gk = 0; gk < sz.nstamp_x; gk++) {
                     int sXMin = bx0 + gk * rpx / sz.nstamp_x, sYMin = by0 + gl * rpy / sz.nstamp_y;
                     int sXMax = imin_(sXMin + sz.fw_stamp - 1, bx1), sYMax = imin_(sYMin + sz.fw_stamp - 1, by1);
                     stamp_t *s = &st[nS];
                     s->sscnt = s->nss = 0; s->chi2 = 0.0;       /* other stats persist in a reused slot */
-                    if (convTmpl) build_stamp(&R, s, t, sXMin, sXMax, sYMin, sYMax, bx0, by0, tUK, ZB_FLAG_T_BAD, ZB_FLAG_T_SKIP);
-                    else          build_stamp(&R, s, i_, sXMin, sXMax, sYMin, sYMax, bx0, by0, iUK, ZB_FLAG_I_BAD, ZB_FLAG_I_SKIP);
+                    if (both) {       /* functions.c:207-330: template statistics, image statistics, template search, image search */
+                        stamp_t *s2 = &st2[nS2];
+                        s2->sscnt = s2->nss = 0; s2->chi2 = 0.0;
+                        build_stamp(&R, s, t, sXMin, sXMax, sYMin, sYMax, bx0, by0, tUK, ZB_FLAG_T_BAD, ZB_FLAG_T_SKIP, 1);
+                        build_stamp(&R, s2, i_, sXMin, sXMax, sYMin, sYMax, bx0, by0, iUK, ZB_FLAG_I_BAD, ZB_FLAG_I_SKIP, 1);
+                        build_stamp(&R, s, t, sXMin, sXMax, sYMin, sYMax, bx0, by0, tUK, ZB_FLAG_T_BAD, ZB_FLAG_T_SKIP, 2);
+                        build_stamp(&R, s2, i_, sXMin, sXMax, sYMin, sYMax, bx0, by0, iUK, ZB_FLAG_I_BAD, ZB_FLAG_I_SKIP, 2);
+                        if (s2->nss > 0) nS2++;
+                    }
+                    else if (convTmpl) build_stamp(&R, s, t, sXMin, sXMax, sYMin, sYMax, bx0, by0, tUK, ZB_FLAG_T_BAD, ZB_FLAG_T_SKIP, 3);
+                    else               build_stamp(&R, s, i_, sXMin, sXMax, sYMin, sYMax, bx0, by0, iUK, ZB_FLAG_I_BAD, ZB_FLAG_I_SKIP, 3);
                     if (s->nss > 0) nS++;
                 }
             if ((nS / (float)sz.n_stamps) < p->min_frac_good_stamps) flag = 1;
+            if (both && (nS2 / (float)sz.n_stamps) < p->min_frac_good_stamps) flag = 1;     /* main.c:921-924 */
             if (!flag) break;
             if (attempt == 1 && p->scale_fit_thresh < 1.f) {   /* stamps are re-allocated (zeroed) only here */
                 R.kft *= p->scale_fit_thresh;
                 memset(st, 0, ((size_t)sz.n_stamps + 1) * sizeof(stamp_t));
+                if (both) memset(st2, 0, ((size_t)sz.n_stamps + 1) * sizeof(stamp_t));
                 for (l = n; l--;) m[l] &= ~0xa00;
                 ri->flags |= ZB_REGION_RETRIED;
             }
         }
+        if (both) {
+            /* main.c:1026-1072: fill both sets, merit of each direction, the smaller one wins (:1076-1085) */
+            stamp_t *sets[2]; int cnt[2], d;
+            sets[0] = st; sets[1] = st2; cnt[0] = nS; cnt[1] = nS2;
+            for (d = 0; d < 2 && (nS > 0 || nS2 > 0); d++) {
+                for (is = 0; is < cnt[d]; is++) {
+                    stamp_t *s = &sets[d][is];
+                    s->vec = (double *)calloc((size_t)nvec * npix, sizeof(double));
+                    s->kref = (double *)calloc((size_t)npix, sizeof(double));
+                    s->mat = (double *)calloc((size_t)nC * nC, sizeof(double));
+                    s->scprod = (double *)calloc((size_t)nC, sizeof(double));
+                    s->sscnt = 0; fill_stamp(&R, s, d == 0 ? t : i_, d == 0 ? i_ : t);
+                }
+                if (d == 0) tMerit = check_stamps(&R, st, nS, i_, o);
+                else        iMerit = check_stamps(&R, st2, nS2, t, o);
+            }
+            convTmpl = (tMerit < iMerit);
+            ri->t_merit = tMerit; ri->i_merit = iMerit;
+            if (!convTmpl) { stamp_t *q = st; st = st2; st2 = q; d = nS; nS = nS2; nS2 = d; }
+            for (is = 0; is < nS2; is++) { free(st2[is].vec); free(st2[is].kref); free(st2[is].mat); free(st2[is].scprod); }
+            free(st2); st2 = NULL;
+        }
+        ri->conv_template = convTmpl;
         ri->n_stamps = nS;
-        if (nS == 0) {          /* main.c:1002-1009: region silently skipped */
+        if (nS == 0) {          /* main.c:1002-1009: region silently skipped (with -c b: the winning direction has no stamps) */
             ri->flags |= ZB_REGION_SKIPPED;
             free(t); free(i_); free(o); free(e); free(nz); free(m); free(mis); free(mts); free(st);
             continue;
         }
-        for (is = 0; is < nS; is++) {
+        imConv = convTmpl ? t : i_; imRef = convTmpl ? i_ : t;
+        if (!both) for (is = 0; is < nS; is++) {
             st[is].vec = (double *)calloc((size_t)nvec * npix, sizeof(double));
             st[is].kref = (double *)calloc((size_t)npix, sizeof(double));
             st[is].mat = (double *)calloc((size_t)nC * nC, sizeof(double));
             st[is].scprod = (double *)calloc((size_t)nC, sizeof(double));
+            st[is].sscnt = 0; fill_stamp(&R, &st[is], imConv, imRef);
         }
-        imConv = convTmpl ? t : i_; imRef = convTmpl ? i_ : t;
-        for (is = 0; is < nS; is++) { st[is].sscnt = 0; fill_stamp(&R, &st[is], imConv, imRef); }
         sol = (double *)calloc((size_t)sz.n_comp_total + 1, sizeof(double));
         fit_kernel(&R, st, nS, imRef, imConv, o, sol, &meansig, &scatter, &nskip, &iters, &singular);
         if (singular) ri->flags |= ZB_REGION_SINGULAR;

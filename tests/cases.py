@@ -24,6 +24,7 @@ class Case:
     use_mask: bool = True         # False: drop -imi
     replace: dict = dataclasses.field(default_factory=dict)   # flag -> new value in the zuds command
     flags: tuple = ()             # bare switches appended to the command (-okn, -convvar)
+    swap: bool = False            # exchange the roles of the two images (the "template" is then the broader one)
 
 
 SMALL = [
@@ -65,6 +66,22 @@ EXTRA = [
     Case("kcs7", (384, 400), 2.0, 1, {"ko": 2, "kcs": 7}, dict(nstars=300, bad_frac=2e-4)),
 ]
 
+# -c b: hotpants' own default, the direction chosen per region by check_stamps (alard.c:483-724).  The synthetic
+# reference is the sharper image, so the template wins unless the images are swapped.
+BOTH = [
+    Case("dir_b_2x2", (448, 480), 2.0, 2, {}, dict(nstars=500, bad_frac=2e-4), replace={"-c": "b"}),
+    Case("dir_b_swapped", (400, 416), 2.4, 1, {"ko": 1, "bgo": 1}, dict(nstars=300, bad_frac=2e-4),
+         replace={"-c": "b"}, swap=True),
+    # no rms maps, 2 sub-stamps per stamp, stricter kernel-sum clip: stamps are dropped from the trial fit
+    Case("dir_b_gain_3x1", (420, 600), 2.0, 1, {"ko": 2, "tg": 6.0, "ig": 6.0, "tr": 8.0, "ir": 9.0, "ks": 1.2, "nss": 2},
+         dict(nstars=700, bad_frac=2e-4), use_rms=False, replace={"-c": "b", "-nry": 3}),
+    # science PSF narrower than the reference's on the left, broader on the right: the two regions go opposite ways
+    Case("dir_b_mixed_2x1", (400, 640), 2.4, 1, {"ko": 1}, dict(nstars=600, bad_frac=2e-4, ref_sharpness=1.0, seeing_gradient=0.35),
+         replace={"-c": "b", "-nrx": 2}),
+    # too few stamps at the first threshold in both directions: the one-shot retry re-searches both sets (main.c:921-995)
+    Case("dir_b_retry", (512, 512), 3.0, 1, {"ko": 0, "ft": 1900.0}, dict(nstars=300, bad_frac=1e-4), replace={"-c": "b"}),
+]
+
 TINY_FULL = Case("tiny_full", (200, 208), 1.3, 1, {"ko": 1}, dict(nstars=120, bad_frac=2e-4))
 
 # BASELINE.json configs at full size (GPU tests / bench only)
@@ -79,7 +96,10 @@ FULL = {
 
 
 def make_pair(case):
-    return synth.make_pair(case.seed, case.shape, case.seeing, **case.synth_kws)
+    pair = synth.make_pair(case.seed, case.shape, case.seeing, **case.synth_kws)
+    if case.swap:
+        pair = dataclasses.replace(pair, sci=pair.ref, ref=pair.sci, sci_rms=pair.ref_rms, ref_rms=pair.sci_rms)
+    return pair
 
 
 def command(case, pair, names=None, exe="hotpants"):

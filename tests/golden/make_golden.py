@@ -7,13 +7,15 @@ synthetic cases of tests/cases.py.  Run in the build container:
 What is stored per case (golden_<name>.json): the exact command line, a sha256 of the inputs (so a
 host whose numpy produces different synthetic pixels is detected, not mis-compared), sha256 of the
 reference's diff / noise / 16-bit mask images, the -hki kernel table, the -savexy stamp centres,
-every per-region header keyword, and an 8x8 centre patch of diff and noise (the same kind of
+every per-region header keyword, for -c b cases the two merits per region that the reference prints
+("Result : merit = %.3f", main.c:1037,1053), and an 8x8 centre patch of diff and noise (the same kind of
 known-answer check the reference's own test uses, zuds/tests/suite/test_sub.py:8-36).
 tiny_full.npz additionally carries complete inputs and outputs of one very small case.
 """
 import hashlib
 import json
 import os
+import re
 import sys
 
 import numpy as np
@@ -72,12 +74,14 @@ def golden_of(case):
                        if k in ("NGAUSS", "FWKERN", "CKORDER", "BGORDER", "KERINFO", "EXTNAME")
                        or k.startswith("DGAUSS") or k.startswith("SGAUSS")},
     }
+    if "-c b" in ref.cmd:
+        g["merits"] = re.findall(r"Result : merit = (\S+)", ref.stderr)      # template, image per region that has stamps
     return g, pair, ref
 
 
 def main():
     only = set(sys.argv[1:])
-    for case in CS.SMALL + CS.EXTRA + [CS.TINY_FULL]:
+    for case in CS.SMALL + CS.EXTRA + CS.BOTH + [CS.TINY_FULL]:
         if only and case.name not in only:
             continue
         g, pair, ref = golden_of(case)

@@ -109,9 +109,18 @@ def check_against_golden(case, res, gold, exact=True, pair=None):
         assert (np.abs(res.noise[cy - 4:cy + 4, cx - 4:cx + 4] - gn) <= 1e-4 * np.maximum(gn, 1e-3)).all()
     bad = keywords_mismatch(region_keywords(res), gold["region_keys"], exact=exact)
     assert not bad, bad
+    if "merits" in gold:
+        # -c b: what check_stamps returned for (template, image) in every region that reached it (main.c:1037,1053)
+        mine = []
+        for i in range(res.sizes.n_regions):
+            r = res.regions[i]
+            if r.t_merit == 0 and r.i_merit == 0:
+                continue                      # no stamps in either direction: the region never got that far
+            mine += ["%.3f" % r.t_merit, "%.3f" % r.i_merit]
+        assert mine == gold["merits"]
 
 
-@pytest.mark.parametrize("case", CS.SMALL + CS.EXTRA + [CS.TINY_FULL], ids=lambda c: c.name)
+@pytest.mark.parametrize("case", CS.SMALL + CS.EXTRA + CS.BOTH + [CS.TINY_FULL], ids=lambda c: c.name)
 def test_oracle_matches_reference_golden(case, oracle):
     pair = CS.make_pair(case)
     gold = load_golden(case.name)
@@ -178,3 +187,15 @@ def test_ran1_first_values(oracle):
     assert all(0.0 <= x < 1.0 for x in v) and len(set(v)) == 4
     idum = C.c_int(-666)
     assert [oracle.hp_oracle_ran1(C.byref(idum)) for _ in range(4)] == v
+
+
+def test_direction_choice_cases_cover_both_outcomes(oracle):
+    """-c b: one case ends with the two regions of a frame convolved in opposite directions, one retries the search
+    in both directions and is left with stamps in one of them only (merit 666 for the other, alard.c:693-721)."""
+    by = {c.name: c for c in CS.BOTH}
+    pair = CS.make_pair(by["dir_b_mixed_2x1"])
+    res = H.run_oracle(oracle, CS.params_of(by["dir_b_mixed_2x1"], pair), *CS.inputs_of(by["dir_b_mixed_2x1"], pair))
+    assert [res.regions[i].conv_template for i in range(2)] == [0, 1]
+    pair = CS.make_pair(by["dir_b_retry"])
+    res = H.run_oracle(oracle, CS.params_of(by["dir_b_retry"], pair), *CS.inputs_of(by["dir_b_retry"], pair))
+    assert res.regions[0].flags & 0x4 and res.regions[0].i_merit == 666 and res.regions[0].conv_template == 1

@@ -51,7 +51,7 @@ class ZbRegionInfo(C.Structure):
         "conv_template", "flags", "n_stamps", "n_skipped", "fit_iters", "nx2norm")] + \
         [(n, C.c_double) for n in (
             "ksum", "sssig", "ssscat", "fsig", "fscat", "x2norm",
-            "dmean", "dsige", "dsig", "dmeano", "dsigeo", "dsigo", "nscalo")]
+            "dmean", "dsige", "dsig", "dmeano", "dsigeo", "dsigo", "nscalo", "t_merit", "i_merit")]
 
 
 class ZbStampInfo(C.Structure):

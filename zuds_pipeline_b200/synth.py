@@ -53,8 +53,13 @@ def _add_stars(img, xs, ys, peaks, sig_of):
 
 
 def make_pair(seed=1000, shape=(3080, 3072), seeing=4.0, nstars=None, ntransients=20,
-              gain=6.0, ref_noise=2.5, flux_ratio=1.05, bad_frac=1e-3, ncols_bad=6, border=12):
-    """One synthetic (science, reference) pair.  Deterministic in ``seed``."""
+              gain=6.0, ref_noise=2.5, flux_ratio=1.05, bad_frac=1e-3, ncols_bad=6, border=12,
+              ref_sharpness=0.8, seeing_gradient=0.04):
+    """One synthetic (science, reference) pair.  Deterministic in ``seed``.
+
+    ``ref_sharpness``: reference PSF width as a fraction of the science seeing; ``seeing_gradient``: relative change
+    of the science PSF width from the frame centre to its left/right edge (a large value with ``ref_sharpness`` = 1
+    makes the science image the sharper one on the left and the broader one on the right: the -c b cases)."""
     rng = np.random.default_rng(seed)
     ny, nx = shape
     if nstars is None:
@@ -64,12 +69,12 @@ def make_pair(seed=1000, shape=(3080, 3072), seeing=4.0, nstars=None, ntransient
     ys = rng.uniform(0, ny - 1, nstars)
     peaks = np.exp(rng.uniform(np.log(60.0), np.log(6000.0), nstars))
 
-    sig_ref = 0.8 * seeing * FWHM2SIG
+    sig_ref = ref_sharpness * seeing * FWHM2SIG
 
     def sig_sci(x, y):
         u = 2.0 * x / max(nx - 1, 1) - 1.0
         v = 2.0 * y / max(ny - 1, 1) - 1.0
-        return seeing * (1.0 + 0.04 * u + 0.03 * v * v) * FWHM2SIG
+        return seeing * (1.0 + seeing_gradient * u + 0.03 * v * v) * FWHM2SIG
 
     ref_sig = np.zeros(shape, np.float64)
     _add_stars(ref_sig, xs, ys, peaks, lambda x, y: sig_ref)
