@@ -9,7 +9,7 @@ cd "$(dirname "$0")/zuds_pipeline_b200/csrc"
 ARCH="-gencode arch=compute_100a,code=sm_100a"
 COMMON="-O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-ffp-contract=off $ARCH"
 mkdir -p ../../build
-NOFMAD="zb_host zb_stamps zb_fit zb_stats zb_tile zb_bkg zb_align"
+NOFMAD="zb_host zb_stamps zb_fit zb_stats zb_tile zb_bkg zb_align zb_check"
 FMAD="zb_mask zb_conv zb_prepost"
 pids=()
 for f in $NOFMAD $FMAD; do rm -f ../../build/$f.o; done

@@ -92,6 +92,10 @@ FULL = {
                replace={"-c": "i"}),
     # coadd-scale frame, one global fit: the row-tile configuration (BASELINE.json configs[4])
     "c5": Case("c5", (6160, 6144), 4.0, 1, {"ko": 2, "nsx": 20, "nsy": 20}),
+    # configs[1] with hotpants' own -c b on a pair whose science PSF is the narrower one on the left and the broader
+    # one on the right: the 3x3 regions do not all go the same way
+    "c1_dir_b": Case("c1_dir_b", (3080, 3072), 4.0, 3, {"ko": 2}, dict(ref_sharpness=1.0, seeing_gradient=0.35),
+                     replace={"-c": "b"}),
 }
 
 

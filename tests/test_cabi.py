@@ -82,7 +82,9 @@ def test_param_checks_follow_vargs():
     q.hw_ksstamp = 5
     rc, msg = _lib.check_params(q)
     assert rc == -1 and "conflicting" in msg                    # vargs.c: rss < r
-    q = P.default_params(512, 512)                              # -c b is a valid hotpants option outside this build
+    q = P.default_params(512, 512)                              # hotpants' own defaults: -c b, -fom v
+    assert _lib.check_params(q)[0] == 0
+    q.fig_merit = ord("s")                                      # a valid hotpants option outside this build
     assert _lib.check_params(q)[0] == -2
 
 

@@ -20,6 +20,9 @@ def compare(o, g):
     for r in range(o.sizes.n_regions):
         ro, rg = o.regions[r], g.regions[r]
         assert (ro.flags, ro.n_stamps, ro.fit_iters, ro.n_skipped) == (rg.flags, rg.n_stamps, rg.fit_iters, rg.n_skipped)
+        assert ro.conv_template == rg.conv_template, "region %d convolved the other way" % r
+        for a, b in ((ro.t_merit, rg.t_merit), (ro.i_merit, rg.i_merit)):      # -c b: check_stamps' merits (0 otherwise)
+            assert abs(a - b) <= 1e-9 * abs(a) or (a != a and b != b), "merit %r vs %r in region %d" % (a, b, r)
     assert np.array_equal(o.mask, g.mask), "hotpants int mask differs in %d pixels" % int((o.mask != g.mask).sum())
     scale = np.abs(o.sol).max(axis=1, keepdims=True) + 1e-300
     assert (np.abs(o.sol - g.sol) / scale).max() <= TOL_COEF
@@ -43,7 +46,7 @@ def compare(o, g):
         assert abs(a - b) <= 2e-4 + 1e-4 * abs(a) or (a != a and b != b)
 
 
-@pytest.mark.parametrize("case", CS.SMALL + CS.EXTRA + [CS.TINY_FULL], ids=lambda c: c.name)
+@pytest.mark.parametrize("case", CS.SMALL + CS.EXTRA + CS.BOTH + [CS.TINY_FULL], ids=lambda c: c.name)
 def test_small_cases_host_call(case, oracle, gpu_ctx):
     pair = CS.make_pair(case)
     p = CS.params_of(case, pair)

@@ -64,7 +64,7 @@ def compare_with_reference_files(g, ref):
     return float(dd.max()), float(dn.max()), int((rd != g.diff).sum() - np.isnan(rd).sum())
 
 
-@pytest.mark.parametrize("name", ["c1", "c4", "c5"])
+@pytest.mark.parametrize("name", ["c1", "c4", "c5", "c1_dir_b"])
 def test_full_size_against_reference_binary(name, gpu_ctx, tmp_path):
     if not os.path.exists(H.REF_BIN):
         pytest.fail("oracle/_ref/hotpants missing: it is built by __graft_entry__.build() where /root/reference exists")

@@ -352,7 +352,7 @@ k_build_matrix(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, 
     for (int k = 0; k < nS; k++) {
         const int slot = base + k;
         const ZbStamp &S = stamps[slot];
-        if (S.sscnt >= S.nss) continue;
+        if (S.sscnt >= S.nss || S.excl) continue;           // excl: only ever set during check_stamps' trial fit (-c b)
         const double *g = gram + (long long)slot * npair;
         const double *w = wxy + (long long)slot * nc2;
         switch (kind) {
@@ -661,7 +661,7 @@ k_stamp_sig(const ZbDev *__restrict__ D, ZbStamp *__restrict__ stamps, const ZbF
     extern __shared__ __align__(16) unsigned char dyn[];
     const int slot = slot0 + blockIdx.x;
     ZbStamp &S = stamps[slot];
-    if (S.nss <= 0 || S.sscnt >= S.nss) return;
+    if (S.nss <= 0 || S.sscnt >= S.nss || S.excl) return;
     if (!fit[S.region].active) return;
     const ZbRegion R = D->reg[S.region];
     const int hwss = D->p.hw_ksstamp, fwss = D->sz.fw_ksstamp, npix = fwss * fwss;

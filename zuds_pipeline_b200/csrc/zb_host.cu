@@ -9,6 +9,7 @@
 #include <math.h>
 #include <stdlib.h>
 #include <new>
+#include <vector>
 
 static inline int imin_(int a, int b) { return a < b ? a : b; }
 static inline int imax_(int a, int b) { return a < b ? b : a; }
@@ -127,7 +128,6 @@ extern "C" int zb_params_check(const zb_params *p, char *msg, int msglen) {
     if (p->nreg_x < 1 || p->nreg_y < 1 || p->nstamp_x < 1 || p->nstamp_y < 1) FAIL(ZB_ERR_PARAM, "region/stamp grid must be >= 1");
     if (p->ngauss < 1) FAIL(ZB_ERR_PARAM, "ngauss must be >= 1");
     // scope of this build
-    if (p->force_convolve == 'b') FAIL(ZB_ERR_UNSUPPORTED, "-c b (check_stamps direction test, alard.c:483) is not built yet; zuds always passes -c t");
     if (p->fig_merit != 'v') FAIL(ZB_ERR_UNSUPPORTED, "-fom %c is not built; only the default 'v'", p->fig_merit);
     if (p->use_full_ss) FAIL(ZB_ERR_UNSUPPORTED, "useFullSS is not built");
     if (p->t_pedestal != 0.f || p->i_pedestal != 0.f) FAIL(ZB_ERR_UNSUPPORTED, "-tp/-ip pedestals are not built");
@@ -138,8 +138,8 @@ extern "C" int zb_params_check(const zb_params *p, char *msg, int msglen) {
     if (p->scale_fit_thresh >= 1.f) FAIL(ZB_ERR_UNSUPPORTED, "-sft 1 (re-search on the already claimed mask, main.c:832-998) is not built");
     // getPsfCenters marks pixels >= tUKThresh while it scans; that is unobservable only while every
     // such pixel is already masked by the -tu/-iu test, i.e. while tuk >= tu.
-    if (p->force_convolve == 't' && p->t_ukthresh < p->t_uthresh) FAIL(ZB_ERR_UNSUPPORTED, "-tuk (%f) < -tu (%f) is not built", p->t_ukthresh, p->t_uthresh);
-    if (p->force_convolve == 'i' && p->i_ukthresh < p->i_uthresh) FAIL(ZB_ERR_UNSUPPORTED, "-iuk (%f) < -iu (%f) is not built", p->i_ukthresh, p->i_uthresh);
+    if (p->force_convolve != 'i' && p->t_ukthresh < p->t_uthresh) FAIL(ZB_ERR_UNSUPPORTED, "-tuk (%f) < -tu (%f) is not built", p->t_ukthresh, p->t_uthresh);
+    if (p->force_convolve != 't' && p->i_ukthresh < p->i_uthresh) FAIL(ZB_ERR_UNSUPPORTED, "-iuk (%f) < -iu (%f) is not built", p->i_ukthresh, p->i_uthresh);
     zb_sizes s; zb_sizes_of(p, &s);
     if (s.n_comp_ker + s.n_bg_vectors > ZB_MAX_BASIS) FAIL(ZB_ERR_UNSUPPORTED, "%d basis vectors > %d", s.n_comp_ker + s.n_bg_vectors, ZB_MAX_BASIS);
     if (s.nstamp_x < 1 || s.nstamp_y < 1) FAIL(ZB_ERR_PARAM, "image too small for any stamp");
@@ -261,9 +261,9 @@ static void free_workspace(zb_ctx *ctx) {
                       (void **)&ctx->d_indx, (void **)&ctx->d_fit, (void **)&ctx->d_jobs, (void **)&ctx->d_njobs, (void **)&ctx->d_kaks,
                       (void **)&ctx->d_ktap, (void **)&ctx->d_tilectr,
                       (void **)&ctx->d_kstat, (void **)&ctx->d_stats, (void **)&ctx->d_qa, (void **)&ctx->d_qpart,
-                      (void **)&ctx->d_qshell, (void **)&ctx->d_qshell_n};
+                      (void **)&ctx->d_qshell, (void **)&ctx->d_qshell_n, (void **)&ctx->d_check};
     for (size_t i = 0; i < sizeof dptrs / sizeof dptrs[0]; i++) { if (*dptrs[i]) cudaFree(*dptrs[i]); *dptrs[i] = NULL; }
-    void **hptrs[] = {(void **)&ctx->h_dev, (void **)&ctx->h_cells, (void **)&ctx->h_stamps, (void **)&ctx->h_fit, (void **)&ctx->h_njobs, (void **)&ctx->h_stats};
+    void **hptrs[] = {(void **)&ctx->h_dev, (void **)&ctx->h_cells, (void **)&ctx->h_stamps, (void **)&ctx->h_fit, (void **)&ctx->h_njobs, (void **)&ctx->h_stats, (void **)&ctx->h_check};
     for (size_t i = 0; i < sizeof hptrs / sizeof hptrs[0]; i++) { if (*hptrs[i]) cudaFreeHost(*hptrs[i]); *hptrs[i] = NULL; }
     ctx->configured = 0;
 }
@@ -311,7 +311,7 @@ static bool same_geometry(const zb_params *a, const zb_params *b) {
     if (a->nx != b->nx || a->ny != b->ny || a->hw_kernel != b->hw_kernel || a->hw_ksstamp != b->hw_ksstamp ||
         a->n_ksstamps != b->n_ksstamps || a->ker_order != b->ker_order || a->bg_order != b->bg_order ||
         a->nreg_x != b->nreg_x || a->nreg_y != b->nreg_y || a->nstamp_x != b->nstamp_x || a->nstamp_y != b->nstamp_y ||
-        a->kc_step != b->kc_step || a->ngauss != b->ngauss) return false;
+        a->kc_step != b->kc_step || a->ngauss != b->ngauss || (a->force_convolve == 'b') != (b->force_convolve == 'b')) return false;
     for (int i = 0; i < a->ngauss && i < ZB_MAX_GAUSS; i++)
         if (a->deg[i] != b->deg[i] || a->beta[i] != b->beta[i]) return false;
     return true;
@@ -389,7 +389,13 @@ int zb_configure(zb_ctx *ctx, const zb_params *p) {
     ctx->n_cells = sz.n_regions * sz.n_stamps;
     ctx->n_slots = sz.n_regions * sz.n_stamps;
     const size_t ns = (size_t)ctx->n_slots;
-    DMALLOC(ctx->d_cells, ns * sizeof(ZbCell));   HMALLOC(ctx->h_cells, ns * sizeof(ZbCell));
+    // -c b searches both images: the science image's grid cells live behind the template's (cell index + n_cells)
+    const size_t ncell_alloc = p->force_convolve == 'b' ? 2 * ns : ns;
+    DMALLOC(ctx->d_cells, ncell_alloc * sizeof(ZbCell));   HMALLOC(ctx->h_cells, ncell_alloc * sizeof(ZbCell));
+    if (p->force_convolve == 'b') {       // per-stamp kernel sums, per-region trial kernel sums, a copy of the regions' statistics blocks
+        DMALLOC(ctx->d_check, (ns + (size_t)sz.n_regions * 65) * sizeof(double));
+        HMALLOC(ctx->h_check, (ns + sz.n_regions) * sizeof(double));
+    }
     DMALLOC(ctx->d_stamps, ns * sizeof(ZbStamp)); HMALLOC(ctx->h_stamps, ns * sizeof(ZbStamp));
     DMALLOC(ctx->d_vec, ns * nvec * npix * sizeof(double));
     DMALLOC(ctx->d_kref, ns * npix * sizeof(double));
@@ -430,12 +436,12 @@ int zb_configure(zb_ctx *ctx, const zb_params *p) {
 
 // ------------------------------------------------------------- orchestration
 
-void zb_init_cells(zb_ctx *ctx, int r, float kft) {
+void zb_init_cells(zb_ctx *ctx, int r, float kft, int cell_base) {
     const zb_sizes &sz = ctx->sz;
     const ZbRegion &R = ctx->h_dev->reg[r];
     for (int gl = 0; gl < sz.nstamp_y; gl++)
         for (int gk = 0; gk < sz.nstamp_x; gk++) {
-            ZbCell &C = ctx->h_cells[(size_t)r * sz.n_stamps + gl * sz.nstamp_x + gk];
+            ZbCell &C = ctx->h_cells[(size_t)cell_base + (size_t)r * sz.n_stamps + gl * sz.nstamp_x + gk];
             memset(&C, 0, sizeof C);
             // main.c:849-852, image coordinates
             int sXMin = R.bx0 + gk * R.rpx / sz.nstamp_x, sYMin = R.by0 + gl * R.rpy / sz.nstamp_y;
@@ -451,12 +457,12 @@ void zb_init_cells(zb_ctx *ctx, int r, float kft) {
 // cell, and getStampStats3 can return early without overwriting mode/fwhm.  Cells are searched in
 // parallel assuming a fresh slot; the rare cell whose statistics bailed out while the slot was NOT
 // fresh is searched again with the inherited values.  Returns the number of kept stamps.
-static int resolve_region(zb_ctx *ctx, int r, const float *conv_img, cudaStream_t st, int *rc_out) {
+static int resolve_region(zb_ctx *ctx, int r, const float *conv_img, cudaStream_t st, int *rc_out, int cell_base = 0, int dir_t = -1) {
     const zb_sizes &sz = ctx->sz;
     double s_mode = 0, s_fwhm = 0, s_mean = 0, s_sd = 0, s_median = 0, s_lfwhm = 0, s_sum = 0;
     int kept = 0;
     for (int c = 0; c < sz.n_stamps; c++) {
-        const int ci = r * sz.n_stamps + c;
+        const int ci = cell_base + r * sz.n_stamps + c;
         ZbCell *C = &ctx->h_cells[ci];
         const bool depends = (C->stat_status == 1 || C->stat_status == 4 || C->stat_status == 5);
         if (depends && (C->in_mode != s_mode || C->in_fwhm != s_fwhm)) {
@@ -465,7 +471,7 @@ static int resolve_region(zb_ctx *ctx, int r, const float *conv_img, cudaStream_
             C->region = r; C->gk = gk; C->gl = gl; C->sx0 = sx0; C->sy0 = sy0; C->spx = spx; C->spy = spy; C->kft = kft;
             C->in_mode = s_mode; C->in_fwhm = s_fwhm; C->mean = s_mean; C->sd = s_sd; C->median = s_median; C->lfwhm = s_lfwhm; C->sum = s_sum;
             zb_copy_small(ctx, &ctx->d_cells[ci], C, sizeof(ZbCell), st);
-            int rc = zb_launch_stamp_search(ctx, conv_img, ci, 1, st);
+            int rc = zb_launch_stamp_search(ctx, conv_img, ci, 1, st, dir_t);
             if (rc != ZB_OK) { *rc_out = rc; return 0; }
             zb_copy_small(ctx, C, &ctx->d_cells[ci], sizeof(ZbCell), st);
             if (zb_stream_wait(ctx, st) != cudaSuccess) { *rc_out = zb_cuda_fail(ctx, cudaGetLastError(), "stamp re-search", __FILE__, __LINE__); return 0; }
@@ -528,6 +534,202 @@ int zb_finish_readback(zb_ctx *ctx, zb_region_info *regions, double *kernel_sol,
     return ZB_OK;
 }
 
+
+// -c b (hotpants' own default; zuds always passes -c t).  Both images are searched for stamps (the two searches use
+// their own mask bits, functions.c:195, and with tuk >= tu / iuk >= iu leave nothing behind that the other could see),
+// check_stamps gives each direction a merit per region (main.c:1026-1072, alard.c:483-724, here zb_check.cu), and the
+// smaller merit decides which image that region convolves (main.c:1076-1085).  The regions are then taken through
+// the fit and the output pass in two groups, one per direction, by the kernels of the fixed-direction path: while a
+// group is processed the other group's regions are inactive (fit) / marked skipped (output pass).
+static int subtract_both(zb_ctx *ctx, const zb_params *p,
+                         const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
+                         const void *sci_mask, int sci_mask_dtype, const void *ref_mask, int ref_mask_dtype,
+                         float *diff, float *noise, int32_t *out_mask,
+                         zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps_out, cudaStream_t st)
+{
+    const zb_sizes &sz = ctx->sz;
+    ZbDev *H = ctx->h_dev;
+    const int nR = sz.n_regions, nC = ctx->n_cells, nS = sz.n_stamps;
+    // direction d: 0 = convolve the template (stamps searched on ref), 1 = convolve the science image
+    const float *conv_of[2] = {ref, sci}, *ref_of[2] = {sci, ref};
+    const int dir_t_of[2] = {1, 0}, base_of[2] = {0, nC};
+    ctx->err[0] = 0;
+    memset(ctx->ms, 0, sizeof ctx->ms);
+
+    // ---- stage 0: input masks
+    STAGE(0);
+    for (int r = 0; r < nR; r++) { H->reg[r].skip = 0; H->reg[r].own_x1 = H->reg[r].rx1; H->reg[r].own_y1 = H->reg[r].ry1; }
+    H->conv_template = 1;
+    zb_copy_small(ctx, ctx->d_dev, H, sizeof(ZbDev), st);
+    CHECK_RC(zb_launch_input_mask(ctx, sci, ref, sci_mask, sci_mask_dtype, ref_mask, ref_mask_dtype, st));
+
+    // ---- stage 1: stamp statistics + sub-stamp search on both images
+    STAGE(1);
+    for (int d = 0; d < 2; d++) for (int r = 0; r < nR; r++) zb_init_cells(ctx, r, p->ker_fit_thresh, base_of[d]);
+    zb_copy_small(ctx, ctx->d_cells, ctx->h_cells, (size_t)2 * nC * sizeof(ZbCell), st);
+    for (int d = 0; d < 2; d++) CHECK_RC(zb_launch_stamp_search(ctx, conv_of[d], base_of[d], nC, st, dir_t_of[d]));
+    zb_copy_small(ctx, ctx->h_cells, ctx->d_cells, (size_t)2 * nC * sizeof(ZbCell), st);
+    SYNC("stamp search");
+
+    // ---- stage 2: per direction compaction, stale-slot fix-ups; one retry of BOTH searches when either found too few (main.c:921-995)
+    STAGE(2);
+    std::vector<ZbStamp> tab[2];
+    std::vector<int> cnt[2], dir(nR, 0), gone(nR, 0);
+    for (int d = 0; d < 2; d++) { tab[d].assign((size_t)ctx->n_slots, ZbStamp()); memset(tab[d].data(), 0, tab[d].size() * sizeof(ZbStamp)); cnt[d].assign(nR, 0); }
+    for (int r = 0; r < nR; r++) {
+        zb_region_info *ri = &regions[r];
+        const ZbRegion &R = H->reg[r];
+        memset(ri, 0, sizeof *ri);
+        ri->rx_min = R.rx0; ri->rx_max = R.rx1; ri->ry_min = R.ry0; ri->ry_max = R.ry1;
+        ri->bx_min = R.bx0; ri->bx_max = R.bx1; ri->by_min = R.by0; ri->by_max = R.by1;
+        int kept[2], rc = ZB_OK;
+        for (int d = 0; d < 2; d++) { kept[d] = resolve_region(ctx, r, conv_of[d], st, &rc, base_of[d], dir_t_of[d]); CHECK_RC(rc); }
+        if (((kept[0] / (float)nS) < p->min_frac_good_stamps || (kept[1] / (float)nS) < p->min_frac_good_stamps) && p->scale_fit_thresh < 1.f) {
+            float kft = p->ker_fit_thresh;
+            kft *= p->scale_fit_thresh;
+            for (int d = 0; d < 2; d++) {
+                zb_init_cells(ctx, r, kft, base_of[d]);
+                const int c0 = base_of[d] + r * nS;
+                zb_copy_small(ctx, &ctx->d_cells[c0], &ctx->h_cells[c0], (size_t)nS * sizeof(ZbCell), st);
+                CHECK_RC(zb_launch_stamp_search(ctx, conv_of[d], c0, nS, st, dir_t_of[d]));
+                zb_copy_small(ctx, &ctx->h_cells[c0], &ctx->d_cells[c0], (size_t)nS * sizeof(ZbCell), st);
+            }
+            SYNC("stamp search retry");
+            for (int d = 0; d < 2; d++) { kept[d] = resolve_region(ctx, r, conv_of[d], st, &rc, base_of[d], dir_t_of[d]); CHECK_RC(rc); }
+            ri->flags |= ZB_REGION_RETRIED;
+        }
+        for (int d = 0; d < 2; d++) {           // kept stamps, in grid order, are this direction's slots
+            int k = 0;
+            for (int c = 0; c < nS; c++) {
+                const ZbCell &C = ctx->h_cells[(size_t)base_of[d] + (size_t)r * nS + c];
+                if (C.nss <= 0) continue;
+                ZbStamp &S = tab[d][R.stamp_base + k];
+                S.region = r; S.x0 = C.sx0; S.y0 = C.sy0; S.nss = C.nss; S.sscnt = 0;
+                for (int q = 0; q < C.nss; q++) { S.xss[q] = C.xss[q]; S.yss[q] = C.yss[q]; }
+                S.mode = C.mode; S.fwhm = C.fwhm;
+                k++;
+            }
+            cnt[d][r] = k;
+        }
+    }
+
+    // ---- stage 3: fill both stamp sets, merit of each direction (main.c:1026-1072), the choice (main.c:1076-1085)
+    STAGE(3);
+    std::vector<double> merit[2];
+    int *jobs = (int *)ctx->h_stats;          // pinned scratch
+    for (int d = 0; d < 2; d++) {
+        merit[d].assign(nR, 666.0);           // what check_stamps returns for a direction without stamps (alard.c:693-721)
+        memcpy(ctx->h_stamps, tab[d].data(), (size_t)ctx->n_slots * sizeof(ZbStamp));
+        int njobs = 0;
+        for (int r = 0; r < nR; r++) {
+            ZbFit &F = ctx->h_fit[r];
+            memset(&F, 0, sizeof F);
+            F.n_stamps = cnt[d][r];
+            for (int k = 0; k < F.n_stamps; k++) jobs[njobs++] = H->reg[r].stamp_base + k;
+        }
+        if (njobs > 0) {
+            zb_copy_small(ctx, ctx->d_stamps, ctx->h_stamps, (size_t)ctx->n_slots * sizeof(ZbStamp), st);
+            zb_copy_small(ctx, ctx->d_jobs, jobs, (size_t)njobs * sizeof(int), st);
+            CHECK_RC(zb_launch_fill(ctx, conv_of[d], ref_of[d], ctx->d_jobs, njobs, st));
+            CHECK_RC(zb_check_stamps(ctx, sci, ref, sci_rms, ref_rms, merit[d].data(), st));
+        }
+        SYNC("check_stamps");
+    }
+    bool any_skip = false, has[2] = {false, false};
+    for (int r = 0; r < nR; r++) {
+        zb_region_info *ri = &regions[r];
+        const ZbRegion &R = H->reg[r];
+        ZbFit &F = ctx->h_fit[r];
+        memset(&F, 0, sizeof F);
+        for (int q = 0; q < nS; q++) memset(&ctx->h_stamps[R.stamp_base + q], 0, sizeof(ZbStamp));
+        if (cnt[0][r] > 0 || cnt[1][r] > 0) {
+            ri->t_merit = merit[0][r]; ri->i_merit = merit[1][r];
+            dir[r] = (ri->t_merit < ri->i_merit) ? 0 : 1;
+        }
+        const int k = cnt[dir[r]][r];
+        ri->conv_template = dir[r] == 0;
+        ri->n_stamps = k;
+        F.n_stamps = k;
+        if (k == 0) { ri->flags |= ZB_REGION_SKIPPED; gone[r] = 1; any_skip = true; continue; }     // main.c:1002-1009
+        memcpy(&ctx->h_stamps[R.stamp_base], &tab[dir[r]][R.stamp_base], (size_t)k * sizeof(ZbStamp));
+        has[dir[r]] = true;
+    }
+    // last-writer-wins ownership of the shared region edges (main.c:548-551,655-658), skipping silent regions
+    for (int j = 0; j < p->nreg_y; j++)
+        for (int i = 0; i < p->nreg_x; i++) {
+            ZbRegion &R = H->reg[j * p->nreg_x + i];
+            R.skip = gone[j * p->nreg_x + i];
+            R.own_x1 = R.rx1; R.own_y1 = R.ry1;
+            if (i + 1 < p->nreg_x && !gone[j * p->nreg_x + i + 1]) R.own_x1 = R.rx1 - 1;
+            if (j + 1 < p->nreg_y && !gone[(j + 1) * p->nreg_x + i]) R.own_y1 = R.ry1 - 1;
+        }
+    if (any_skip) {
+        cudaMemsetAsync(diff, 0, (size_t)p->nx * p->ny * sizeof(float), st);
+        cudaMemsetAsync(noise, 0, (size_t)p->nx * p->ny * sizeof(float), st);
+        if (out_mask) cudaMemsetAsync(out_mask, 0, (size_t)p->nx * p->ny * sizeof(int32_t), st);
+    }
+    zb_copy_small(ctx, ctx->d_dev, H, sizeof(ZbDev), st);
+    zb_copy_small(ctx, ctx->d_stamps, ctx->h_stamps, (size_t)ctx->n_slots * sizeof(ZbStamp), st);
+    zb_copy_small(ctx, ctx->d_fit, ctx->h_fit, (size_t)nR * sizeof(ZbFit), st);
+    SYNC("direction choice");
+
+    // ---- stage 4: fill + global fit with sigma clipping (alard.c:316-381), one group of regions per direction
+    STAGE(4);
+    for (int d = 0; d < 2; d++) {
+        if (!has[d]) continue;
+        int njobs = 0;
+        for (int r = 0; r < nR; r++) {
+            if (gone[r] || dir[r] != d) continue;
+            ctx->h_fit[r].active = 1;
+            for (int k = 0; k < ctx->h_fit[r].n_stamps; k++) jobs[njobs++] = H->reg[r].stamp_base + k;
+        }
+        zb_copy_small(ctx, ctx->d_fit, ctx->h_fit, (size_t)nR * sizeof(ZbFit), st);
+        zb_copy_small(ctx, ctx->d_jobs, jobs, (size_t)njobs * sizeof(int), st);
+        CHECK_RC(zb_launch_fill(ctx, conv_of[d], ref_of[d], ctx->d_jobs, njobs, st));
+        bool any_active = true;
+        int guard = 0;
+        while (any_active) {
+            CHECK_RC(zb_launch_fit_iteration(ctx, conv_of[d], ref_of[d], sci, ref, sci_rms, ref_rms, st));
+            zb_copy_small(ctx, ctx->h_fit, ctx->d_fit, (size_t)nR * sizeof(ZbFit), st);
+            zb_copy_small(ctx, ctx->h_njobs, ctx->d_njobs, sizeof(int), st);
+            SYNC("fit iteration");
+            any_active = false;
+            for (int r = 0; r < nR; r++) any_active |= ctx->h_fit[r].active != 0;
+            if (ctx->h_njobs[0] > 0) CHECK_RC(zb_launch_fill(ctx, conv_of[d], ref_of[d], ctx->d_jobs, ctx->h_njobs[0], st));
+            if (++guard > 4 * nS * ZB_MAX_KSS) { snprintf(ctx->err, sizeof ctx->err, "fit loop did not converge"); return ZB_ERR_INTERNAL; }
+        }
+    }
+
+    // ---- stages 5-7: the fused output pass, FSIG and the region statistics, again one group per direction.  The
+    // statistics kernels clear the result block of every region when they start, so the first group's is set aside.
+    STAGE(5);
+    double *d_qsave = ctx->d_check + ctx->n_slots + nR;
+    const int last = has[1] ? 1 : 0;
+    for (int d = 0; d < 2; d++) {
+        if (!has[d]) continue;
+        SYNC("direction group");                 // H is read when the copy kernel runs, not when it is queued
+        H->conv_template = d == 0;
+        for (int r = 0; r < nR; r++) H->reg[r].skip = gone[r] || dir[r] != d;
+        zb_copy_small(ctx, ctx->d_dev, H, sizeof(ZbDev), st);
+        CHECK_RC(zb_launch_convolve(ctx, sci, ref, sci_rms, ref_rms, sci_mask, sci_mask_dtype, ref_mask, ref_mask_dtype, diff, noise, out_mask, st));
+        if (d == last) STAGE(6);
+        CHECK_RC(zb_launch_final_sig(ctx, st));
+        if (d == last) STAGE(7);
+        CHECK_RC(zb_launch_region_stats(ctx, noise, out_mask, st));
+        if (d == 0 && has[1]) zb_copy_small(ctx, d_qsave, ctx->d_stats, (size_t)nR * 64 * sizeof(double), st);
+        if (d == 1 && has[0])
+            for (int r = 0; r < nR; r++)
+                if (!gone[r] && dir[r] == 0) zb_copy_small(ctx, ctx->d_stats + (size_t)r * 64, d_qsave + (size_t)r * 64, 64 * sizeof(double), st);
+    }
+    if (!has[0] && !has[1]) { STAGE(6); STAGE(7); }
+    SYNC("output pass");
+    for (int r = 0; r < nR; r++) H->reg[r].skip = gone[r];
+
+    // ---- stage 8: small read-backs
+    STAGE(8);
+    return zb_finish_readback(ctx, regions, kernel_sol, stamps_out, (has[0] || has[1]) ? 2 : 1, st);
+}
+
 extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
                            const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
                            const void *sci_mask, int sci_mask_dtype, const void *ref_mask, int ref_mask_dtype,
@@ -540,6 +742,9 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
     if (cudaSetDevice(ctx->device) != cudaSuccess) return zb_cuda_fail(ctx, cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
     CHECK_RC(zb_configure(ctx, p));
     cudaStream_t st = zb_pick_stream(ctx, stream);
+    if (p->force_convolve == 'b')
+        return subtract_both(ctx, p, sci, ref, sci_rms, ref_rms, sci_mask, sci_mask_dtype, ref_mask, ref_mask_dtype,
+                             diff, noise, out_mask, regions, kernel_sol, stamps_out, st);
     const zb_sizes &sz = ctx->sz;
     ZbDev *H = ctx->h_dev;
     const int nR = sz.n_regions;

@@ -62,7 +62,7 @@ struct ZbStamp {
     double mode, fwhm, chi2, sum;
     double sig1;                 // last getStampSig value
     int sig_flag;
-    int pad;
+    int excl;                    // -c b: left out of check_stamps' trial fit (kernel sum beyond kerSigReject sigma, alard.c:590-606)
 };
 
 // Per-region state of the fit loop.
@@ -150,6 +150,7 @@ struct zb_ctx {
     double  *d_sol;              // [region][n_comp_total+1]
     double  *d_vv; int *d_indx;  // LU scratch
     ZbFit   *d_fit, *h_fit;
+    double  *d_check, *h_check;  // -c b: [n_slots] per-stamp kernel sums + [n_regions] trial kernel sums (zb_check.cu)
     int     *d_jobs, *d_njobs, *h_njobs;
     double  *d_kaks;             // [region][blocks+1]  sum |K| per block in the reference's tap order
     void    *d_ktap;             // [region][blocks+1][fw*fwp] 16-byte taps (K double, K^2 float), reversed, rows padded: k_convolve's operand
@@ -202,7 +203,8 @@ cudaError_t zb_zero_small(zb_ctx *ctx, void *dst, size_t bytes, cudaStream_t st)
 // kernel launchers (each returns a zb_status)
 int zb_launch_input_mask(zb_ctx *ctx, const float *sci, const float *ref, const void *smask, int sdt,
                          const void *tmask, int tdt, cudaStream_t st, int y_lo = 0, int y_hi = 0x7fffffff);
-int zb_launch_stamp_search(zb_ctx *ctx, const float *conv_img, int first_cell, int n_cells, cudaStream_t st);
+// dir_t: 1 the template is searched, 0 the science image, -1 whichever the call convolves (ZbDev::conv_template)
+int zb_launch_stamp_search(zb_ctx *ctx, const float *conv_img, int first_cell, int n_cells, cudaStream_t st, int dir_t = -1);
 int zb_launch_fill(zb_ctx *ctx, const float *conv_img, const float *ref_img, const int *d_jobs, int n_jobs, cudaStream_t st);
 int zb_launch_fit_iteration(zb_ctx *ctx, const float *conv_img, const float *ref_img,
                             const float *sci, const float *ref, const float *sci_rms, const float *ref_rms, cudaStream_t st);
@@ -216,11 +218,13 @@ int zb_launch_stamp_sig(zb_ctx *ctx, const float *sci, const float *ref, const f
 int zb_launch_clip(zb_ctx *ctx, cudaStream_t st);
 int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStream_t st);
 int zb_launch_final_sig(zb_ctx *ctx, cudaStream_t st);
+int zb_check_stamps(zb_ctx *ctx, const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
+                    double *merit, cudaStream_t st);
 
 // host helpers
 int zb_stage_buf(zb_ctx *ctx, int i, size_t bytes);
 int zb_configure(zb_ctx *ctx, const zb_params *p);
-void zb_init_cells(zb_ctx *ctx, int r, float kft);
+void zb_init_cells(zb_ctx *ctx, int r, float kft, int cell_base = 0);
 int zb_finish_readback(zb_ctx *ctx, zb_region_info *regions, double *kernel_sol, zb_stamp_info *stamps_out, int timing, cudaStream_t st);
 void zb_host_ran1_stream(double *out, int n);
 void zb_host_basis(const zb_params *p, double *kvec, double *fx, double *fy, int *ren);

@@ -32,8 +32,9 @@ namespace zs1024 {
 #undef NW
 }
 
-int zb_launch_stamp_search(zb_ctx *ctx, const float *conv_img, int first_cell, int n_cells, cudaStream_t st)
+int zb_launch_stamp_search(zb_ctx *ctx, const float *conv_img, int first_cell, int n_cells, cudaStream_t st, int dir_t)
 {
+    if (dir_t < 0) dir_t = ctx->h_dev->conv_template;
     if (n_cells <= 0) return ZB_OK;
     size_t npx = (size_t)ctx->sz.fw_stamp * ctx->sz.fw_stamp;
     size_t smem = npx * (sizeof(float) + sizeof(int) + 1) + 32 + ((npx + 31) / 32) * sizeof(unsigned);
@@ -56,10 +57,10 @@ int zb_launch_stamp_search(zb_ctx *ctx, const float *conv_img, int first_cell, i
     }
     if (npx >= 160 * 160) {
         cudaFuncSetAttribute(zs1024::k_stamp_search, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
-        zs1024::k_stamp_search<<<n_cells, 1024, smem, st>>>(ctx->d_dev, conv_img, ctx->d_min, ctx->d_cells, first_cell, ctx->d_ran, ctx->n_ran, gs, per);
+        zs1024::k_stamp_search<<<n_cells, 1024, smem, st>>>(ctx->d_dev, conv_img, ctx->d_min, ctx->d_cells, first_cell, ctx->d_ran, ctx->n_ran, gs, per, dir_t);
     } else {
         cudaFuncSetAttribute(zs256::k_stamp_search, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
-        zs256::k_stamp_search<<<n_cells, 256, smem, st>>>(ctx->d_dev, conv_img, ctx->d_min, ctx->d_cells, first_cell, ctx->d_ran, ctx->n_ran, gs, per);
+        zs256::k_stamp_search<<<n_cells, 256, smem, st>>>(ctx->d_dev, conv_img, ctx->d_min, ctx->d_cells, first_cell, ctx->d_ran, ctx->n_ran, gs, per, dir_t);
     }
     ZB_DBG("k_stamp_search");
     ctx->launches++;

@@ -202,7 +202,7 @@ __device__ static void qsort_idx(const double *v, int *idx, int n) {
 __global__ void __launch_bounds__(NT)
 k_stamp_search(const ZbDev *__restrict__ D, const float *__restrict__ img, int32_t *__restrict__ m_in,
                ZbCell *__restrict__ cells, int first_cell, const double *__restrict__ ran, int n_ran,
-               unsigned char *__restrict__ gscratch, size_t gscratch_per_cell)
+               unsigned char *__restrict__ gscratch, size_t gscratch_per_cell, int dir_t)
 {
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     // stamps too large for shared memory (coadd-scale frames with a coarse stamp grid) work out of a
@@ -237,9 +237,11 @@ k_stamp_search(const ZbDev *__restrict__ D, const float *__restrict__ img, int32
     // ---- getPsfCenters ----
     const int hwss = D->p.hw_ksstamp, nkss = D->p.n_ksstamps, fcnt = 2 * nkss;
     const float kft = C.kft;
-    const double hiThresh = D->conv_template ? (double)D->tUK : (double)D->iUK;
-    const int bbit2 = D->conv_template ? ZB_FLAG_T_SKIP : ZB_FLAG_I_SKIP;
-    const int bbit = (D->conv_template ? (ZB_FLAG_T_BAD | ZB_FLAG_T_SKIP) : (ZB_FLAG_I_BAD | ZB_FLAG_I_SKIP)) | 0xbf;
+    // dir_t: the image searched is the template (1) or the science image (0); with -c b both are searched, each
+    // with its own pair of mask bits (functions.c:195,251-330), so the two searches do not see each other
+    const double hiThresh = dir_t ? (double)D->tUK : (double)D->iUK;
+    const int bbit2 = dir_t ? ZB_FLAG_T_SKIP : ZB_FLAG_I_SKIP;
+    const int bbit = (dir_t ? (ZB_FLAG_T_BAD | ZB_FLAG_T_SKIP) : (ZB_FLAG_I_BAD | ZB_FLAG_I_SKIP)) | 0xbf;
     const double sky = S.mode, invdsky = 1. / S.fwhm;
     const float skyf = (float)sky, invdskyf = (float)invdsky;     // checkPsfCenter takes them as floats
     const double floor_ = sky + kft * S.fwhm;
