@@ -871,8 +871,13 @@ static double check_stamps(reg_t *R, stamp_t *st, int nS, const float *imRef, co
     lu_backsub(M, n, indx, tsol);
     kmean = make_kernel(R, 0, 0, tsol);
     m1 = (float *)calloc((size_t)ntest + 1, sizeof(float)); m2 = (float *)calloc((size_t)ntest + 1, sizeof(float));
+    if (getenv("HP_ORACLE_DEBUG")) {
+        fprintf(stderr, "CHK region nS %d kmean %.17g\n", nS, kmean);
+        for (i = 0; i < nS; i++) fprintf(stderr, "CHK  stamp %d ksum %.17g excl %d\n", i, norm[i], !(dif[i] < R->p->ker_sig_reject));
+    }
     for (i = 0; i < ntest; i++) {
         double sig1 = stamp_sig(R, &ts[i], tsol, imNoise);
+        if (getenv("HP_ORACLE_DEBUG")) fprintf(stderr, "CHK  test %d sig1 %.17g\n", i, sig1);
         if (sig1 != -1 && sig1 <= MAXVAL) m1[mcnt1++] = (float)sig1;
         m2[mcnt2++] = 0.f;                                 /* sig2 and sig3 stay 0 with -fom v */
     }

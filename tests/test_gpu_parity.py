@@ -22,7 +22,14 @@ def compare(o, g):
         assert (ro.flags, ro.n_stamps, ro.fit_iters, ro.n_skipped) == (rg.flags, rg.n_stamps, rg.fit_iters, rg.n_skipped)
         assert ro.conv_template == rg.conv_template, "region %d convolved the other way" % r
         for a, b in ((ro.t_merit, rg.t_merit), (ro.i_merit, rg.i_merit)):      # -c b: check_stamps' merits (0 otherwise)
-            assert abs(a - b) <= 1e-9 * abs(a) or (a != a and b != b), "merit %r vs %r in region %d" % (a, b, r)
+            assert abs(a - b) <= 1e-12 * abs(a) or (a != a and b != b), "merit %r vs %r in region %d" % (a, b, r)
+    # the last figure of merit of every stamp (getStampSig): it feeds the clip decisions, so it should agree far
+    # below float precision (a float-rounded intermediate would show up at 6e-8)
+    ns = o.sizes.n_stamps
+    for r in range(o.sizes.n_regions):
+        for k in range(o.regions[r].n_stamps):
+            a, b = o.stamps[r * ns + k].chi2, g.stamps[r * ns + k].chi2
+            assert abs(a - b) <= 1e-9 * abs(a) or (a != a and b != b), "chi2 %r vs %r, region %d stamp %d" % (a, b, r, k)
     assert np.array_equal(o.mask, g.mask), "hotpants int mask differs in %d pixels" % int((o.mask != g.mask).sum())
     scale = np.abs(o.sol).max(axis=1, keepdims=True) + 1e-300
     assert (np.abs(o.sol - g.sol) / scale).max() <= TOL_COEF

@@ -219,12 +219,19 @@ int zb_check_stamps(zb_ctx *ctx, const float *sci, const float *ref, const float
     zb_copy_small(ctx, ctx->h_check + ctx->n_slots, ctx->d_check + ctx->n_slots, (size_t)nR * sizeof(double), st);
     SYNC("check_stamps trial fit");
 
+    static int dbg = -1;
+    if (dbg < 0) { const char *e = getenv("ZB_CHECK_DEBUG"); dbg = (e && e[0] == '1') ? 1 : 0; }
     for (int r = 0; r < nR; r++) {
         const ZbFit &F = ctx->h_fit[r];
         if (!F.active) continue;
         const int base = H->reg[r].stamp_base;
         const double kmean = ctx->h_check[ctx->n_slots + r];
         int ntest = 0, mcnt1 = 0;
+        if (dbg) {
+            fprintf(stderr, "CHK region %d nS %d kmean %.17g\n", r, F.n_stamps, kmean);
+            for (int k = 0; k < F.n_stamps; k++)
+                fprintf(stderr, "CHK  stamp %d ksum %.17g excl %d sig1 %.17g\n", k, ctx->h_check[base + k], ctx->h_stamps[base + k].excl, ctx->h_stamps[base + k].sig1);
+        }
         for (int k = 0; k < F.n_stamps; k++) {
             ZbStamp &S = ctx->h_stamps[base + k];
             if (!S.excl) {

@@ -639,15 +639,17 @@ k_lu_subst(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, const dou
 
 // ------------------------------------------------------------ model and clipping
 
-// noise^2 used as the fit's figure-of-merit weight (hotpants/main.c:739-770): float arithmetic
+// noise^2 used as the fit's figure-of-merit weight (hotpants/main.c:739-770): squares and the sum of the two images'
+// terms in float; the gain model (makeNoiseImage4, functions.c:1172-1187) multiplies and adds in DOUBLE (C's fabs
+// returns double) and rounds once -- fabs(float) here would be C++'s float overload and round the product first
 __device__ static inline float approx_var(const ZbDev *D, const float *sci, const float *ref,
                                           const float *sci_rms, const float *ref_rms, long long g)
 {
     float o, e;
     if (sci_rms) { float v = sci_rms[g]; o = v * v; }
-    else { float inv = (float)(1. / D->p.i_gain), quad = D->p.i_rdnoise / D->p.i_gain; double qq = quad * quad; o = (float)(fabs(sci[g]) * inv + qq); }
+    else { float inv = (float)(1. / D->p.i_gain), quad = D->p.i_rdnoise / D->p.i_gain; double qq = quad * quad; o = (float)(fabs((double)sci[g]) * (double)inv + qq); }
     if (ref_rms) { float v = ref_rms[g]; e = v * v; }
-    else { float inv = (float)(1. / D->p.t_gain), quad = D->p.t_rdnoise / D->p.t_gain; double qq = quad * quad; e = (float)(fabs(ref[g]) * inv + qq); }
+    else { float inv = (float)(1. / D->p.t_gain), quad = D->p.t_rdnoise / D->p.t_gain; double qq = quad * quad; e = (float)(fabs((double)ref[g]) * (double)inv + qq); }
     return o + e;
 }
 
