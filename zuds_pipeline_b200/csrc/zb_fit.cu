@@ -318,17 +318,13 @@ __device__ static inline double gram_at(const double *g, int u, int v) {   // u 
     return g[u * (u + 1) / 2 + v];
 }
 
-// One thread per matrix element (I >= J) or right-hand-side element; stamps summed in ascending order.
-__global__ void __launch_bounds__(256)
-k_build_matrix(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
-               const double *__restrict__ gram, const double *__restrict__ rhs, const double *__restrict__ wxy,
-               double *__restrict__ mat, double *__restrict__ sol)
+// One matrix element (I >= J) or right-hand-side element (J == n); stamps summed in ascending order.
+__device__ static void bm_element(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
+                                  const double *__restrict__ gram, const double *__restrict__ rhs, const double *__restrict__ wxy,
+                                  double *__restrict__ mat, double *__restrict__ sol, int r, int I, int J)
 {
-    const int r = blockIdx.z;
-    if (!fit[r].active) return;
     const int n = D->sz.mat_size, nK = D->sz.n_comp_ker, nc2 = D->sz.n_comp, ncomp = (nK - 1) * nc2;
     const int nvec = nK + D->sz.n_bg_vectors, npair = nvec * (nvec + 1) / 2;
-    const int I = blockIdx.y * 16 + threadIdx.y, J = blockIdx.x * 16 + threadIdx.x;
     if (I >= n || J > n || (J < n && J > I)) return;
     const int base = D->reg[r].stamp_base, nS = fit[r].n_stamps;
     // classify the element once
@@ -369,6 +365,108 @@ k_build_matrix(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, 
         M[(long long)I * n + J] = acc;
         M[(long long)J * n + I] = acc;
     }
+}
+
+// One thread per element, every kind (the form of round 1; ZB_BM_LEGACY=1 selects it for A/B runs)
+__global__ void __launch_bounds__(256)
+k_build_matrix(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
+               const double *__restrict__ gram, const double *__restrict__ rhs, const double *__restrict__ wxy,
+               double *__restrict__ mat, double *__restrict__ sol)
+{
+    const int r = blockIdx.z;
+    if (!fit[r].active) return;
+    bm_element(D, stamps, fit, gram, rhs, wxy, mat, sol, r, blockIdx.y * 16 + threadIdx.y, blockIdx.x * 16 + threadIdx.x);
+}
+
+// The bulk of the normal matrix: elements (I, J) = (1 + i1*nc2 + wi, 1 + j1*nc2 + wj) with j1 <= i1, i.e.
+// sum over stamps of w[wi] * w[wj] * gram(i1+1, j1+1) (alard.c:905-913).  k_build_matrix spends ~20 instructions per
+// term (three loads, the stamp's state, a switch); at ko = 4 that made it the largest consumer of SM time of a pair
+// (n = 722: 2.8 of 7.3 ms, profiles/r02_launches_c1b_summary.txt).  Here a thread owns one (wi, wj) and BM_R pairs
+// (i1, j1): per stamp it forms w[wi] * w[wj] once and adds its product with BM_R gram entries, still one element per
+// accumulator, stamps ascending, (w * w) * g then the add, each rounded: the same sums bit for bit.
+#define BM_R 8
+__global__ void __launch_bounds__(256)
+k_build_matrix_main(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
+                    const double *__restrict__ gram, const double *__restrict__ wxy, double *__restrict__ mat)
+{
+    extern __shared__ int s_act[];                   // slots of the stamps that enter the sums, ascending
+    __shared__ int s_nact;
+    const int r = blockIdx.y;
+    if (!fit[r].active) return;
+    const int n = D->sz.mat_size, nK = D->sz.n_comp_ker, nc2 = D->sz.n_comp, PP = nc2 * nc2;
+    const int nvec = nK + D->sz.n_bg_vectors, npair = nvec * (nvec + 1) / 2;
+    const int nb1 = nK - 1, nuv = nb1 * (nb1 + 1) / 2;
+    const int base = D->reg[r].stamp_base, nS = fit[r].n_stamps;
+    if (threadIdx.x == 0) {
+        int c = 0;
+        for (int k = 0; k < nS; k++) { const ZbStamp &S = stamps[base + k]; if (!(S.sscnt >= S.nss || S.excl)) s_act[c++] = base + k; }
+        s_nact = c;
+    }
+    __syncthreads();
+    const int nA = s_nact;
+    const int G = PP >= 256 ? 1 : 256 / PP;          // (wi, wj) groups side by side in a CTA
+    const int grp = PP >= 256 ? 0 : threadIdx.x / PP;
+    if (grp >= G) return;
+    const int q0 = (blockIdx.x * G + grp) * BM_R;    // first (i1, j1) pair of this group, triangular order
+    if (q0 >= nuv) return;
+    int i1_0 = (int)((sqrt(8.0 * q0 + 1.0) - 1.0) * 0.5);
+    while ((i1_0 + 1) * (i1_0 + 2) / 2 <= q0) i1_0++;
+    while (i1_0 * (i1_0 + 1) / 2 > q0) i1_0--;
+    const int j1_0 = q0 - i1_0 * (i1_0 + 1) / 2;
+    double *M = mat + (long long)r * n * n;
+    for (int p = PP >= 256 ? threadIdx.x : threadIdx.x - grp * PP; p < PP; p += (PP >= 256 ? 256 : PP)) {
+        const int wi = p / nc2, wj = p - wi * nc2;
+        int goff[BM_R]; double acc[BM_R];
+        {
+            int i1 = i1_0, j1 = j1_0;
+#pragma unroll
+            for (int e = 0; e < BM_R; e++) {
+                const int u = i1 + 1, v = j1 + 1;
+                goff[e] = (q0 + e < nuv) ? u * (u + 1) / 2 + v : 0;
+                acc[e] = 0.0;
+                if (++j1 > i1) { i1++; j1 = 0; }
+            }
+        }
+        for (int k = 0; k < nA; k++) {
+            const int slot = s_act[k];
+            const double *w = wxy + (long long)slot * nc2;
+            const double *g = gram + (long long)slot * npair;
+            const double ww = __dmul_rn(w[wi], w[wj]);
+#pragma unroll
+            for (int e = 0; e < BM_R; e++) acc[e] = __dadd_rn(acc[e], __dmul_rn(ww, g[goff[e]]));
+        }
+        int i1 = i1_0, j1 = j1_0;
+#pragma unroll
+        for (int e = 0; e < BM_R; e++) {
+            if (q0 + e < nuv) {
+                const int I = 1 + i1 * nc2 + wi, J = 1 + j1 * nc2 + wj;
+                if (J <= I) { M[(long long)I * n + J] = acc[e]; M[(long long)J * n + I] = acc[e]; }
+            }
+            if (++j1 > i1) { i1++; j1 = 0; }
+        }
+    }
+}
+
+// Everything else: column 0, the background rows and the right-hand side, by the generic element code.
+__global__ void __launch_bounds__(256)
+k_build_matrix_edges(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
+                     const double *__restrict__ gram, const double *__restrict__ rhs, const double *__restrict__ wxy,
+                     double *__restrict__ mat, double *__restrict__ sol)
+{
+    const int r = blockIdx.y;
+    if (!fit[r].active) return;
+    const int n = D->sz.mat_size, nK = D->sz.n_comp_ker, nc2 = D->sz.n_comp, ncomp = (nK - 1) * nc2;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    int I, J;
+    if (idx < n) { I = idx; J = 0; }
+    else if (idx < 2 * n) { I = idx - n; J = n; }
+    else {
+        const int e = idx - 2 * n, ibg = e / (n - 1);
+        if (ibg >= D->sz.n_bg_vectors) return;
+        I = ncomp + 1 + ibg; J = e - ibg * (n - 1) + 1;
+        if (J > I) return;
+    }
+    bm_element(D, stamps, fit, gram, rhs, wxy, mat, sol, r, I, J);
 }
 
 // ---------------------------------------------------------------------------- LU
@@ -547,14 +645,18 @@ k_lu_trail(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, double *_
     __syncthreads();
     const int jj = tid & 31, ib = tid >> 5;       // 8 row groups x 32 columns, 4 rows each
     if (j0 + jj >= n) return;
+    // the four rows of a thread advance together: each element's chain (product rounded, then the difference, kk
+    // ascending) is unchanged, but four independent chains are in flight instead of one
+    double v[4];
 #pragma unroll
-    for (int q = 0; q < 4; q++) {
-        const int i = ib * 4 + q;
-        if (i0 + i >= n) break;
-        double v = a[(long long)(i0 + i) * n + j0 + jj];
-        for (int kk = 0; kk < nb; kk++) v -= Ls[i][kk] * Us[kk][jj];
-        a[(long long)(i0 + i) * n + j0 + jj] = v;
+    for (int q = 0; q < 4; q++) v[q] = (i0 + ib * 4 + q < n) ? a[(long long)(i0 + ib * 4 + q) * n + j0 + jj] : 0.0;
+    for (int kk = 0; kk < nb; kk++) {
+        const double uu = Us[kk][jj];
+#pragma unroll
+        for (int q = 0; q < 4; q++) v[q] = __dsub_rn(v[q], __dmul_rn(Ls[ib * 4 + q][kk], uu));
     }
+#pragma unroll
+    for (int q = 0; q < 4; q++) if (i0 + ib * 4 + q < n) a[(long long)(i0 + ib * 4 + q) * n + j0 + jj] = v[q];
 }
 
 // lubksb.  Forward: column sweep in blocks of 32 (per row the terms are subtracted for j ascending).
@@ -807,8 +909,21 @@ int zb_launch_fit_solve(zb_ctx *ctx, cudaStream_t st)
     const zb_sizes &sz = ctx->sz;
     const int n = sz.mat_size, nR = sz.n_regions;
     k_wxy<<<(ctx->n_slots + 127) / 128, 128, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->n_slots, ctx->d_wxy); ZB_DBG("k_wxy");
-    dim3 gb((n + 1 + 15) / 16, (n + 15) / 16, nR);
-    k_build_matrix<<<gb, dim3(16, 16), 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_rhs, ctx->d_wxy, ctx->d_mat, ctx->d_sol); ZB_DBG("k_build_matrix");
+    static int bm_legacy = -1;
+    if (bm_legacy < 0) { const char *e = getenv("ZB_BM_LEGACY"); bm_legacy = (e && e[0] == '1') ? 1 : 0; }
+    if (bm_legacy) {
+        dim3 gb((n + 1 + 15) / 16, (n + 15) / 16, nR);
+        k_build_matrix<<<gb, dim3(16, 16), 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_rhs, ctx->d_wxy, ctx->d_mat, ctx->d_sol); ZB_DBG("k_build_matrix");
+    } else {
+        const int PP = sz.n_comp * sz.n_comp, G = PP >= 256 ? 1 : 256 / PP;
+        const int nb1 = sz.n_comp_ker - 1, nuv = nb1 * (nb1 + 1) / 2;
+        if (nuv > 0)
+            k_build_matrix_main<<<dim3((nuv + G * BM_R - 1) / (G * BM_R), nR), 256, (size_t)(sz.n_stamps + 1) * sizeof(int), st>>>(
+                ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_wxy, ctx->d_mat); ZB_DBG("k_build_matrix_main");
+        const int nedge = 2 * n + sz.n_bg_vectors * (n - 1);
+        k_build_matrix_edges<<<dim3((nedge + 255) / 256, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_rhs, ctx->d_wxy, ctx->d_mat, ctx->d_sol); ZB_DBG("k_build_matrix_edges");
+        ctx->launches++;
+    }
     k_lu_init<<<dim3((n + 3) / 4, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv); ZB_DBG("k_lu_init");
     const size_t smp = ((size_t)n * (LU_NB + 1) + n) * sizeof(double);
     if (smp > ZB_SMEM_OPTIN) { snprintf(ctx->err, sizeof ctx->err, "normal matrix of %d rows too large for the LU panel kernel", n); return ZB_ERR_UNSUPPORTED; }
