@@ -37,7 +37,7 @@ int zb_launch_stamp_search(zb_ctx *ctx, const float *conv_img, int first_cell, i
     if (dir_t < 0) dir_t = ctx->h_dev->conv_template;
     if (n_cells <= 0) return ZB_OK;
     size_t npx = (size_t)ctx->sz.fw_stamp * ctx->sz.fw_stamp;
-    size_t smem = npx * (sizeof(float) + sizeof(int) + 1) + 32 + ((npx + 31) / 32) * sizeof(unsigned);
+    size_t smem = npx * sizeof(float) + ((npx + 1) & ~(size_t)1) * sizeof(unsigned short) + npx + 32 + ((npx + 31) / 32) * sizeof(unsigned);
     unsigned char *gs = NULL;
     size_t per = 0;
     if (smem > ZB_SMEM_OPTIN) {
