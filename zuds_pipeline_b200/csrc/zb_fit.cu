@@ -367,21 +367,11 @@ __device__ static void bm_element(const ZbDev *__restrict__ D, const ZbStamp *__
     }
 }
 
-// One thread per element, every kind (the form of round 1; ZB_BM_LEGACY=1 selects it for A/B runs)
-__global__ void __launch_bounds__(256)
-k_build_matrix(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
-               const double *__restrict__ gram, const double *__restrict__ rhs, const double *__restrict__ wxy,
-               double *__restrict__ mat, double *__restrict__ sol)
-{
-    const int r = blockIdx.z;
-    if (!fit[r].active) return;
-    bm_element(D, stamps, fit, gram, rhs, wxy, mat, sol, r, blockIdx.y * 16 + threadIdx.y, blockIdx.x * 16 + threadIdx.x);
-}
 
 // The bulk of the normal matrix: elements (I, J) = (1 + i1*nc2 + wi, 1 + j1*nc2 + wj) with j1 <= i1, i.e.
-// sum over stamps of w[wi] * w[wj] * gram(i1+1, j1+1) (alard.c:905-913).  k_build_matrix spends ~20 instructions per
-// term (three loads, the stamp's state, a switch); at ko = 4 that made it the largest consumer of SM time of a pair
-// (n = 722: 2.8 of 7.3 ms, profiles/r02_launches_c1b_summary.txt).  Here a thread owns one (wi, wj) and BM_R pairs
+// sum over stamps of w[wi] * w[wj] * gram(i1+1, j1+1) (alard.c:905-913).  One thread per element through bm_element
+// is ~20 instructions per term (three loads, the stamp's state, a switch); at ko = 4 that made this step the largest
+// consumer of SM time of a pair (n = 722: 2.8 of 7.3 ms, profiles/r02_launches_c1b_summary.txt, r02_fit_ab_s25.txt).  Here a thread owns one (wi, wj) and BM_R pairs
 // (i1, j1): per stamp it forms w[wi] * w[wj] once and adds its product with BM_R gram entries, still one element per
 // accumulator, stamps ascending, (w * w) * g then the add, each rounded: the same sums bit for bit.
 #define BM_R 8
@@ -909,12 +899,7 @@ int zb_launch_fit_solve(zb_ctx *ctx, cudaStream_t st)
     const zb_sizes &sz = ctx->sz;
     const int n = sz.mat_size, nR = sz.n_regions;
     k_wxy<<<(ctx->n_slots + 127) / 128, 128, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->n_slots, ctx->d_wxy); ZB_DBG("k_wxy");
-    static int bm_legacy = -1;
-    if (bm_legacy < 0) { const char *e = getenv("ZB_BM_LEGACY"); bm_legacy = (e && e[0] == '1') ? 1 : 0; }
-    if (bm_legacy) {
-        dim3 gb((n + 1 + 15) / 16, (n + 15) / 16, nR);
-        k_build_matrix<<<gb, dim3(16, 16), 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_rhs, ctx->d_wxy, ctx->d_mat, ctx->d_sol); ZB_DBG("k_build_matrix");
-    } else {
+    {
         const int PP = sz.n_comp * sz.n_comp, G = PP >= 256 ? 1 : 256 / PP;
         const int nb1 = sz.n_comp_ker - 1, nuv = nb1 * (nb1 + 1) / 2;
         if (nuv > 0)
