@@ -87,7 +87,7 @@ def test_sub_name():
     assert subtraction.sub_name("/d/ztf_1_sciimg.fits", "/r/ref_2.fits") == "/d/sub.ztf_1_sciimg_ref_2.fits"
 
 
-@pytest.mark.parametrize("case", [CS.SMALL[1], CS.SMALL[4]], ids=lambda c: c.name)
+@pytest.mark.parametrize("case", [CS.SMALL[1], CS.SMALL[4], CS.BOTH[3]], ids=lambda c: c.name)
 def test_fits_products_match_reference_binary(case, oracle, tmp_path):
     """Keyword set / order / values and pixel data of the written FITS files against the files the
     unmodified reference binary wrote for the same command (volatile AUTHOR/ORIGIN/DATE values aside)."""
@@ -185,6 +185,25 @@ def test_hotpants_cli_shim(oracle, tmp_path):
     bad = subprocess.run([sys.executable, os.path.join(ROOT, "bin", "hotpants"), "-inim", "nope.fits", "-tmplim", "x", "-outim", "y"],
                          capture_output=True, text=True)
     assert bad.returncode != 0
+
+
+@pytest.mark.gpu
+def test_hotpants_cli_shim_default_direction(oracle, tmp_path):
+    """No -c on the command line: hotpants' own default, -c b (vargs.c:55-128); the two regions of this frame end up
+    convolved in opposite directions and CONVOLnn says so."""
+    case = [c for c in CS.BOTH if c.name == "dir_b_mixed_2x1"][0]
+    pair = CS.make_pair(case)
+    names = H.write_pair(pair, str(tmp_path))
+    names["out"] = str(tmp_path / "sub.fits")
+    toks = CS.command(case, pair, names, exe=os.path.join(ROOT, "bin", "hotpants")).split()
+    i = toks.index("-c")
+    del toks[i:i + 2]
+    pr = subprocess.run([sys.executable] + toks, capture_output=True, text=True)
+    assert pr.returncode == 0 and "SUCCESS" in pr.stderr, pr.stderr[-2000:]
+    o = H.run_oracle(oracle, CS.params_of(case, pair), *CS.inputs_of(case, pair))
+    diff, hdr = fitsio.read_image(names["out"])
+    assert (hdr["CONVOL00"], hdr["CONVOL01"]) == ("IMAGE", "TEMPLATE")
+    assert (np.abs(diff - o.diff) <= 1e-4 * np.maximum(o.noise, 1e-3)).all()
 
 
 def test_import_sets_hardware_queue_default():
