@@ -101,7 +101,7 @@ def test_fits_products_match_reference_binary(case, oracle, tmp_path):
     res = H.run_oracle(oracle, args.params, *CS.inputs_of(case, pair))
     out = tmp_path / "mine"
     out.mkdir()
-    for k in ("outim", "noise_image", "out_mask"):
+    for k in ("outim", "noise_image", "out_mask", "savexy"):
         args.files[k] = str(out / os.path.basename(args.files[k]))
     sci_hdr = fitsio.read_image(args.files["image"])[1]
     hotpants.write_outputs(args, sci_hdr, res, argv0=ref.cmd.split()[0])
@@ -130,6 +130,13 @@ def test_fits_products_match_reference_binary(case, oracle, tmp_path):
         assert hn[k] == pytest.approx(hr[k]) if isinstance(hn[k], float) else hn[k] == hr[k]
     assert [k for k in hn.keys() if k.startswith("NSCALO")] == [k for k in hr.keys() if k.startswith("NSCALO")]
     assert np.array_equal(fitsio.read_image(args.files["out_mask"])[0].astype(np.int32) & 0xffff, ref.mask & 0xffff)
+    # -savexy: the three ds9 region files, byte for byte (functions.c:75-127); a run whose only region is skipped writes none
+    for suffix in ("", ".all", ".skipped"):
+        theirs_xy = os.path.join(ref.workdir, "xy" + suffix)
+        if os.path.exists(theirs_xy):
+            assert open(args.files["savexy"] + suffix).read() == open(theirs_xy).read(), suffix
+        else:
+            assert not os.path.exists(args.files["savexy"] + suffix)
 
 
 def test_usage_text_has_version_on_line_2(capsys):

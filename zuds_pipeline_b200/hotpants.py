@@ -272,6 +272,35 @@ def write_outputs(args, sci_header, result, argv0="hotpants"):
         mh = copy_header(sci_header)
         mh["OBJECT"] = "Hotpants output Mask Image"
         fitsio.write_image(args.files["out_mask"], (m & 0xffff).astype(np.int32), mh)
+    if "savexy" in args.files and getattr(result, "stamps", None) is not None:
+        write_savexy(args.files["savexy"], result)
+
+
+def write_savexy(name, result):
+    """-savexy: the ds9 region files of hotpants/functions.c:75-127 (``name``: the sub-stamp in use per stamp,
+    ``name.all``: every sub-stamp found, ``name.skipped``: the ones given up), one block per region that was fitted.
+    The file is started by region 0 and appended to by the others (functions.c:84-92); a region convolving the image
+    is written one pixel further up and right than one convolving the template (main.c:1176 vs :1297)."""
+    sz = result.sizes
+    fw = sz.fw_ksstamp
+    for i in range(sz.n_regions):
+        r = result.regions[i]
+        if r.flags & 0x1:
+            continue
+        off = 1 if r.conv_template else 2
+        mode = "w" if i == 0 else "a"
+        with open(name, mode) as used, open(name + ".all", mode) as alls, open(name + ".skipped", mode) as skipped:
+            for f in (alls, used, skipped):
+                f.write("#%4s %4s\n" % ("X", "Y"))
+            for k in range(r.n_stamps):
+                s = result.stamps[i * sz.n_stamps + k]
+                for q in range(s.nss):
+                    x, y = s.xss[q] + r.bx_min + off, s.yss[q] + r.by_min + off
+                    alls.write("image;box(%4d,%4d,%d,%d) # color=yellow\n" % (x, y, fw, fw))
+                    if q == s.sscnt:
+                        used.write("image;box(%4d,%4d,%d,%d) # color=green\n" % (x, y, fw, fw))
+                    if q < s.sscnt:
+                        skipped.write("image;box(%4d,%4d,%d,%d) # color=red\n" % (x, y, fw, fw))
 
 
 def run_hotpants(command, device=None, ctx=None):
@@ -330,7 +359,7 @@ Required options:
 
 Options built into the B200 path (see hotpants/vargs.c:130-260 for their meaning):
    -tu -tuk -tl -tg -tr -tp -tni -tmi   -iu -iuk -il -ig -ir -ip -ini -imi
-   -ki(n/a) -r -kcs -ft -sft -nft -mins -mous -omi -gd(n/a) -nrx -nry -nsx -nsy -nss -rss -savexy(n/a)
+   -ki(n/a) -r -kcs -ft -sft -nft -mins -mous -omi -gd(n/a) -nrx -nry -nsx -nsy -nss -rss -savexy
    -c [t|i] -n [t|i|u] -fom [v] -sconv(n/a) -ko -bgo -ssig -ks -kfm -okn -fi -fin -convvar
    -oni -hki -nc -ng -v
 """ % VERSION
