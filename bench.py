@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — ZTF quadrant subtractions per second on N B200s (BASELINE.json metric).
 
-    python bench.py --gpus N --steps K --warmup W [--workload c1|c1b|c4|c5|batch256]   # this repo's CUDA path
+    python bench.py --gpus N --steps K --warmup W [--workload c1|c1b|c1_dir_b|c4|c5|batch256]   # this repo's CUDA path
     python bench.py --impl reference --gpus N --steps K ... [--workload ...]           # the reference hotpants on the host cores
 
 Workloads ("Notation and sizes"; the same string goes into `config.workload` of both arms):
@@ -55,6 +55,7 @@ WORKLOADS = {
     "c1b": ("c1b", "c1b: 3080x3072 quadrant pair as zuds calls it at seeing 2 px, -c t -n i -r 5 -rss 12 -ko 4 -bgo 0, 3x3 regions x 10x10 stamps"),
     "c4": ("c4", "c4: 3080x3072 quadrant pair, -c i -n i -r 15 -rss 15 -ko 4 -bgo 0, 1 region x 32x32 stamps (BASELINE configs[3])"),
     "batch256": ("c1", "batch256: 256 distinct 3080x3072 pairs (seeds 1000..1255) as c1, sharded by image over the ranks (BASELINE configs[2])"),
+    "c1_dir_b": ("c1_dir_b", "c1_dir_b: c1 with hotpants' own default -c b (direction chosen per region by check_stamps) on a pair whose science PSF is narrower than the reference's on the left and broader on the right"),
     "c5": ("c5", "c5: one 6160x6144 pair, -c t -n i -r 10 -rss 24 -ko 2 -bgo 0 -nrx 1 -nry 1 -nsx 20 -nsy 20, row tiles over the ranks (BASELINE configs[4])"),
 }
 
