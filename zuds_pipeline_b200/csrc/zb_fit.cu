@@ -314,149 +314,178 @@ __global__ void k_wxy(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ s
     }
 }
 
-__device__ static inline double gram_at(const double *g, int u, int v) {   // u >= v
-    return g[u * (u + 1) / 2 + v];
-}
-
-// One matrix element (I >= J) or right-hand-side element (J == n); stamps summed in ascending order.
-__device__ static void bm_element(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
-                                  const double *__restrict__ gram, const double *__restrict__ rhs, const double *__restrict__ wxy,
-                                  double *__restrict__ mat, double *__restrict__ sol, int r, int I, int J)
-{
-    const int n = D->sz.mat_size, nK = D->sz.n_comp_ker, nc2 = D->sz.n_comp, ncomp = (nK - 1) * nc2;
-    const int nvec = nK + D->sz.n_bg_vectors, npair = nvec * (nvec + 1) / 2;
-    if (I >= n || J > n || (J < n && J > I)) return;
-    const int base = D->reg[r].stamp_base, nS = fit[r].n_stamps;
-    // classify the element once
-    int kind, u = 0, v = 0, wi = -1, wj = -1;
-    if (J == n) {                                     // right-hand side
-        if (I == 0) { kind = 10; u = 0; }
-        else if (I <= ncomp) { kind = 11; u = (I - 1) / nc2 + 1; wi = (I - 1) % nc2; }
-        else { kind = 10; u = nK + (I - ncomp - 1); }
-    } else if (I == 0) { kind = 0; u = 0; v = 0; }
-    else if (I <= ncomp) {
-        int i = I - 1, i1 = i / nc2; wi = i - i1 * nc2;
-        if (J == 0) { kind = 1; u = i1 + 1; v = 0; }
-        else { int j = J - 1, j1 = j / nc2; wj = j - j1 * nc2; kind = 2; u = i1 + 1; v = j1 + 1; }
-    } else {
-        int ibg = I - ncomp - 1; u = nK + ibg;
-        if (J == 0) { kind = 0; v = 0; }
-        else if (J <= ncomp) { int j = J - 1, j1 = j / nc2; wi = j - j1 * nc2; kind = 1; v = j1 + 1; }
-        else { kind = 0; v = nK + (J - ncomp - 1); }
-    }
-    double acc = 0.0;
-    for (int k = 0; k < nS; k++) {
-        const int slot = base + k;
-        const ZbStamp &S = stamps[slot];
-        if (S.sscnt >= S.nss || S.excl) continue;           // excl: only ever set during check_stamps' trial fit (-c b)
-        const double *g = gram + (long long)slot * npair;
-        const double *w = wxy + (long long)slot * nc2;
-        switch (kind) {
-        case 0:  acc += gram_at(g, u, v); break;
-        case 1:  acc += w[wi] * gram_at(g, u, v); break;
-        case 2:  acc += w[wi] * w[wj] * gram_at(g, u, v); break;
-        case 10: acc += rhs[(long long)slot * nvec + u]; break;
-        default: acc += rhs[(long long)slot * nvec + u] * w[wi]; break;
-        }
-    }
-    if (J == n) sol[(long long)r * (D->sz.n_comp_total + 1) + I + 1] = acc;     // 1-indexed like kernelSol
-    else {
-        double *M = mat + (long long)r * n * n;
-        M[(long long)I * n + J] = acc;
-        M[(long long)J * n + I] = acc;
-    }
-}
-
+// per-stamp normal matrices are packed lower triangles: gram(u, v), u >= v, sits at u (u + 1) / 2 + v
 
 // The bulk of the normal matrix: elements (I, J) = (1 + i1*nc2 + wi, 1 + j1*nc2 + wj) with j1 <= i1, i.e.
-// sum over stamps of w[wi] * w[wj] * gram(i1+1, j1+1) (alard.c:905-913).  One thread per element through bm_element
-// is ~20 instructions per term (three loads, the stamp's state, a switch); at ko = 4 that made this step the largest
+// sum over stamps of w[wi] * w[wj] * gram(i1+1, j1+1) (alard.c:905-913).  One thread per element, every kind of element through one
+// switch, was ~20 instructions per term (three loads, the stamp's state, a switch); at ko = 4 that made this step the largest
 // consumer of SM time of a pair (n = 722: 2.8 of 7.3 ms, profiles/r02_launches_c1b_summary.txt, r02_fit_ab_s25.txt).  Here a thread owns one (wi, wj) and BM_R pairs
 // (i1, j1): per stamp it forms w[wi] * w[wj] once and adds its product with BM_R gram entries, still one element per
 // accumulator, stamps ascending, (w * w) * g then the add, each rounded: the same sums bit for bit.
 #define BM_R 8
+#define BM_CS 16                                     // stamps staged per round
+#define BM_GROUPS(PP) ((PP) >= 256 ? 1 : (256 / (PP) > 32 ? 32 : 256 / (PP)))   // at most 32: the staged record stays small at ko <= 1
 __global__ void __launch_bounds__(256)
 k_build_matrix_main(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
                     const double *__restrict__ gram, const double *__restrict__ wxy, double *__restrict__ mat)
 {
-    extern __shared__ int s_act[];                   // slots of the stamps that enter the sums, ascending
+    extern __shared__ __align__(16) unsigned char bm_dyn[];
     __shared__ int s_nact;
     const int r = blockIdx.y;
     if (!fit[r].active) return;
     const int n = D->sz.mat_size, nK = D->sz.n_comp_ker, nc2 = D->sz.n_comp, PP = nc2 * nc2;
     const int nvec = nK + D->sz.n_bg_vectors, npair = nvec * (nvec + 1) / 2;
     const int nb1 = nK - 1, nuv = nb1 * (nb1 + 1) / 2;
-    const int base = D->reg[r].stamp_base, nS = fit[r].n_stamps;
-    if (threadIdx.x == 0) {
+    const int base = D->reg[r].stamp_base, nS = fit[r].n_stamps, tid = threadIdx.x;
+    const int G = BM_GROUPS(PP);                     // (wi, wj) groups side by side in a CTA
+    const int NE = G * BM_R, L = NE + nc2;           // staged per stamp: the CTA's gram entries, then the stamp's weights
+    double *buf = (double *)bm_dyn;                  // [BM_CS][L]
+    int *s_act = (int *)(buf + (size_t)BM_CS * L);   // slots of the stamps that enter the sums, ascending
+    int *s_goff = s_act + D->sz.n_stamps;            // [NE] packed-gram offset of every (i1, j1) pair of the CTA, -1 beyond the last
+    if (tid == 0) {
         int c = 0;
         for (int k = 0; k < nS; k++) { const ZbStamp &S = stamps[base + k]; if (!(S.sscnt >= S.nss || S.excl)) s_act[c++] = base + k; }
         s_nact = c;
     }
+    const int qc = blockIdx.x * NE;                  // first (i1, j1) pair of the CTA, triangular order
+    for (int e = tid; e < NE; e += 256) {
+        const int q = qc + e;
+        int off = -1;
+        if (q < nuv) {
+            int i1 = (int)((sqrt(8.0 * q + 1.0) - 1.0) * 0.5);
+            while ((i1 + 1) * (i1 + 2) / 2 <= q) i1++;
+            while (i1 * (i1 + 1) / 2 > q) i1--;
+            const int j1 = q - i1 * (i1 + 1) / 2, u = i1 + 1, v = j1 + 1;
+            off = u * (u + 1) / 2 + v;
+        }
+        s_goff[e] = off;
+    }
     __syncthreads();
     const int nA = s_nact;
-    const int G = PP >= 256 ? 1 : 256 / PP;          // (wi, wj) groups side by side in a CTA
-    const int grp = PP >= 256 ? 0 : threadIdx.x / PP;
-    if (grp >= G) return;
-    const int q0 = (blockIdx.x * G + grp) * BM_R;    // first (i1, j1) pair of this group, triangular order
-    if (q0 >= nuv) return;
-    int i1_0 = (int)((sqrt(8.0 * q0 + 1.0) - 1.0) * 0.5);
-    while ((i1_0 + 1) * (i1_0 + 2) / 2 <= q0) i1_0++;
-    while (i1_0 * (i1_0 + 1) / 2 > q0) i1_0--;
-    const int j1_0 = q0 - i1_0 * (i1_0 + 1) / 2;
+    const int grp = PP >= 256 ? 0 : tid / PP;
+    const bool worker = grp < G && qc + grp * BM_R < nuv;
     double *M = mat + (long long)r * n * n;
-    for (int p = PP >= 256 ? threadIdx.x : threadIdx.x - grp * PP; p < PP; p += (PP >= 256 ? 256 : PP)) {
-        const int wi = p / nc2, wj = p - wi * nc2;
-        int goff[BM_R]; double acc[BM_R];
-        {
-            int i1 = i1_0, j1 = j1_0;
+    for (int p0 = 0; p0 < PP; p0 += 256) {           // one round unless ko >= 5 (more than 256 (wi, wj) pairs)
+        const int p = PP >= 256 ? p0 + tid : tid - grp * PP;
+        const bool mine = worker && p < PP;
+        const int wi = mine ? p / nc2 : 0, wj = mine ? p - wi * nc2 : 0;
+        double acc[BM_R];
+#pragma unroll
+        for (int e = 0; e < BM_R; e++) acc[e] = 0.0;
+        for (int c0 = 0; c0 < nA; c0 += BM_CS) {
+            const int ns = min(BM_CS, nA - c0);
+            __syncthreads();                         // the previous round's values have been consumed
+            for (int idx = tid; idx < ns * L; idx += 256) {
+                const int sidx = idx / L, o = idx - sidx * L, slot = s_act[c0 + sidx];
+                double v = 0.0;
+                if (o < NE) { const int off = s_goff[o]; if (off >= 0) v = gram[(long long)slot * npair + off]; }
+                else v = wxy[(long long)slot * nc2 + (o - NE)];
+                buf[idx] = v;
+            }
+            __syncthreads();
+            if (mine)
+                for (int k = 0; k < ns; k++) {
+                    const double *b = buf + (size_t)k * L;
+                    const double ww = __dmul_rn(b[NE + wi], b[NE + wj]);
+#pragma unroll
+                    for (int e = 0; e < BM_R; e++) acc[e] = __dadd_rn(acc[e], __dmul_rn(ww, b[grp * BM_R + e]));
+                }
+        }
+        if (mine) {
 #pragma unroll
             for (int e = 0; e < BM_R; e++) {
-                const int u = i1 + 1, v = j1 + 1;
-                goff[e] = (q0 + e < nuv) ? u * (u + 1) / 2 + v : 0;
-                acc[e] = 0.0;
-                if (++j1 > i1) { i1++; j1 = 0; }
-            }
-        }
-        for (int k = 0; k < nA; k++) {
-            const int slot = s_act[k];
-            const double *w = wxy + (long long)slot * nc2;
-            const double *g = gram + (long long)slot * npair;
-            const double ww = __dmul_rn(w[wi], w[wj]);
-#pragma unroll
-            for (int e = 0; e < BM_R; e++) acc[e] = __dadd_rn(acc[e], __dmul_rn(ww, g[goff[e]]));
-        }
-        int i1 = i1_0, j1 = j1_0;
-#pragma unroll
-        for (int e = 0; e < BM_R; e++) {
-            if (q0 + e < nuv) {
-                const int I = 1 + i1 * nc2 + wi, J = 1 + j1 * nc2 + wj;
+                const int off = s_goff[grp * BM_R + e];
+                if (off < 0) continue;
+                int u = (int)((sqrt(8.0 * off + 1.0) - 1.0) * 0.5);
+                while ((u + 1) * (u + 2) / 2 <= off) u++;
+                while (u * (u + 1) / 2 > off) u--;
+                const int v = off - u * (u + 1) / 2;            // off = u(u+1)/2 + v, 1 <= v <= u
+                const int I = 1 + (u - 1) * nc2 + wi, J = 1 + (v - 1) * nc2 + wj;
                 if (J <= I) { M[(long long)I * n + J] = acc[e]; M[(long long)J * n + I] = acc[e]; }
             }
-            if (++j1 > i1) { i1++; j1 = 0; }
         }
     }
 }
 
-// Everything else: column 0, the background rows and the right-hand side, by the generic element code.
+// Everything else: column 0, the background rows and the right-hand side (alard.c:915-953, 967-1025).
+// A term is value or w * value with value one of gram(u, 0), rhs[u], gram(nK + ibg, v): those are staged per round
+// of BM_CS stamps together with the stamp's weights, so an element's sum (stamps ascending, one add per stamp) reads
+// shared memory only; with one global load chain per stamp and element this step took 94 us at 100 stamps per region
+// and 0.9 ms at 1024 (profiles/r02_launches_c1b_after_summary.txt).
 __global__ void __launch_bounds__(256)
 k_build_matrix_edges(const ZbDev *__restrict__ D, const ZbStamp *__restrict__ stamps, const ZbFit *__restrict__ fit,
                      const double *__restrict__ gram, const double *__restrict__ rhs, const double *__restrict__ wxy,
-                     double *__restrict__ mat, double *__restrict__ sol)
+                     double *__restrict__ mat, double *__restrict__ sol, int cs)
 {
+    extern __shared__ __align__(16) unsigned char bm_dyn[];
+    __shared__ int s_nact;
     const int r = blockIdx.y;
     if (!fit[r].active) return;
     const int n = D->sz.mat_size, nK = D->sz.n_comp_ker, nc2 = D->sz.n_comp, ncomp = (nK - 1) * nc2;
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    int I, J;
-    if (idx < n) { I = idx; J = 0; }
-    else if (idx < 2 * n) { I = idx - n; J = n; }
-    else {
-        const int e = idx - 2 * n, ibg = e / (n - 1);
-        if (ibg >= D->sz.n_bg_vectors) return;
-        I = ncomp + 1 + ibg; J = e - ibg * (n - 1) + 1;
-        if (J > I) return;
+    const int nbg = D->sz.n_bg_vectors, nvec = nK + nbg, npair = nvec * (nvec + 1) / 2;
+    const int base = D->reg[r].stamp_base, nS = fit[r].n_stamps, tid = threadIdx.x;
+    const int OW = (2 + nbg) * nvec, L = OW + nc2;   // per stamp: gram(u,0) | rhs[u] | gram(nK+ibg, v) rows | weights
+    double *buf = (double *)bm_dyn;                  // [cs][L], cs stamps staged per round
+    int *s_act = (int *)(buf + (size_t)cs * L);
+    if (tid == 0) {
+        int c = 0;
+        for (int k = 0; k < nS; k++) { const ZbStamp &S = stamps[base + k]; if (!(S.sscnt >= S.nss || S.excl)) s_act[c++] = base + k; }
+        s_nact = c;
     }
-    bm_element(D, stamps, fit, gram, rhs, wxy, mat, sol, r, I, J);
+    // this thread's element: where its value sits in a staged record (ia), which weight multiplies it (iw, -1: none)
+    const int idx = blockIdx.x * 256 + tid;
+    int I = -1, J = -1, ia = 0, iw = -1;
+    if (idx < n) {                                   // column 0
+        I = idx; J = 0;
+        if (I == 0) ia = 0;
+        else if (I <= ncomp) { const int i1 = (I - 1) / nc2; iw = (I - 1) - i1 * nc2; ia = i1 + 1; }
+        else ia = nK + (I - ncomp - 1);
+    } else if (idx < 2 * n) {                        // right-hand side
+        I = idx - n; J = n;
+        if (I == 0) ia = nvec;
+        else if (I <= ncomp) { const int i1 = (I - 1) / nc2; iw = (I - 1) - i1 * nc2; ia = nvec + i1 + 1; }
+        else ia = nvec + nK + (I - ncomp - 1);
+    } else {                                         // background rows, J = 1 .. I
+        const int e = idx - 2 * n, ibg = e / (n - 1);
+        if (ibg < nbg) {
+            const int Ib = ncomp + 1 + ibg, Jb = e - ibg * (n - 1) + 1;
+            if (Jb <= Ib) {
+                I = Ib; J = Jb;
+                if (J <= ncomp) { const int j1 = (J - 1) / nc2; iw = (J - 1) - j1 * nc2; ia = (2 + ibg) * nvec + j1 + 1; }
+                else ia = (2 + ibg) * nvec + nK + (J - ncomp - 1);
+            }
+        }
+    }
+    __syncthreads();
+    const int nA = s_nact;
+    double acc = 0.0;
+    for (int c0 = 0; c0 < nA; c0 += cs) {
+        const int ns = min(cs, nA - c0);
+        __syncthreads();
+        for (int q = tid; q < ns * L; q += 256) {
+            const int sidx = q / L, o = q - sidx * L, slot = s_act[c0 + sidx];
+            const double *g = gram + (long long)slot * npair;
+            double v = 0.0;
+            if (o < nvec) v = g[o * (o + 1) / 2];
+            else if (o < 2 * nvec) v = rhs[(long long)slot * nvec + (o - nvec)];
+            else if (o < OW) { const int ibg = (o - 2 * nvec) / nvec, vv = (o - 2 * nvec) - ibg * nvec, u = nK + ibg; if (vv <= u) v = g[u * (u + 1) / 2 + vv]; }
+            else v = wxy[(long long)slot * nc2 + (o - OW)];
+            buf[q] = v;
+        }
+        __syncthreads();
+        if (I >= 0)
+            for (int k = 0; k < ns; k++) {
+                const double *b = buf + (size_t)k * L;
+                acc = __dadd_rn(acc, iw >= 0 ? __dmul_rn(b[OW + iw], b[ia]) : b[ia]);
+            }
+    }
+    if (I < 0) return;
+    if (J == n) sol[(long long)r * (D->sz.n_comp_total + 1) + I + 1] = acc;     // 1-indexed like kernelSol
+    else {
+        double *M = mat + (long long)r * n * n;
+        M[(long long)I * n + J] = acc;
+        M[(long long)J * n + I] = acc;
+    }
 }
 
 // ---------------------------------------------------------------------------- LU
@@ -857,40 +886,66 @@ __device__ static void sigma_clip_seq(const float *data, char *rej, int count, d
     }
 }
 
-// check_again: one thread per region walks its stamps in order (the decisions are sequential and tiny).
-__global__ void k_clip(const ZbDev *__restrict__ D, ZbStamp *__restrict__ stamps, ZbFit *__restrict__ fit,
-                       float *__restrict__ ss_scratch, char *__restrict__ rej_scratch, int *__restrict__ jobs, int *__restrict__ njobs)
+// check_again (alard.c:1143-1247), one CTA per region.  The per-stamp steps are independent and run one stamp per
+// thread; the sigma clip in between sums in stamp order (sequential by definition) and is done by one thread on
+// shared memory.  As one thread per region walking global memory this took 137 us at 100 stamps per region and
+// ~1.4 ms at 1024, once per clip iteration (profiles/r02_launches_c1b_after_summary.txt).
+__global__ void __launch_bounds__(256)
+k_clip(const ZbDev *__restrict__ D, ZbStamp *__restrict__ stamps, ZbFit *__restrict__ fit, int *__restrict__ jobs, int *__restrict__ njobs)
 {
-    const int r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= D->n_regions) return;
+    extern __shared__ __align__(16) unsigned char clip_dyn[];
+    const int r = blockIdx.x, tid = threadIdx.x;
     ZbFit &F = fit[r];
     if (!F.active) return;
     const int base = D->reg[r].stamp_base, nS = F.n_stamps, cap = D->sz.n_stamps;
-    float *ss = ss_scratch + (long long)r * cap;
-    char *rej = rej_scratch + (long long)r * cap;
-    int nss = 0, check = 0, nskip = 0;
-    for (int k = 0; k < nS; k++) {
+    double *chi2 = (double *)clip_dyn;               // [cap] figure the second test uses (a bumped stamp keeps its previous one)
+    float *val = (float *)(chi2 + cap);              // [cap] (float)sig1 of the stamps that enter the clip
+    float *ss = val + cap;                           // [cap] the same, compacted in stamp order
+    int *sc = (int *)(ss + cap);                     // [cap] sscnt
+    int *ns_ = sc + cap;                             // [cap] nss
+    char *live = (char *)(ns_ + cap);                // [cap] enters the clip
+    char *rej = live + cap;                          // [cap]
+    char *refill = rej + cap;                        // [cap]
+    __shared__ double s_mean, s_sd;
+    __shared__ int s_check, s_nskip;
+    if (tid == 0) { s_check = 0; s_nskip = 0; }
+    __syncthreads();
+    for (int k = tid; k < nS; k += 256) {
         ZbStamp &S = stamps[base + k];
-        S.refill = 0;
-        if (S.sscnt < S.nss) {
-            if (S.sig1 == -1) { S.sscnt++; S.refill = 1; check = 1; }
-            else { S.chi2 = S.sig1; ss[nss++] = (float)S.sig1; }
-        } else nskip++;
+        int sscnt = S.sscnt; const int nss = S.nss;
+        char lv = 0, rf = 0;
+        double c2 = S.chi2;
+        if (sscnt < nss) {
+            const double sig1 = S.sig1;
+            if (sig1 == -1) { sscnt++; rf = 1; s_check = 1; }
+            else { c2 = sig1; lv = 1; val[k] = (float)sig1; }
+        } else atomicAdd(&s_nskip, 1);
+        chi2[k] = c2; sc[k] = sscnt; ns_[k] = nss; live[k] = lv; refill[k] = rf;
     }
-    double mean = 0, stdev = 0;
-    sigma_clip_seq(ss, rej, nss, &mean, &stdev, 10, D->p.stat_sig);
-    for (int k = 0; k < nS; k++) {
+    __syncthreads();
+    if (tid == 0) {
+        int nss = 0;
+        for (int k = 0; k < nS; k++) if (live[k]) ss[nss++] = val[k];
+        double mean = 0, stdev = 0;
+        sigma_clip_seq(ss, rej, nss, &mean, &stdev, 10, D->p.stat_sig);
+        s_mean = mean; s_sd = stdev;
+    }
+    __syncthreads();
+    const double mean = s_mean, stdev = s_sd;
+    for (int k = tid; k < nS; k += 256) {
+        if (sc[k] < ns_[k] && (chi2[k] - mean) > D->p.ker_sig_reject * stdev) { sc[k]++; refill[k] = 1; s_check = 1; }
         ZbStamp &S = stamps[base + k];
-        if (S.sscnt < S.nss) {
-            if ((S.chi2 - mean) > D->p.ker_sig_reject * stdev) { S.sscnt++; S.refill = 1; check = 1; }
-        }
+        S.sscnt = sc[k]; S.refill = refill[k]; S.chi2 = chi2[k];
     }
-    for (int k = 0; k < nS; k++) {
-        ZbStamp &S = stamps[base + k];
-        if (S.refill && S.sscnt < S.nss) { int q = atomicAdd(njobs, 1); jobs[q] = base + k; }
+    __syncthreads();
+    if (tid == 0) {
+        int cnt = 0;
+        for (int k = 0; k < nS; k++) cnt += (refill[k] && sc[k] < ns_[k]);
+        int q = cnt ? atomicAdd(njobs, cnt) : 0;
+        for (int k = 0; k < nS; k++) if (refill[k] && sc[k] < ns_[k]) jobs[q++] = base + k;
+        F.meansig = mean; F.scatter = stdev; F.n_skipped = s_nskip; F.iters++;
+        F.active = s_check;
     }
-    F.meansig = mean; F.scatter = stdev; F.n_skipped = nskip; F.iters++;
-    F.active = check;
 }
 
 // wxy + global normal equations + LU solve (alard.c:343-360) for every active region
@@ -900,13 +955,23 @@ int zb_launch_fit_solve(zb_ctx *ctx, cudaStream_t st)
     const int n = sz.mat_size, nR = sz.n_regions;
     k_wxy<<<(ctx->n_slots + 127) / 128, 128, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->n_slots, ctx->d_wxy); ZB_DBG("k_wxy");
     {
-        const int PP = sz.n_comp * sz.n_comp, G = PP >= 256 ? 1 : 256 / PP;
+        const int PP = sz.n_comp * sz.n_comp, G = BM_GROUPS(PP);
         const int nb1 = sz.n_comp_ker - 1, nuv = nb1 * (nb1 + 1) / 2;
+        const size_t sm_main = (size_t)BM_CS * (G * BM_R + sz.n_comp) * sizeof(double) + (size_t)(sz.n_stamps + G * BM_R + 1) * sizeof(int);
+        // the edge records grow with the background order ((2 + nbg) * nvec values per stamp): fewer stamps per round then
+        const size_t rec_edge = ((size_t)(2 + sz.n_bg_vectors) * (sz.n_comp_ker + sz.n_bg_vectors) + sz.n_comp) * sizeof(double);
+        const size_t act_bytes = (size_t)(sz.n_stamps + 1) * sizeof(int);
+        int cs_edge = BM_CS;
+        while (cs_edge > 1 && cs_edge * rec_edge + act_bytes > (size_t)ZB_SMEM_OPTIN / 2) cs_edge /= 2;
+        const size_t sm_edge = cs_edge * rec_edge + act_bytes;
+        if (sm_main > ZB_SMEM_OPTIN || sm_edge > ZB_SMEM_OPTIN) { snprintf(ctx->err, sizeof ctx->err, "%d stamps per region too many for the normal-matrix kernels", sz.n_stamps); return ZB_ERR_UNSUPPORTED; }
+        cudaFuncSetAttribute(k_build_matrix_main, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
+        cudaFuncSetAttribute(k_build_matrix_edges, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
         if (nuv > 0)
-            k_build_matrix_main<<<dim3((nuv + G * BM_R - 1) / (G * BM_R), nR), 256, (size_t)(sz.n_stamps + 1) * sizeof(int), st>>>(
+            k_build_matrix_main<<<dim3((nuv + G * BM_R - 1) / (G * BM_R), nR), 256, sm_main, st>>>(
                 ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_wxy, ctx->d_mat); ZB_DBG("k_build_matrix_main");
         const int nedge = 2 * n + sz.n_bg_vectors * (n - 1);
-        k_build_matrix_edges<<<dim3((nedge + 255) / 256, nR), 256, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_rhs, ctx->d_wxy, ctx->d_mat, ctx->d_sol); ZB_DBG("k_build_matrix_edges");
+        k_build_matrix_edges<<<dim3((nedge + 255) / 256, nR), 256, sm_edge, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_gram, ctx->d_rhs, ctx->d_wxy, ctx->d_mat, ctx->d_sol, cs_edge); ZB_DBG("k_build_matrix_edges");
         ctx->launches++;
     }
     k_lu_init<<<dim3((n + 3) / 4, nR), 128, 0, st>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_vv); ZB_DBG("k_lu_init");
@@ -982,8 +1047,10 @@ int zb_launch_clip(zb_ctx *ctx, cudaStream_t st)
     const zb_sizes &sz = ctx->sz;
     const int nR = sz.n_regions;
     zb_zero_small(ctx, ctx->d_njobs, sizeof(int), st);
-    k_clip<<<(nR + 31) / 32, 32, 0, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, (float *)ctx->d_stats, (char *)(ctx->d_stats) + (size_t)nR * sz.n_stamps * sizeof(float),
-                                          ctx->d_jobs, ctx->d_njobs); ZB_DBG("k_clip");
+    const size_t sm = (size_t)sz.n_stamps * (sizeof(double) + 2 * sizeof(float) + 2 * sizeof(int) + 3) + 16;
+    if (sm > ZB_SMEM_OPTIN) { snprintf(ctx->err, sizeof ctx->err, "%d stamps per region too many for the clip kernel", sz.n_stamps); return ZB_ERR_UNSUPPORTED; }
+    cudaFuncSetAttribute(k_clip, cudaFuncAttributeMaxDynamicSharedMemorySize, ZB_SMEM_OPTIN);
+    k_clip<<<nR, 256, sm, st>>>(ctx->d_dev, ctx->d_stamps, ctx->d_fit, ctx->d_jobs, ctx->d_njobs); ZB_DBG("k_clip");
     ctx->launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "clip", __FILE__, __LINE__);
