@@ -572,7 +572,21 @@ k_lu_panel(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, double *_
                 double *row = P + i * ld;
                 const double l = row[kk] * dum;
                 row[kk] = l;
-                for (int c = kk + 1; c < nb; c++) row[c] -= l * P[kk * ld + c];
+                // eight columns at a time, every load ahead of the first store: a store to `row` might alias the pivot
+                // row for all the compiler knows, and an in-order warp then waits out one load-multiply-subtract
+                // chain per column
+                const double *prow = P + kk * ld;
+                int c = kk + 1;
+                for (; c + 8 <= nb; c += 8) {
+                    double pv[8], rv[8];
+#pragma unroll
+                    for (int q = 0; q < 8; q++) { pv[q] = prow[c + q]; rv[q] = row[c + q]; }
+#pragma unroll
+                    for (int q = 0; q < 8; q++) rv[q] = __dsub_rn(rv[q], __dmul_rn(l, pv[q]));
+#pragma unroll
+                    for (int q = 0; q < 8; q++) row[c + q] = rv[q];
+                }
+                for (; c < nb; c++) row[c] = __dsub_rn(row[c], __dmul_rn(l, prow[c]));
             }
         }
         __syncthreads();
@@ -595,18 +609,30 @@ k_lu_swap_u(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, double *
     const int n = D->sz.mat_size, nb = min(LU_NB, n - k0);
     double *a = mat + (long long)r * n * n;
     for (int e = threadIdx.x; e < nb * nb; e += blockDim.x) { int i = e / nb, c = e - i * nb; L[i][c] = a[(long long)(k0 + i) * n + k0 + c]; }
-    if (threadIdx.x == 0) {
-        // positions 0..nb-1 are the panel rows; pivots outside the panel are appended once each
+    if (threadIdx.x < 32) {
+        // positions 0..nb-1 are the panel rows; pivots outside the panel are appended once each.  Warp 0 composes the
+        // permutation: the panel's pivots are fetched once (one per lane), the look-up among the appended rows is a
+        // ballot.  (One thread reading a pivot from global memory per step and scanning the list was two thirds of
+        // this kernel's 32 us.)
+        const int lane = threadIdx.x;
+        const int my_ip = lane < nb ? indxs[(long long)r * n + k0 + lane] : 0;
+        if (lane < nb) { rows[lane] = k0 + lane; src[lane] = lane; }
+        __syncwarp();
         int nrow = nb;
-        for (int q = 0; q < nb; q++) { rows[q] = k0 + q; src[q] = q; }
         for (int kk = 0; kk < nb; kk++) {
-            const int ip = indxs[(long long)r * n + k0 + kk];
-            int pos = -1;
+            const int ip = __shfl_sync(0xffffffffu, my_ip, kk);
+            int pos;
             if (ip < k0 + nb) pos = ip - k0;
-            else { for (int q = nb; q < nrow; q++) if (rows[q] == ip) pos = q; if (pos < 0) { pos = nrow; rows[nrow] = ip; src[nrow] = nrow; nrow++; } }
-            const int t = src[pos]; src[pos] = src[kk]; src[kk] = t;      // after all swaps position p holds original row rows[src[p]]
+            else {
+                const unsigned hit = __ballot_sync(0xffffffffu, nb + lane < nrow && rows[nb + lane] == ip);   // at most nb <= 32 appended rows
+                if (hit) pos = nb + __ffs(hit) - 1;
+                else { pos = nrow; if (lane == 0) { rows[nrow] = ip; src[nrow] = nrow; } nrow++; }
+            }
+            __syncwarp();
+            if (lane == 0) { const int t = src[pos]; src[pos] = src[kk]; src[kk] = t; }      // after all swaps position p holds original row rows[src[p]]
+            __syncwarp();
         }
-        s_nrow = nrow;
+        if (lane == 0) s_nrow = nrow;
     }
     __syncthreads();
     int j = blockIdx.x * blockDim.x + threadIdx.x;           // index among the n - nb outside columns
