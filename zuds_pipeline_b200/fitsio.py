@@ -208,6 +208,24 @@ def read_image(path, hdu=0):
     return data, hdr
 
 
+def read_header(path):
+    """The primary header alone (the pixels are not read)."""
+    size = 16 * BLOCK
+    while True:
+        buf = np.fromfile(path, dtype=np.uint8, count=size)
+        try:
+            hdr = _read_header(buf, 0)[0]
+            # as read_hdus: scaling cards other than the neutral ones belong to the stored integers, not to the pixels
+            if float(hdr.get("BSCALE", 1.0)) != 1.0 or float(hdr.get("BZERO", 0.0)) != 0.0:
+                hdr.remove("BSCALE")
+                hdr.remove("BZERO")
+            return hdr
+        except IOError:
+            if len(buf) < size:
+                raise
+            size *= 4
+
+
 def _header_bytes(cards80):
     text = "".join(cards80) + "END".ljust(80)
     pad = (-len(text)) % BLOCK
@@ -246,9 +264,9 @@ def write_image(path, data, header=None, extra_hdus=()):
         data = (data.astype(np.int32) - 32768).astype(np.int16)
     with open(path, "wb") as f:
         f.write(_header_bytes(cards))
-        raw = data.astype(_DT[bitpix]).tobytes()
-        f.write(raw)
-        f.write(b"\0" * ((-len(raw)) % BLOCK))
+        raw = np.ascontiguousarray(data.astype(_DT[bitpix], copy=False))      # big-endian copy, written from its own buffer
+        f.write(raw.reshape(-1).view(np.uint8))
+        f.write(b"\0" * ((-raw.nbytes) % BLOCK))
         for kind, hdr, arr in extra_hdus:
             assert kind == "bintable"
             arr = np.ascontiguousarray(arr, dtype=np.float64)

@@ -254,7 +254,8 @@ def _read_float(path):
 
 
 def write_outputs(args, sci_header, result, argv0="hotpants"):
-    """Write -outim (+ -hki table), -oni and -omi exactly where the command line says."""
+    """Write -outim (+ -hki table), -oni and -omi exactly where the command line says.  Returns the extension HDUs
+    of -outim as ``fitsio.write_image`` takes them (the kernel table, or nothing)."""
     d, n, t = build_headers(args, sci_header, result, argv0=argv0)
     sz = result.sizes
     extra = ()
@@ -274,6 +275,7 @@ def write_outputs(args, sci_header, result, argv0="hotpants"):
         fitsio.write_image(args.files["out_mask"], (m & 0xffff).astype(np.int32), mh)
     if "savexy" in args.files and getattr(result, "stamps", None) is not None:
         write_savexy(args.files["savexy"], result)
+    return extra
 
 
 def write_savexy(name, result):

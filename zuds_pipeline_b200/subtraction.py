@@ -98,11 +98,25 @@ class _Scratch:
         files += [m.local_path for m in maps]
         for f in files:
             shutil.copy(f, self.path)
-        mine = CalibratableImageBase.from_file(os.path.join(self.path, image.basename), load_others=False)
-        mine.mask_image = MaskImageBase.from_file(os.path.join(self.path, image.mask_image.basename))
+
+        def reopened(src, klass):
+            """``src`` as an object of ``klass`` mapped to the private copy.  Pixels and header already in memory are
+            taken over as they are (what was loaded from the original a moment ago is what the copy holds);
+            an image that was never loaded is read from the copy."""
+            path = os.path.join(self.path, src.basename)
+            if src._data is None:
+                return klass.from_file(path, load_others=False) if klass is CalibratableImageBase else klass.from_file(path)
+            obj = klass()
+            obj.map_to_local_file(path)
+            obj.basename = src.basename
+            obj._data, obj.header = src._data, src.header.copy()
+            obj.header_comments = dict(src.header_comments)
+            return obj
+        mine = reopened(image, CalibratableImageBase)
+        mine.mask_image = reopened(image.mask_image, MaskImageBase)
         for attr in ('_rmsimg', '_weightimg'):
             if hasattr(image, attr):
-                setattr(mine, attr, FITSImage.from_file(os.path.join(self.path, getattr(image, attr).basename)))
+                setattr(mine, attr, reopened(getattr(image, attr), FITSImage))
         return mine
 
 
@@ -196,7 +210,7 @@ class Subtraction(CalibratableImageBase):
             submask_data = prod.mask.cpu().numpy()
 
             # the three products, written where hotpants would have written them, then published next to the science image
-            hotpants.write_outputs(prod.args, my_sci.header, result, argv0='hotpants')
+            table_hdus = hotpants.write_outputs(prod.args, my_sci.header, result, argv0='hotpants')
             submask = MaskImageBase(submask_data, sci.mask_image.header.copy(), os.path.basename(outname.replace('.fits', '.mask.fits')))
             submask.header_comments = dict(sci.mask_image.header_comments)
             submask.header['BIT%d' % HOTPANTS_BIT] = HOTPANTS_BIT
@@ -207,10 +221,19 @@ class Subtraction(CalibratableImageBase):
             for suffix in ('.fits', '.rms.fits', '.mask.fits'):
                 shutil.copy(outname.replace('.fits', suffix), final_out.replace('.fits', suffix))
 
-        sub = cls.from_file(final_out, load_others=False)
-        sub.mask_image = MaskImageBase.from_file(final_out.replace('.fits', '.mask.fits'))
+        def product(klass, path, pixels):
+            """The object ``klass.from_file(path)`` would give: the header as the file holds it, the pixels that were
+            just written to it (37.8 MB per product are not read back and byte-swapped again)."""
+            obj = klass()
+            obj.map_to_local_file(path)
+            obj.basename = os.path.basename(path)
+            obj.header, obj._data = fitsio.read_header(path), pixels
+            return obj
+        sub = product(cls, final_out, result.diff)
+        sub._table_hdus = table_hdus
+        sub.mask_image = product(MaskImageBase, final_out.replace('.fits', '.mask.fits'), submask_data)
         sub.mask_image.parent_image = sub
-        sub._rmsimg = FITSImage.from_file(final_out.replace('.fits', '.rms.fits'))
+        sub._rmsimg = product(FITSImage, final_out.replace('.fits', '.rms.fits'), result.noise)
         for key in ('FIELD', 'CCDID', 'QID', 'FID'):                    # zuds/subtraction.py:193-201
             v = sci.header.get(key)
             if v is not None:
@@ -232,11 +255,18 @@ class Subtraction(CalibratableImageBase):
 
     def save(self):
         """Re-write the primary HDU keeping the -hki kernel table HDU the subtraction wrote."""
-        extra = ()
-        if self.ismapped and os.path.exists(self.local_path):
-            hdus = fitsio.read_hdus(self.local_path)
-            if len(hdus) > 1:
-                extra = tuple(("bintable", h, d) for h, d in hdus[1:])
+        extra = getattr(self, '_table_hdus', None)
+        if extra is None:
+            extra = ()
+            if self.ismapped and os.path.exists(self.local_path):
+                hdus = fitsio.read_hdus(self.local_path)
+                if len(hdus) > 1:
+                    structural = {"XTENSION", "BITPIX", "NAXIS", "NAXIS1", "NAXIS2", "PCOUNT", "GCOUNT", "TFIELDS"}
+                    extra = []
+                    for h, d in hdus[1:]:
+                        h.cards = [c for c in h.cards if c[0] not in structural]      # write_image supplies them
+                        extra.append(("bintable", h, d))
+                    extra = tuple(extra)
         data = np.asarray(self.data, np.float32)
         hdr = self.header.copy()
         for k, c in self.header_comments.items():
