@@ -64,6 +64,9 @@ EXTRA = [
                                        "fi": -7.0, "fin": 99.0}, dict(nstars=420, bad_frac=3e-4)),
     # kernel re-evaluated every 7 pixels instead of every 2 hw + 1 (-kcs, alard.c:1272-1278)
     Case("kcs7", (384, 400), 2.0, 1, {"ko": 2, "kcs": 7}, dict(nstars=300, bad_frac=2e-4)),
+    # ADU pedestals taken off both images before anything else (-tp / -ip, main.c:212-218,728-733), gain/read-noise model
+    Case("pedestals", (384, 400), 2.2, 1, {"ko": 1, "tp": 20.0, "ip": 35.0, "tg": 6.0, "ig": 6.0, "tr": 8.0, "ir": 9.0},
+         dict(nstars=260, bad_frac=2e-4), use_rms=False),
 ]
 
 # -c b: hotpants' own default, the direction chosen per region by check_stamps (alard.c:483-724).  The synthetic

@@ -130,7 +130,6 @@ extern "C" int zb_params_check(const zb_params *p, char *msg, int msglen) {
     // scope of this build
     if (p->fig_merit != 'v') FAIL(ZB_ERR_UNSUPPORTED, "-fom %c is not built; only the default 'v'", p->fig_merit);
     if (p->use_full_ss) FAIL(ZB_ERR_UNSUPPORTED, "useFullSS is not built");
-    if (p->t_pedestal != 0.f || p->i_pedestal != 0.f) FAIL(ZB_ERR_UNSUPPORTED, "-tp/-ip pedestals are not built");
     if (p->ngauss > ZB_MAX_GAUSS) FAIL(ZB_ERR_UNSUPPORTED, "-ng %d > %d", p->ngauss, ZB_MAX_GAUSS);
     if (p->n_ksstamps > ZB_MAX_KSS || p->n_ksstamps < 1) FAIL(ZB_ERR_UNSUPPORTED, "-nss %d outside 1..%d", p->n_ksstamps, ZB_MAX_KSS);
     if (p->nreg_x * p->nreg_y > ZB_MAX_REGIONS) FAIL(ZB_ERR_UNSUPPORTED, "more than %d regions", ZB_MAX_REGIONS);
@@ -279,6 +278,7 @@ extern "C" void zb_destroy(zb_ctx *ctx) {
         cudaStreamDestroy(ctx->st_h2d); cudaStreamDestroy(ctx->st_d2h);
         for (int i = 0; i < 2; i++) { cudaEventDestroy(ctx->ev_h2d[i]); cudaEventDestroy(ctx->ev_d2h[i]); cudaEventDestroy(ctx->ev_done[i]); }
     }
+    for (int i = 0; i < 2; i++) if (ctx->d_ped[i]) cudaFree(ctx->d_ped[i]);
     if (ctx->d_search_scratch) cudaFree(ctx->d_search_scratch);
     if (ctx->d_bkg) cudaFree(ctx->d_bkg);
     if (ctx->h_bkg) cudaFreeHost(ctx->h_bkg);
@@ -742,6 +742,8 @@ extern "C" int zb_subtract(zb_ctx *ctx, const zb_params *p,
     if (cudaSetDevice(ctx->device) != cudaSuccess) return zb_cuda_fail(ctx, cudaGetLastError(), "cudaSetDevice", __FILE__, __LINE__);
     CHECK_RC(zb_configure(ctx, p));
     cudaStream_t st = zb_pick_stream(ctx, stream);
+    if (p->t_pedestal != 0.f || p->i_pedestal != 0.f)          // main.c:728-733; the thresholds moved with them in set_scalars
+        CHECK_RC(zb_launch_pedestals(ctx, sci, ref, p->i_pedestal, p->t_pedestal, (long long)p->nx * p->ny, &sci, &ref, st));
     if (p->force_convolve == 'b')
         return subtract_both(ctx, p, sci, ref, sci_rms, ref_rms, sci_mask, sci_mask_dtype, ref_mask, ref_mask_dtype,
                              diff, noise, out_mask, regions, kernel_sol, stamps_out, st);

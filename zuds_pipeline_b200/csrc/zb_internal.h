@@ -150,6 +150,7 @@ struct zb_ctx {
     double  *d_sol;              // [region][n_comp_total+1]
     double  *d_vv; int *d_indx;  // LU scratch
     ZbFit   *d_fit, *h_fit;
+    float   *d_ped[2]; size_t ped_bytes[2];      // -tp / -ip: the images with their pedestals removed (zb_prepost.cu)
     double  *d_check, *h_check;  // -c b: [n_slots] per-stamp kernel sums + [n_regions] trial kernel sums (zb_check.cu)
     int     *d_jobs, *d_njobs, *h_njobs;
     double  *d_kaks;             // [region][blocks+1]  sum |K| per block in the reference's tap order
@@ -218,6 +219,8 @@ int zb_launch_stamp_sig(zb_ctx *ctx, const float *sci, const float *ref, const f
 int zb_launch_clip(zb_ctx *ctx, cudaStream_t st);
 int zb_launch_region_stats(zb_ctx *ctx, float *noise, int32_t *out_mask, cudaStream_t st);
 int zb_launch_final_sig(zb_ctx *ctx, cudaStream_t st);
+int zb_launch_pedestals(zb_ctx *ctx, const float *sci, const float *ref, float i_ped, float t_ped, long long n,
+                        const float **sci_out, const float **ref_out, cudaStream_t st);
 int zb_check_stamps(zb_ctx *ctx, const float *sci, const float *ref, const float *sci_rms, const float *ref_rms,
                     double *merit, cudaStream_t st);
 

@@ -45,6 +45,14 @@ k_rms_weight(const float *__restrict__ in, const uint8_t *__restrict__ bad, cons
     }
 }
 
+// -tp / -ip (hotpants/main.c:728-733): the ADU pedestal comes off every pixel before anything else looks at it
+__global__ void __launch_bounds__(256)
+k_sub_pedestal(const float *__restrict__ in, float ped, long long n, float *__restrict__ out)
+{
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        out[i] = __fsub_rn(in[i], ped);
+}
+
 static int grid_for(long long n) {
     long long g = (n + 255) / 256;
     return (int)(g < 1 ? 1 : (g > 148 * 16 ? 148 * 16 : g));
@@ -101,4 +109,27 @@ extern "C" int zb_weight_from_rms(zb_ctx *ctx, const float *rms, const uint8_t *
                                   long long n, float *weight, void *stream)
 {
     return rms_weight(ctx, rms, bad, data, sat_level, 0.f, n, weight, 1, stream);
+}
+
+// Copies of the two images with their pedestals removed, in buffers the context keeps (zb_subtract works on them
+// instead of the caller's arrays when -tp / -ip are given).
+int zb_launch_pedestals(zb_ctx *ctx, const float *sci, const float *ref, float i_ped, float t_ped, long long n,
+                        const float **sci_out, const float **ref_out, cudaStream_t st)
+{
+    const size_t bytes = (size_t)n * sizeof(float);
+    for (int k = 0; k < 2; k++) {
+        if (ctx->ped_bytes[k] >= bytes && ctx->d_ped[k]) continue;
+        cudaStreamSynchronize(st);
+        if (ctx->d_ped[k]) cudaFree(ctx->d_ped[k]);
+        ctx->d_ped[k] = NULL; ctx->ped_bytes[k] = 0;
+        if (cudaMalloc((void **)&ctx->d_ped[k], bytes) != cudaSuccess) { snprintf(ctx->err, sizeof ctx->err, "cudaMalloc of %zu bytes failed (pedestal copy)", bytes); return ZB_ERR_NOMEM; }
+        ctx->ped_bytes[k] = bytes;
+    }
+    k_sub_pedestal<<<grid_for(n), 256, 0, st>>>(sci, i_ped, n, ctx->d_ped[0]);
+    k_sub_pedestal<<<grid_for(n), 256, 0, st>>>(ref, t_ped, n, ctx->d_ped[1]);
+    ctx->launches += 2;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return zb_cuda_fail(ctx, e, "k_sub_pedestal", __FILE__, __LINE__);
+    *sci_out = ctx->d_ped[0]; *ref_out = ctx->d_ped[1];
+    return ZB_OK;
 }

@@ -44,6 +44,7 @@ extern "C" int zb_tile_plan(const zb_params *p, int world, int rank, zb_tile_inf
     if (!p || !out || world < 1 || rank < 0 || rank >= world) return ZB_ERR_PARAM;
     if (p->nreg_x != 1 || p->nreg_y != 1) return ZB_ERR_UNSUPPORTED;      // several regions shard by region/pair instead
     if (p->force_convolve == 'b') return ZB_ERR_UNSUPPORTED;               // row tiles fix the direction (-c t | i)
+    if (p->t_pedestal != 0.f || p->i_pedestal != 0.f) return ZB_ERR_UNSUPPORTED;   // the caller's rows are used as they are
     zb_sizes sz;
     int rc = zb_sizes_of(p, &sz);
     if (rc != ZB_OK) return rc;
