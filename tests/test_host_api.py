@@ -251,6 +251,20 @@ def test_fits_scaling_cards_do_not_travel(tmp_path):
     assert np.array_equal(fitsio.read_image(str(tmp_path / "m2.fits"))[0], m)
 
 
+def test_read_header_alone_equals_the_header_of_a_full_read(tmp_path):
+    """from_images re-opens the products it has just written by their headers only (the pixels are in memory)."""
+    from zuds_pipeline_b200 import fitsio
+    h = fitsio.Header()
+    for i in range(300):                                      # more than the first chunk read_header tries
+        h["KEY%04d" % i if i < 100 else "K%d" % i] = i * 0.5
+    h["OBJECT"] = "a string value"
+    for arr in (np.arange(12, dtype=np.float32).reshape(3, 4), np.arange(12, dtype=np.uint16).reshape(3, 4)):
+        path = str(tmp_path / ("x_%s.fits" % arr.dtype.name))
+        fitsio.write_image(path, arr, h)
+        full = fitsio.read_image(path)[1]
+        assert fitsio.read_header(path).cards == full.cards
+
+
 def test_background_estimate_follows_float32_numpy():
     """zuds/utils.py:32-53 on float32 pixels: np.median stays float32 (the two central values of an even count are
     averaged in float32) and so do the deviations; only the 1.4826 factor is double."""
