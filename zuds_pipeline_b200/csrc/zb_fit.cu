@@ -723,15 +723,17 @@ k_lu_subst(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, const dou
     double *b = (double *)dyn;                    // [n]
     double *prod = b + n;                         // [2][n]
     double *dg = prod + 2 * n, *sd1 = dg + n;     // diagonal and first super-diagonal of U
+    int *sidx = (int *)(sd1 + n);                 // the pivots, fetched in parallel: the permutation below walks them one by one
     __shared__ double Lb[32][33];
     for (int i = tid; i < n; i += LU_ST) {
         b[i] = bg[i];
         dg[i] = a[(long long)i * n + i];
         sd1[i] = i + 1 < n ? a[(long long)i * n + i + 1] : 0.0;
+        sidx[i] = indx[i];
     }
     __syncthreads();
     if (tid == 0)
-        for (int i = 0; i < n; i++) { int ip = indx[i]; double t = b[ip]; b[ip] = b[i]; b[i] = t; }
+        for (int i = 0; i < n; i++) { int ip = sidx[i]; double t = b[ip]; b[ip] = b[i]; b[i] = t; }
     __syncthreads();
     for (int j0 = 0; j0 < n; j0 += 32) {
         const int w = min(32, n - j0);
@@ -773,11 +775,14 @@ k_lu_subst(const ZbDev *__restrict__ D, const ZbFit *__restrict__ fit, const dou
             }
             for (; j < n; j++) sum -= p[j];
             b[i] = sum / dg[i];
-        } else if (i >= 1) {
-            // prepare row i-1: products with x_j, j >= i+1 (all known while thread 0 works on row i)
+        } else if (tid >= 32 && i >= 1) {
+            // prepare row i-1: products with x_j, j >= i+1 (all known while thread 0 works on row i).  Warps 1-7 only:
+            // with lanes 1-31 of warp 0 taking part, thread 0's chain ran behind its own warp's global loads (the two
+            // sides of a divergent warp take turns): 2-3 k cycles per matrix row, as much as the chain itself
+            // (ncu source view, profiles/r02_ncu_k_lu_subst_c1b.txt)
             const double *rown = a + (long long)(i - 1) * n;
             double *pn = prod + (size_t)((i - 1) & 1) * n;
-            for (int j = i + 1 + (tid - 1); j < n; j += LU_ST - 1) pn[j] = rown[j] * b[j];
+            for (int j = i + 1 + (tid - 32); j < n; j += LU_ST - 32) pn[j] = rown[j] * b[j];
         }
         __syncthreads();
     }
@@ -1020,7 +1025,7 @@ int zb_launch_fit_solve(zb_ctx *ctx, cudaStream_t st)
             if (n - nb > 0) { k_lu_swap_u<<<dim3((n - nb + 127) / 128, nR), 128, 0, s>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, k0); nlaunch++; }
             if (rest > 0) { k_lu_trail<<<dim3((rest + 31) / 32, (rest + 31) / 32, nR), 256, 0, s>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, k0); nlaunch++; }
         }
-        k_lu_subst<<<nR, LU_ST, (size_t)5 * n * sizeof(double), s>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, ctx->d_sol);
+        k_lu_subst<<<nR, LU_ST, (size_t)5 * n * sizeof(double) + (size_t)n * sizeof(int), s>>>(ctx->d_dev, ctx->d_fit, ctx->d_mat, ctx->d_indx, ctx->d_sol);
         nlaunch++;
     };
     if (use_graph && !(ctx->lu_exec && ctx->lu_key[0] == n && ctx->lu_key[1] == nR)) {
