@@ -505,7 +505,7 @@ def bench_pairs(args):
     line = {
         "metric": METRIC, "value": pairs_total / dev_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32 products folded into f64 per kernel row (k_convolve); f64 fit", "data": "synthetic",
+        "vs_baseline": None, "dtype": "f64 (image convolution and fit, float x double products summed in double as the reference does); the variance sum of k_convolve in f32", "data": "synthetic",
         "config": {"workload": WORKLOADS[args.workload][1]},
         "run": {"pairs_per_step_per_gpu": B, "contexts_per_gpu": W, "host_cores": box_cores,
                 "rank_cores": None if pinned_cores is None else len(pinned_cores), "distinct_pairs_per_gpu": npairs_distinct,
@@ -656,7 +656,7 @@ def bench_c5(args):
         line = {"metric": "coadd-scale frame subtractions/sec (one global fit)", "value": args.steps / tv, "unit": "frames/s",
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tv / args.steps,
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-                "dtype": "f32 products folded into f64 per kernel row (k_convolve); f64 fit",
+                "dtype": "f64 (image convolution and fit, float x double products summed in double as the reference does); the variance sum of k_convolve in f32",
                 "data": "synthetic", "config": {"workload": WORKLOADS["c5"][1]},
                 "run": {"tiles": [i.as_dict() for i in infos] if world > 1 else None,
                         "collectives": "P2P halo rows (inputs, then search-claimed mask rows), all-reduce(SUM) of search records / per-stamp Gram+rhs / per-stamp sigma, gather of output rows on rank 0",
